@@ -1,0 +1,192 @@
+/*
+ * hako.h -- C ABI of libhako_b200.so: the B200-native (sm_100a, ahead-of-time CUDA) replacement for the
+ * GPU half of Ushio/MassiveVoxelRayTracing ("Hako").  Citations are relative to the reference tree.
+ *
+ * What this replaces: the reference has no FFI layer; its "operator API" is three C++ types whose GPU
+ * halves are reached by launch-by-name on an nvrtc module (hipUtil.hpp:112-186):
+ *   IntersectorOctree      IntersectorOctree.hpp:214-266     (CPU build / intersect)
+ *   IntersectorOctreeGPU   IntersectorOctreeGPU.hpp:21-275   (GPU build, device intersect)
+ *   PathTracer             PathTracer.hpp:14-170             (setup / updateScene / step / resolve)
+ * Each entry point below names the reference interface it stands in for.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative HAKO_E_* code otherwise; hako_last_error() returns
+ *     a thread-local message.  (The reference has no return codes: __debugbreak()/abort()/assert,
+ *     hipUtil.hpp:18-22, IntersectorOctreeGPU.hpp:48-51.)
+ *   - `stream` is a cudaStream_t passed as void* (stand-in for oroStream); NULL = the legacy default stream.
+ *     Calls are stream-ordered.  Functions whose pointer arguments are HOST buffers return after the
+ *     results have landed in them; the *_device variants take DEVICE pointers and only enqueue work.
+ *   - handles are opaque and owned by the library; one hako_ctx per device, no hidden statics
+ *     (unlike `static thrs::RadixSort`, IntersectorOctreeGPU.hpp:58).
+ *   - there is NO CPU fallback: every call fails with HAKO_E_CUDA when no sm_100 device is usable.
+ */
+#ifndef HAKO_H
+#define HAKO_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HAKO_OK 0
+#define HAKO_E_INVALID -1 /* bad argument (e.g. gridRes not a power of two: IntersectorOctreeGPU.hpp:48-51 abort()) */
+#define HAKO_E_CUDA -2	  /* CUDA runtime error / no device */
+#define HAKO_E_LIMIT -3	  /* 32-bit / 24-bit format ceiling exceeded (SURVEY.md section 7 hard part 5) */
+#define HAKO_E_STATE -4	  /* call order (e.g. step before resize) */
+
+typedef struct hako_ctx hako_ctx;
+typedef struct hako_octree hako_octree;
+typedef struct hako_pt hako_pt;
+typedef void* hako_stream; /* cudaStream_t */
+
+/* == OctreeNode, voxCommon.hpp:133-138 (68 bytes, align 4).  children[i] = index | mask<<24 after embedMasks
+ * (voxCommon.hpp:183-195); absent and leaf-level children are 0xFFFFFFFF. */
+typedef struct hako_node68
+{
+	uint8_t mask;
+	uint8_t _pad[3];
+	uint32_t children[8];
+	uint32_t nVoxelsPSum[8];
+} hako_node68;
+
+/* == VoxelAttirb, voxCommon.hpp:121-125 */
+typedef struct hako_voxel_attrib
+{
+	uint8_t color[4];
+	uint8_t emission[4];
+} hako_voxel_attrib;
+
+/* == CameraPinhole members, renderCommon.hpp:77-83 (60 bytes) */
+typedef struct hako_camera
+{
+	float o[3];
+	float front[3];
+	float up[3];
+	float right[3];
+	float tanHthetaY;
+	float lensR;
+	float focus;
+} hako_camera;
+
+/* == the POD members of IntersectorOctreeGPU, IntersectorOctreeGPU.hpp:265-274 */
+typedef struct hako_octree_info
+{
+	uint32_t numberOfNodes;
+	uint32_t numberOfVoxels;
+	float lower[3];
+	float upper[3];
+	float dps;
+	float emissionScale;
+	uint32_t hasEmission;
+	int32_t gridRes;
+	uint64_t deviceBytes; /* nodes + attributes (+ kept Morton keys) resident in HBM */
+} hako_octree_info;
+
+/* per-stage record of the last hako_octree_build* call on a context (voxRTGPU.cpp:169-173 prints one total) */
+typedef struct hako_build_stats
+{
+	uint64_t nTriangles;
+	uint64_t dumpedVoxels; /* D: voxels emitted before sort/unique */
+	uint64_t uniqueVoxels; /* U */
+	uint32_t numberOfNodes;
+	uint32_t sortPasses;
+	float ms_h2d, ms_voxelize, ms_sort, ms_unique, ms_octree, ms_total;
+	uint32_t hostSyncs;
+	uint32_t kernelLaunches;
+} hako_build_stats;
+
+const char* hako_last_error( void );
+int hako_version( void );
+
+/* ---- context (replaces oroInitialize/oroCtxCreate/Shader nvrtc compile, voxRTGPU.cpp:25-68) ---- */
+int hako_ctx_create( int device, hako_ctx** out );
+void hako_ctx_destroy( hako_ctx* ctx );
+int hako_ctx_synchronize( hako_ctx* ctx, hako_stream stream );
+int hako_ctx_build_stats( const hako_ctx* ctx, hako_build_stats* out );
+/* number of kernel launches issued through this context since creation (bench.py's gpu_launches claim) */
+uint64_t hako_ctx_launch_count( const hako_ctx* ctx );
+
+/* ---- build: IntersectorOctreeGPU::build, IntersectorOctreeGPU.hpp:40-241 ----
+ * pos/col/emi: 9 floats per triangle (v0,v1,v2), as trianglesFlattened (voxUtil.hpp:8-65) produces.
+ * HOST pointers; the H2D copy is part of the call, as in the reference (:68-70). */
+int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi,
+					   uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out );
+/* same with DEVICE-resident vertex data (per-frame rebuilds skip the H2D) */
+int hako_octree_build_device( hako_ctx* ctx, hako_stream stream, const float* pos_d, const float* col_d, const float* emi_d,
+							  uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out );
+/* IntersectorOctree::buildDAGReference / build, IntersectorOctree.hpp:221-235: sorted unique Morton list
+ * (HOST) -> octree.  attrs may be NULL.  dag = 1: DAG (reference numbering), 0: naive (no dedupe). */
+int hako_octree_build_from_morton( hako_ctx* ctx, hako_stream stream, const uint64_t* mortons, const hako_voxel_attrib* attrs,
+								   uint64_t n, const float origin[3], float dps, int gridRes, int dag, hako_octree** out );
+/* upload a tree built elsewhere (canonical 68-byte layout, masks embedded); parity tooling */
+int hako_octree_import( hako_ctx* ctx, hako_stream stream, const hako_node68* nodes, uint32_t nNodes,
+						const hako_voxel_attrib* attrs, uint32_t nVoxels, const float lower[3], const float upper[3], float dps,
+						hako_octree** out );
+int hako_octree_info_get( const hako_octree* o, hako_octree_info* out );
+/* download in the reference layout.  Any of nodes / mortons / attrs may be NULL.  HOST pointers. */
+int hako_octree_export( const hako_octree* o, hako_stream stream, hako_node68* nodes, uint64_t* mortons, hako_voxel_attrib* attrs );
+/* IntersectorOctreeGPU::cleanUp, IntersectorOctreeGPU.hpp:26-38 */
+void hako_octree_destroy( hako_octree* o );
+/* device addresses of the resident arrays (for NCCL broadcast by the host layer); sizes in bytes */
+int hako_octree_device_arrays( const hako_octree* o, void** nodes_d, uint64_t* nodeBytes, void** masks_d, uint64_t* maskBytes,
+							   void** attrs_d, uint64_t* attrBytes );
+/* allocate an empty replica of given sizes to receive a broadcast; fill via hako_octree_device_arrays */
+int hako_octree_create_replica( hako_ctx* ctx, const hako_octree_info* info, hako_octree** out );
+
+/* ---- build stages, exposed for stage-level parity and the build sweep (BASELINE config 4) ---- */
+/* voxCount + voxelize, voxKernel.cu:58-166.  HOST in, HOST out.  Call with keys == NULL to get D only.
+ * Emission order is unspecified (the reference's is an atomicAdd race); compare as a multiset. */
+int hako_voxelize( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+				   const float origin[3], float dps, int gridRes, int sixSeparating,
+				   uint64_t* keys, hako_voxel_attrib* attrs, uint64_t capacity, uint64_t* D );
+/* thrs::RadixSort::sortPairs, tinyhipradixsort.hpp:849-944: stable LSD sort of (u64 key, u64 value) on bits
+ * [beginBit, endBit).  DEVICE pointers, sorted in place.  values_d may be NULL (sortKeys). */
+int hako_sort_pairs_device( hako_ctx* ctx, hako_stream stream, uint64_t* keys_d, uint64_t* values_d, uint64_t n, int beginBit, int endBit );
+/* HOST convenience wrapper of the above */
+int hako_sort_pairs( hako_ctx* ctx, hako_stream stream, uint64_t* keys, uint64_t* values, uint64_t n, int beginBit, int endBit );
+/* `unique` kernel, voxKernel.cu:170-243 == mergeVoxels, voxRT.cpp:14-51: sorted (key, attrib) -> first of each run,
+ * integer-mean attributes.  HOST in/out (in place), *U receives the count. */
+int hako_unique_merge( hako_ctx* ctx, hako_stream stream, uint64_t* keys, hako_voxel_attrib* attrs, uint64_t n, uint64_t* U, uint32_t* hasEmission );
+
+/* ---- intersect: IntersectorOctreeGPU::intersect (device, :243-251) / IntersectorOctree::intersect (:248-257) ----
+ * ro/rd: 3 floats per ray (rd un-normalised).  Caller presets t = FLT_MAX; a miss leaves t / nMajor / vIndex
+ * untouched (voxRT.cpp:313-325).  HOST pointers. */
+int hako_intersect_batch( const hako_octree* o, hako_stream stream, const float* ro, const float* rd, uint64_t n, int isShadowRay,
+						  float* t, int32_t* nMajor, uint32_t* vIndex );
+int hako_intersect_batch_device( const hako_octree* o, hako_stream stream, const float* ro_d, const float* rd_d, uint64_t n, int isShadowRay,
+								 float* t_d, int32_t* nMajor_d, uint32_t* vIndex_d );
+
+/* ---- primary rays: `render` kernel, voxKernel.cu:437-483 / renderLine, voxRT.cpp:307-347 ----
+ * Pixel-centre rays of rows [y0, y1) of a w x h image (the row range is how image tiles are sharded over GPUs).
+ * Outputs are (y1-y0) x w, row-major; any may be NULL.  rgba: hit -> (hitN+1)/2 or voxel colour, miss -> (0,0,0,255).
+ * t / nMajor / vIndex: miss -> FLT_MAX / -1 / 0xFFFFFFFF. */
+int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_camera* cam, int w, int h, int y0, int y1,
+						 int showVertexColor, uint8_t* rgba, float* t, int32_t* nMajor, uint32_t* vIndex );
+int hako_render_primary_device( const hako_octree* o, hako_stream stream, const hako_camera* cam, int w, int h, int y0, int y1,
+								int showVertexColor, uint8_t* rgba_d, float* t_d, int32_t* nMajor_d, uint32_t* vIndex_d );
+
+/* ---- path tracer: PathTracer, PathTracer.hpp:14-170 ---- */
+/* setup (:43-69): PMJ table generation (pmjSampler.hpp:114-134) + upload.  No stack pool (DynamicAllocatorGPU is replaced). */
+int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out );
+void hako_pt_destroy( hako_pt* pt ); /* cleanUp, :70-79 */
+int hako_pt_resize( hako_pt* pt, hako_stream stream, int w, int h ); /* resizeFrameBufferIfNeeded, :81-97 */
+int hako_pt_clear( hako_pt* pt, hako_stream stream );				 /* clearFrameBuffer, :98-103 */
+/* loadHDRI (:104-116) minus the file decode: RGBA32F pixels (HOST), optional separate primary image (may be NULL). */
+int hako_pt_load_hdri( hako_pt* pt, hako_stream stream, const float* rgba, int w, int h, const float* rgbaPrimary, int wP, int hP );
+/* step (:150-169): one call = 16 spp; `iteration` is m_steps (spp = iteration*16 + localSpp, voxKernel.cu:642).
+ * Rows [y0,y1) only (tile sharding); maxDepth: reference = 8 (voxKernel.cu:691). */
+int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const hako_camera* cam, int iteration, int y0, int y1, int maxDepth );
+int hako_pt_resolve( hako_pt* pt, hako_stream stream );										/* resolve, :118-127 */
+int hako_pt_read_rgba8( hako_pt* pt, hako_stream stream, uint8_t* rgba );					/* toImageAsync, :128-137 (HOST) */
+int hako_pt_read_accum( hako_pt* pt, hako_stream stream, float* rgbw );						/* float4 accumulators (HOST) */
+int hako_pt_accum_device( hako_pt* pt, void** accum_d, uint64_t* bytes );					/* for ncclReduce by the host layer */
+int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, int reset ); /* traversal calls since reset */
+/* pieces of the sampler / environment exposed for parity tests */
+int hako_pt_pmj_table( hako_pt* pt, hako_stream stream, float* samples /* [128][4096][2], HOST */ );
+int hako_pt_hdri_sats( hako_pt* pt, hako_stream stream, uint32_t* sats /* [7][w*h], HOST */ );
+
+#ifdef __cplusplus
+}
+#endif
+#endif
