@@ -166,6 +166,15 @@ int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_ca
 int hako_render_primary_device( const hako_octree* o, hako_stream stream, const hako_camera* cam, int w, int h, int y0, int y1,
 								int showVertexColor, uint8_t* rgba_d, float* t_d, int32_t* nMajor_d, uint32_t* vIndex_d );
 
+/* ---- camera (host-side math; no device work) ----
+ * CameraPinhole::initFromPerspective( viewMatrix, projMatrix, focus, lensR ), renderCommon.hpp:21-35.
+ * view / proj: column-major 4x4 as glm stores them (glm::value_ptr). */
+int hako_camera_from_matrices( const float view[16], const float proj[16], float focus, float lensR, hako_camera* out );
+/* pr::GetCameraMatrix (libs/prlib/src/pr.cpp:1099-1191) == glm::lookAt + glm::perspectiveFov, then initFromPerspective:
+ * what voxRT.cpp:300-305 / PathTracer::step (PathTracer.hpp:150-160) do with a pr::Camera3D. */
+int hako_camera_lookat( const float eye[3], const float center[3], const float up[3], float fovy, int width, int height,
+						float zNear, float zFar, float focus, float lensR, hako_camera* out );
+
 /* ---- path tracer: PathTracer, PathTracer.hpp:14-170 ---- */
 /* setup (:43-69): PMJ table generation (pmjSampler.hpp:114-134) + upload.  No stack pool (DynamicAllocatorGPU is replaced). */
 int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out );

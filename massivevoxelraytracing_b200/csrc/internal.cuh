@@ -1,0 +1,102 @@
+// internal.cuh -- host-side objects behind the opaque handles of include/hako.h, and the launch plumbing.
+#pragma once
+
+#include <atomic>
+#include <vector>
+
+#include "common.cuh"
+
+struct hako_ctx
+{
+	int device = 0;
+	int smCount = 148;
+	size_t l2Bytes = 0;
+	cudaMemPool_t pool = nullptr;
+	std::atomic<uint64_t> launches{ 0 };
+	hako_build_stats stats{};
+	cudaEvent_t ev[8] = {};
+	// pinned staging word(s) for the few device->host counter reads a build needs
+	uint64_t* pinned = nullptr; // 64 x u64
+};
+
+struct hako_octree
+{
+	hako_ctx* ctx = nullptr;
+	hako::TraceNode* nodes = nullptr;
+	uint8_t* masks = nullptr;
+	hako_voxel_attrib* attrs = nullptr;
+	uint64_t* mortons = nullptr; // sorted unique keys (kept for export / parity), may be null for imported trees
+	uint32_t numberOfNodes = 0;
+	uint32_t numberOfVoxels = 0;
+	hako::V3 lower{}, upper{};
+	float dps = 0.0f;
+	float emissionScale = 7.5f; // IntersectorOctreeGPU.hpp:273
+	uint32_t hasEmission = 0;
+	int gridRes = 0;
+
+	hako::OctreeView view() const
+	{
+		hako::OctreeView v;
+		v.nodes = nodes;
+		v.masks = masks;
+		v.attrs = attrs;
+		v.numberOfNodes = numberOfNodes;
+		v.numberOfVoxels = numberOfVoxels;
+		v.lower = lower;
+		v.upper = upper;
+		v.emissionScale = emissionScale;
+		v.hasEmission = hasEmission;
+		return v;
+	}
+};
+
+namespace hako
+{
+// stream-ordered allocation from the context's pool (replaces the ~12 oroMalloc/oroFree per build,
+// IntersectorOctreeGPU.hpp:94-228; the pool keeps freed blocks so steady-state builds do not hit the driver)
+template <class T>
+inline int dalloc( hako_ctx* ctx, T** p, uint64_t count, cudaStream_t s )
+{
+	*p = nullptr;
+	uint64_t bytes = count * sizeof( T );
+	if( bytes == 0 ) bytes = 16;
+	HAKO_CUDA( cudaMallocFromPoolAsync( (void**)p, bytes, ctx->pool, s ) );
+	return 0;
+}
+template <class T>
+inline void dfree( T* p, cudaStream_t s )
+{
+	if( p ) cudaFreeAsync( (void*)p, s );
+}
+
+// every kernel of the library goes through this so hako_ctx_launch_count() is a true count
+#define HAKO_LAUNCH( ctx, kernel, grid, block, smem, stream, ... )              \
+	do                                                                          \
+	{                                                                           \
+		kernel<<<( grid ), ( block ), ( smem ), ( stream )>>>( __VA_ARGS__ );   \
+		( ctx )->launches.fetch_add( 1, std::memory_order_relaxed );            \
+		cudaError_t le__ = cudaGetLastError();                                  \
+		if( le__ != cudaSuccess ) return hako::cudaFail( le__, #kernel, __FILE__, __LINE__ ); \
+	} while( 0 )
+
+// ---- stage entry points (defined in the per-stage .cu files; all stream-ordered, device pointers) ----
+int traceImportNodes( hako_ctx* ctx, cudaStream_t s, const hako_node68* nodes68_d, uint32_t n, TraceNode* out, uint8_t* masks );
+int traceExportNodes( hako_ctx* ctx, cudaStream_t s, const TraceNode* nodes, const uint8_t* masks, uint32_t n, hako_node68* out68_d );
+int launchIntersectBatch( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, const float* ro, const float* rd, uint64_t n, int shadow,
+						  float* t, int32_t* nMajor, uint32_t* vIndex );
+int launchRenderPrimary( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, const hako_camera& cam, int w, int h, int y0, int y1,
+						 int showVertexColor, uint8_t* rgba, float* t, int32_t* nMajor, uint32_t* vIndex );
+
+// voxelize.cu
+int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D );
+// sort.cu
+int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* values, uint64_t* keysTmp, uint64_t* valuesTmp,
+					 uint64_t n, int beginBit, int endBit, int* resultInTmp );
+// unique.cu
+int uniqueMergeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
+					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, uint64_t* U, uint32_t* hasEmission );
+// octree.cu
+int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, uint64_t n, int gridRes, int dag,
+					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodes, uint32_t* launchesOut );
+} // namespace hako

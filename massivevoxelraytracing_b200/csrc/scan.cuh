@@ -1,0 +1,135 @@
+// scan.cuh -- single-pass device-wide exclusive scan with decoupled look-back, as a device function that fused
+// kernels call once per tile.  It replaces two serialising constructs of the reference:
+//   - StreamCompaction::filter's CAS chain on a {prefix, nextBlock} word + granteeBlockExecutionOrder spin
+//     (StreamCompaction.hpp:121-138,186-196), which orders blocks strictly one after another;
+//   - thrs prefixSumExclusiveInplace's g_iterator chain (tinyhipradixsort.hpp:182-250).
+// Here a tile publishes its aggregate immediately and only *reads* its predecessors, so tiles overlap.
+//
+// Descriptor word (u64): bits 63..62 = status (0 not ready, 1 aggregate, 2 inclusive prefix), bits 61..0 = value.
+// Tile ids come from an atomic ticket so that a tile's predecessors are always resident or finished (forward progress).
+#pragma once
+
+#include "common.cuh"
+
+namespace hako
+{
+#define SCAN_FLAG_AGG ( 1ull << 62 )
+#define SCAN_FLAG_INC ( 2ull << 62 )
+#define SCAN_VALUE_MASK ( ( 1ull << 62 ) - 1 )
+
+struct ScanState
+{
+	unsigned long long* desc; // [numTiles], zero-initialised
+	uint32_t* ticket;		  // zero-initialised
+};
+// bytes to allocate (and zero) for a scan over `tiles` tiles: descriptors, then the ticket
+inline uint64_t scanStateBytes( uint64_t tiles ) { return ( tiles + 2 ) * 8; }
+inline ScanState makeScanState( void* mem, uint64_t tiles )
+{
+	ScanState s;
+	s.desc = (unsigned long long*)mem;
+	s.ticket = (uint32_t*)( s.desc + tiles + 1 );
+	return s;
+}
+
+__device__ __forceinline__ uint32_t scanTakeTicket( const ScanState& st )
+{
+	__shared__ uint32_t s_ticket;
+	if( threadIdx.x == 0 ) s_ticket = atomicAdd( st.ticket, 1u );
+	__syncthreads();
+	return s_ticket;
+}
+
+__device__ __forceinline__ unsigned long long ldVolatile( const unsigned long long* p ) { return *(const volatile unsigned long long*)p; }
+__device__ __forceinline__ void stVolatile( unsigned long long* p, unsigned long long v ) { *(volatile unsigned long long*)p = v; }
+
+// Called by ALL threads of the block with the tile's total (valid in thread 0 at least); returns the exclusive prefix of the
+// tile (sum of the totals of tiles 0..tile-1) to all threads.  Warp 0 does the look-back.
+__device__ __forceinline__ uint64_t scanTilePrefix( const ScanState& st, uint32_t tile, uint64_t tileTotal )
+{
+	__shared__ unsigned long long s_prefix;
+	if( threadIdx.x < 32 )
+	{
+		const uint32_t lane = threadIdx.x;
+		tileTotal = __shfl_sync( 0xFFFFFFFFu, tileTotal, 0 );
+		if( tile == 0 )
+		{
+			if( lane == 0 )
+			{
+				stVolatile( &st.desc[0], SCAN_FLAG_INC | tileTotal );
+				s_prefix = 0;
+			}
+		}
+		else
+		{
+			if( lane == 0 ) stVolatile( &st.desc[tile], SCAN_FLAG_AGG | tileTotal );
+			uint64_t prefix = 0;
+			int64_t base = (int64_t)tile - 1; // lane l inspects tile base - l
+			for( ;; )
+			{
+				const int64_t idx = base - lane;
+				unsigned long long d = SCAN_FLAG_INC; // virtual tiles before 0: inclusive prefix 0
+				if( idx >= 0 )
+				{
+					do
+					{
+						d = ldVolatile( &st.desc[idx] );
+					} while( ( d >> 62 ) == 0 );
+				}
+				const uint32_t incMask = __ballot_sync( 0xFFFFFFFFu, ( d >> 62 ) == 2 );
+				const uint32_t firstInc = incMask ? ( __ffs( incMask ) - 1 ) : 32u;
+				uint64_t v = ( lane <= firstInc ) ? ( d & SCAN_VALUE_MASK ) : 0ull;
+#pragma unroll
+				for( int o = 16; o > 0; o >>= 1 ) v += __shfl_xor_sync( 0xFFFFFFFFu, v, o );
+				prefix += v;
+				if( incMask ) break;
+				base -= 32;
+			}
+			if( lane == 0 )
+			{
+				stVolatile( &st.desc[tile], SCAN_FLAG_INC | ( prefix + tileTotal ) );
+				s_prefix = prefix;
+			}
+		}
+	}
+	__syncthreads();
+	return s_prefix;
+}
+
+// Block-wide exclusive scan of one uint32 per thread (BLOCK threads, BLOCK a multiple of 32, <= 1024).
+// Returns the exclusive prefix; *total receives the block sum (all threads).
+template <int BLOCK>
+__device__ __forceinline__ uint32_t blockExclusiveScan( uint32_t v, uint32_t* total )
+{
+	__shared__ uint32_t s_warp[BLOCK / 32];
+	__shared__ uint32_t s_total;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for( int o = 1; o < 32; o <<= 1 )
+	{
+		uint32_t n = __shfl_up_sync( 0xFFFFFFFFu, inc, o );
+		if( lane >= o ) inc += n;
+	}
+	if( lane == 31 ) s_warp[warp] = inc;
+	__syncthreads();
+	if( warp == 0 )
+	{
+		uint32_t w = ( lane < BLOCK / 32 ) ? s_warp[lane] : 0u;
+		uint32_t winc = w;
+#pragma unroll
+		for( int o = 1; o < 32; o <<= 1 )
+		{
+			uint32_t n = __shfl_up_sync( 0xFFFFFFFFu, winc, o );
+			if( lane >= o ) winc += n;
+		}
+		if( lane < BLOCK / 32 ) s_warp[lane] = winc - w;
+		if( lane == 31 ) s_total = winc;
+	}
+	__syncthreads();
+	const uint32_t r = s_warp[warp] + inc - v;
+	*total = s_total;
+	__syncthreads(); // s_warp / s_total may be reused by the next call
+	return r;
+}
+} // namespace hako

@@ -1,0 +1,206 @@
+// traverse.cuh -- Revelles parametric ray/octree traversal on the 64-byte trace layout.
+//
+// Follows octreeTraverse_EfficientParametric (voxCommon.hpp:231-423, SMALL_STACK + ENABLE_EMBEDED_MASK branch)
+// operation for operation in fp32 (the library is built with -fmad=false, IEEE division), so t / nMajor / vIndex
+// are bit-identical to the CPU IntersectorOctree::intersect (IntersectorOctree.hpp:248-257).
+//
+// What is different from the reference's GPU half:
+//   - no DynamicAllocatorGPU (IntersectorOctreeGPU.hpp:277-361, a 1 GiB global stack pool with CAS locks): the stack is
+//     per-thread, 6 words per entry (one 16-B + one 8-B local store), at most one entry per tree level;
+//   - `scale` is not stored: it is 2^-level, rebuilt exactly from the level counter;
+//   - one descent = ONE 8-byte read-only load (child pointer + voxel prefix sum share a slot) instead of two 4-byte
+//     loads 32 bytes apart in a 68-byte node.
+#pragma once
+
+#include "common.cuh"
+
+namespace hako
+{
+#define HAKO_STACK_DEPTH 22 // <= one push per level, 21-bit Morton axes (morton.hpp:73)
+
+// 2^-level, exact (what `scale *= 0.5f` per descent produces, voxCommon.hpp:385)
+__device__ __forceinline__ float levelScale( uint32_t level ) { return __uint_as_float( ( 127u - level ) << 23 ); }
+
+// returns true on a hit (and then writes t / nMajor / vIndex); a miss leaves the outputs untouched (voxRT.cpp:313-325)
+template <bool SHADOW>
+__device__ __forceinline__ bool octreeTraverse( const OctreeView& v, V3 ro, V3 rd, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
+{
+	if( v.numberOfNodes == 0 ) return false;
+
+	// voxCommon.hpp:240-260: mirror negative directions
+	V3 inv = { 1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z };
+	uint32_t vMask = 0;
+	if( inv.x < 0.0f )
+	{
+		vMask |= 1u;
+		inv.x = -inv.x;
+		ro.x = v.lower.x + v.upper.x - ro.x;
+	}
+	if( inv.y < 0.0f )
+	{
+		vMask |= 2u;
+		inv.y = -inv.y;
+		ro.y = v.lower.y + v.upper.y - ro.y;
+	}
+	if( inv.z < 0.0f )
+	{
+		vMask |= 4u;
+		inv.z = -inv.z;
+		ro.z = v.lower.z + v.upper.z - ro.z;
+	}
+	// :265-269: clamp 1/rd so that (bound - ro) * inv never overflows to inf (no inf * 0)
+	V3 lo = v.lower - ro, up = v.upper - ro;
+	inv.x = smin( inv.x, HAKO_MAX_FLOAT / smax( smax( sabs( lo.x ), sabs( up.x ) ), 1.0f ) );
+	inv.y = smin( inv.y, HAKO_MAX_FLOAT / smax( smax( sabs( lo.y ), sabs( up.y ) ), 1.0f ) );
+	inv.z = smin( inv.z, HAKO_MAX_FLOAT / smax( smax( sabs( lo.z ), sabs( up.z ) ), 1.0f ) );
+
+	// :271-278 root slab test
+	float t0x = lo.x * inv.x, t0y = lo.y * inv.y, t0z = lo.z * inv.z;
+	float c_tx1 = up.x * inv.x, c_ty1 = up.y * inv.y, c_tz1 = up.z * inv.z;
+	if( min3( c_tx1, c_ty1, c_tz1 ) < max3( t0x, t0y, t0z ) ) return false;
+	const float dtx = c_tx1 - t0x, dty = c_ty1 - t0y, dtz = c_tz1 - t0z;
+
+	uint4 stackA[HAKO_STACK_DEPTH]; // node, tx1, ty1, tz1
+	uint2 stackB[HAKO_STACK_DEPTH]; // childMask | level << 8, nVoxelSkipped
+	int sp = 0;
+
+	const uint32_t root = v.numberOfNodes - 1; // the root is the last node (IntersectorOctree.hpp:252)
+	uint32_t c_node = root | ( (uint32_t)__ldg( v.masks + root ) << 24 );
+	uint32_t c_level = 0;
+	uint32_t c_childMask = 0xFFu; // "not chosen yet" (reference: 0xFFFFFFFF)
+	uint32_t c_skipped = 0;
+
+	for( ;; )
+	{
+		const float scale = levelScale( c_level );
+		// :317-319 t0 is recomputed from t1 each visit
+		const float tx0 = c_tx1 - dtx * scale;
+		const float ty0 = c_ty1 - dty * scale;
+		const float tz0 = c_tz1 - dtz * scale;
+		const float lmax = max3( tx0, ty0, tz0 );
+
+		bool descended = false;
+		if( c_node == 0xFFFFFFFFu )
+		{
+			// :322-336 leaf voxel
+			if( 0.0f < lmax )
+			{
+				*tOut = lmax;
+				*nMajorOut = ( lmax == tx0 ) ? 1 : ( ( lmax == ty0 ) ? 2 : 0 );
+				*vIndexOut = c_skipped;
+				return true;
+			}
+		}
+		else
+		{
+			// :338-348
+			const float txM = 0.5f * ( tx0 + c_tx1 );
+			const float tyM = 0.5f * ( ty0 + c_ty1 );
+			const float tzM = 0.5f * ( tz0 + c_tz1 );
+			if( c_childMask == 0xFFu )
+			{
+				c_childMask = ( txM < lmax ? 1u : 0u ) | ( tyM < lmax ? 2u : 0u ) | ( tzM < lmax ? 4u : 0u );
+			}
+			const uint32_t mask = c_node >> 24;
+			float x1 = ( c_childMask & 1u ) ? c_tx1 : txM;
+			float y1 = ( c_childMask & 2u ) ? c_ty1 : tyM;
+			float z1 = ( c_childMask & 4u ) ? c_tz1 : tzM;
+			// :365-411 walk the (at most 4) children the ray crosses inside this node
+			for( ;; )
+			{
+				const float umin = min3( x1, y1, z1 );
+				const uint32_t mv = ( umin == x1 ) ? 1u : ( ( umin == y1 ) ? 2u : 4u );
+				const bool hasNext = ( c_childMask & mv ) == 0;
+				const uint32_t ci = c_childMask ^ vMask;
+				c_childMask |= mv;
+				if( ( ( mask >> ci ) & 1u ) && !( umin < 0.0f ) )
+				{
+					if( hasNext )
+					{
+						stackA[sp] = make_uint4( c_node, __float_as_uint( c_tx1 ), __float_as_uint( c_ty1 ), __float_as_uint( c_tz1 ) );
+						stackB[sp] = make_uint2( c_childMask | ( c_level << 8 ), c_skipped );
+						sp++;
+					}
+					const uint2 slot = ldg_u2( &v.nodes[c_node & 0xFFFFFFu].slot[ci] );
+					c_node = slot.x;
+					c_tx1 = x1;
+					c_ty1 = y1;
+					c_tz1 = z1;
+					c_level++;
+					c_childMask = 0xFFu;
+					if( !SHADOW ) c_skipped += slot.y; // :388-391
+					descended = true;
+					break;
+				}
+				if( !hasNext ) break;
+				if( mv == 1u )
+					x1 = c_tx1;
+				else if( mv == 2u )
+					y1 = c_ty1;
+				else
+					z1 = c_tz1;
+			}
+		}
+		if( descended ) continue;
+		// :414-422 pop
+		if( sp == 0 ) return false;
+		sp--;
+		const uint4 a = stackA[sp];
+		const uint2 b = stackB[sp];
+		c_node = a.x;
+		c_tx1 = __uint_as_float( a.y );
+		c_ty1 = __uint_as_float( a.z );
+		c_tz1 = __uint_as_float( a.w );
+		c_childMask = b.x & 0xFFu;
+		c_level = b.x >> 8;
+		c_skipped = b.y;
+	}
+}
+
+// getHitN, voxCommon.hpp:564-577
+__device__ __forceinline__ V3 getHitN( int major, V3 rd )
+{
+	switch( major )
+	{
+	case 0:
+		return { 0.0f, 0.0f, 0.0f < rd.z ? -1.0f : 1.0f };
+	case 1:
+		return { 0.0f < rd.x ? -1.0f : 1.0f, 0.0f, 0.0f };
+	case 2:
+		return { 0.0f, 0.0f < rd.y ? -1.0f : 1.0f, 0.0f };
+	}
+	return { 0.0f, 0.0f, 0.0f };
+}
+
+// CameraPinhole::shoot, renderCommon.hpp:37-49: ((right * mix) * W) / H + up * mix + front
+__device__ __forceinline__ void cameraShoot( const hako_camera& cam, int x, int y, float ox, float oy, int w, int h, V3* ro, V3* rd )
+{
+	const float xf = ( x + ox ) / w;
+	const float yf = ( y + oy ) / h;
+	const float a = mixf( -cam.tanHthetaY, cam.tanHthetaY, xf );
+	const float b = mixf( cam.tanHthetaY, -cam.tanHthetaY, yf );
+	rd->x = cam.right[0] * a * w / h + cam.up[0] * b + cam.front[0];
+	rd->y = cam.right[1] * a * w / h + cam.up[1] * b + cam.front[1];
+	rd->z = cam.right[2] * a * w / h + cam.up[2] * b + cam.front[2];
+	*ro = { cam.o[0], cam.o[1], cam.o[2] };
+}
+// CameraPinhole::shootThinLens, renderCommon.hpp:50-75
+__device__ __forceinline__ void cameraShootThinLens( const hako_camera& cam, int x, int y, float ox, float oy, int w, int h, float u0, float u1, V3* ro, V3* rd )
+{
+	const float xf = ( x + ox ) / w;
+	const float yf = ( y + oy ) / h;
+	const float fx = cam.focus * mixf( -cam.tanHthetaY, cam.tanHthetaY, xf ) * w / h;
+	const float fy = cam.focus * mixf( cam.tanHthetaY, -cam.tanHthetaY, yf );
+	const float fz = cam.focus;
+	const float lx = mixf( -cam.lensR, cam.lensR, u0 );
+	const float ly = mixf( -cam.lensR, cam.lensR, u1 );
+	const float lz = 0.0f;
+	const float dx = fx - lx, dy = fy - ly, dz = fz - lz;
+	rd->x = cam.right[0] * dx + cam.up[0] * dy + cam.front[0] * dz;
+	rd->y = cam.right[1] * dx + cam.up[1] * dy + cam.front[1] * dz;
+	rd->z = cam.right[2] * dx + cam.up[2] * dy + cam.front[2] * dz;
+	ro->x = cam.o[0] + cam.right[0] * lx + cam.up[0] * ly + cam.front[0] * lz;
+	ro->y = cam.o[1] + cam.right[1] * lx + cam.up[1] * ly + cam.front[1] * lz;
+	ro->z = cam.o[2] + cam.right[2] * lx + cam.up[2] * ly + cam.front[2] * lz;
+}
+} // namespace hako

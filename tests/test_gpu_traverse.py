@@ -1,0 +1,142 @@
+"""GPU parity of the traversal path (hako_octree_import / hako_intersect_batch / hako_render_primary) against the
+CPU oracle: bit-exact t / nMajor / vIndex (fp32 operation order is the reference's; the library is built -fmad=false)."""
+import numpy as np
+import pytest
+
+from scenes import scene_params
+
+pytestmark = pytest.mark.gpu
+FLT_MAX = np.float32(3.402823466e38)
+
+
+@pytest.fixture(scope="module")
+def hk():
+    import massivevoxelraytracing_b200 as h
+    return h
+
+
+@pytest.fixture(scope="module")
+def ctx(hk):
+    c = hk.Context(0)
+    yield c
+    c.close()
+
+
+def _oracle_tree(oracle, bunny, grid):
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), grid)
+    mk, mc, me = oracle.merge_voxels(keys, c, e)
+    tree = oracle.build_octree(mk, origin, float(dps), grid)
+    return tree, mk, mc, me, origin, dps
+
+
+def _import(hk, ctx, tree, mc, me, dps):
+    lo, up = tree.bounds()
+    attrs = np.zeros(mc.shape[0], hk.VOXEL_ATTRIB)
+    attrs["color"] = mc
+    attrs["emission"] = me
+    g = hk.IntersectorOctreeGPU(ctx)
+    g.import_nodes(tree.nodes(), lo, up, float(dps), attrs)
+    return g, attrs
+
+
+@pytest.mark.parametrize("grid,W,H", [(16, 64, 64), (64, 256, 256), (256, 1024, 1024)])
+def test_render_primary_matches_oracle(hk, ctx, oracle, bunny, golden, grid, W, H):
+    tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, grid)
+    g, attrs = _import(hk, ctx, tree, mc, me, dps)
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H)
+    ocam = oracle.camera_lookat((4, 4, 4), (0, 0, 0), (0, 1, 0), None, W, H)
+    assert bytes(cam) == bytes(ocam)
+    t, nm, vi = tree.render_primary(ocam, W, H, threads=8)
+    rgba, gt, gnm, gvi = g.render(cam, W, H)
+    np.testing.assert_array_equal(gvi.reshape(-1), vi)
+    np.testing.assert_array_equal(gnm.reshape(-1), nm)
+    np.testing.assert_array_equal(gt.reshape(-1).view(np.uint32), t.view(np.uint32))   # bit-exact, stricter than 1e-6 rel
+    case = golden["cases"][str(grid)]
+    if case["image"] == [W, H]:
+        assert "%016x" % oracle.fnv1a64(gvi) == case["fnv_vindex"]
+        assert "%016x" % oracle.fnv1a64(gnm) == case["fnv_nmajor"]
+        assert "%016x" % oracle.fnv1a64(gt) == case["fnv_t"]
+        assert int((gt != FLT_MAX).sum()) == case["hits"]
+    # normal-colour image: miss -> (0,0,0,255); hit -> (hitN + 1) / 2 (voxKernel.cu:470-476)
+    hit = (gt != FLT_MAX)
+    assert (rgba[~hit] == np.array([0, 0, 0, 255], np.uint8)).all()
+    assert (rgba[hit][:, 3] == 255).all() and set(np.unique(rgba[hit][:, :3])) <= {0, 128, 255}
+    # vertex-colour image == attribute lookup by hit id (voxKernel.cu:466-468)
+    rgba2, _, _, _ = g.render(cam, W, H, showVertexColor=True, ids=False)
+    np.testing.assert_array_equal(rgba2[hit], attrs["color"][gvi[hit]])
+    # row-range sharding (how image tiles are split over GPUs) gives the same pixels
+    y0, y1 = H // 3, H // 3 + 37 if H > 64 else H // 3 + 5
+    _, t2, nm2, vi2 = g.render(cam, W, H, y0=y0, y1=y1)
+    np.testing.assert_array_equal(vi2, gvi[y0:y1])
+    np.testing.assert_array_equal(t2.view(np.uint32), gt[y0:y1].view(np.uint32))
+    g.cleanUp()
+
+
+def test_export_roundtrip(hk, ctx, oracle, bunny):
+    tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 64)
+    g, attrs = _import(hk, ctx, tree, mc, me, dps)
+    nodes, _, a = g.export(nodes=True, attrs=True)
+    ref = tree.nodes()
+    for f in ("mask", "children", "psum"):
+        np.testing.assert_array_equal(nodes[f], ref[f])
+    np.testing.assert_array_equal(a, attrs)
+    assert g.m_numberOfNodes == ref.size and g.m_numberOfVoxels == mk.size
+    assert g.hasEmission() == bool(me[:, :3].any())
+
+
+def test_random_rays_and_shadow(hk, ctx, oracle, bunny, small_cases):
+    s = small_cases
+    tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 64)
+    g, _ = _import(hk, ctx, tree, mc, me, dps)
+    t, nm, vi = g.intersect(s["rays_ro"], s["rays_rd"])
+    np.testing.assert_array_equal(t.view(np.uint32), s["rays_t"].view(np.uint32))
+    np.testing.assert_array_equal(nm.astype(np.int8), s["rays_nmajor"])
+    np.testing.assert_array_equal(vi, s["rays_vindex"])
+    ts, _, vis = g.intersect(s["rays_ro"], s["rays_rd"], isShadowRay=True)
+    np.testing.assert_array_equal(ts.view(np.uint32), s["rays_shadow_t"].view(np.uint32))
+    np.testing.assert_array_equal(vis, s["rays_shadow_vindex"])
+    # caller presets survive a miss (voxRT.cpp:313-325)
+    n = s["rays_ro"].shape[0]
+    t0 = np.full(n, 123.0, np.float32)
+    nm0 = np.full(n, 77, np.int32)
+    vi0 = np.full(n, 99, np.uint32)
+    g.intersect(s["rays_ro"], s["rays_rd"], t0, nm0, vi0)
+    miss = s["rays_t"] == FLT_MAX
+    assert miss.any() and (t0[miss] == 123.0).all() and (nm0[miss] == 77).all() and (vi0[miss] == 99).all()
+    np.testing.assert_array_equal(vi0[~miss], s["rays_vindex"][~miss])
+
+
+def test_edge_rays(hk, ctx, oracle, bunny):
+    """axis-parallel rays (rd component = +-0), rays starting inside, negative directions, zero-length batches"""
+    tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 64)
+    g, _ = _import(hk, ctx, tree, mc, me, dps)
+    lo, up = tree.bounds()
+    c = (lo + up) * np.float32(0.5)
+    rng = np.random.default_rng(3)
+    ro, rd = [], []
+    for ax in range(3):
+        for sgn in (1.0, -1.0):
+            for k in range(200):
+                o = c + (rng.random(3).astype(np.float32) - np.float32(0.5)) * (up - lo)
+                d = np.zeros(3, np.float32)
+                d[ax] = sgn
+                if k % 2:
+                    d[(ax + 1) % 3] = -0.0
+                o[ax] = (lo[ax] - 1.0) if sgn > 0 else (up[ax] + 1.0)
+                ro.append(o)
+                rd.append(d)
+    inside = c + (rng.random((500, 3)).astype(np.float32) - np.float32(0.5)) * (up - lo) * np.float32(0.9)
+    ro += list(inside)
+    rd += list(rng.standard_normal((500, 3)).astype(np.float32) * np.float32(1e-3))   # un-normalised, tiny
+    ro = np.array(ro, np.float32)
+    rd = np.array(rd, np.float32)
+    t, nm, vi = tree.intersect(ro, rd)
+    gt, gnm, gvi = g.intersect(ro, rd)
+    np.testing.assert_array_equal(gt.view(np.uint32), t.view(np.uint32))
+    np.testing.assert_array_equal(gnm, nm)
+    np.testing.assert_array_equal(gvi, vi)
+    assert (t != FLT_MAX).sum() > 100
+    e = np.zeros((0, 3), np.float32)
+    assert g.intersect(e, e)[0].size == 0
