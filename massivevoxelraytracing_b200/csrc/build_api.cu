@@ -1,0 +1,363 @@
+// build_api.cu -- C ABI of the build path: IntersectorOctreeGPU::build (IntersectorOctreeGPU.hpp:40-241),
+// IntersectorOctree::build / buildDAGReference (IntersectorOctree.hpp:221-235) and the individual stages.
+//
+// Launch sequence of the reference: voxCount -> [sync] -> voxelize -> sortPairs (3 kernels x P) -> [sync] -> unique -> [sync]
+// -> octreeTaskInit -> [sync] -> bottomUpOctreeBuild x log2(N) (+ memset of the hash table per level) -> [sync] -> D2D compaction
+// -> embedMasks, with ~12 oroMalloc/oroFree.  Here: columns -> [read] -> count -> [read D] -> emit -> histogram + P onesweep
+// passes -> unique -> [read U] -> level histogram -> [read] -> 4 kernels per level -> [read node count] -> D2D copy.
+// Allocations come from the context's stream-ordered pool.
+#include "internal.cuh"
+
+using namespace hako;
+
+namespace hako
+{
+int uniqueMergeLaunch( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
+					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, unsigned long long* counters_d );
+}
+
+#define CHECK_ARG( cond, msg )           \
+	do                                   \
+	{                                    \
+		if( !( cond ) )                  \
+		{                                \
+			hako::setError( "%s", msg ); \
+			return HAKO_E_INVALID;       \
+		}                                \
+	} while( 0 )
+
+static bool isPow2( int v ) { return v > 0 && ( v & ( v - 1 ) ) == 0; }
+static int log2i( int v )
+{
+	int l = 0;
+	while( ( 1 << l ) < v ) l++;
+	return l;
+}
+// IntersectorOctreeGPU.hpp:118: sort bits = next multiple of 8 of 3 * log2( gridRes )
+static int sortEndBit( int gridRes )
+{
+	int bits = 3 * log2i( gridRes );
+	return ( bits + 7 ) / 8 * 8;
+}
+
+static void initOctree( hako_octree* o, hako_ctx* ctx, const float origin[3], float dps, int gridRes )
+{
+	o->ctx = ctx;
+	o->lower = { origin[0], origin[1], origin[2] };
+	// IntersectorOctreeGPU.hpp:63-65 / IntersectorOctree.hpp:224: upper = origin + dps * gridRes
+	const float ext = dps * (float)gridRes;
+	o->upper = { origin[0] + ext, origin[1] + ext, origin[2] + ext };
+	o->dps = dps;
+	o->gridRes = gridRes;
+}
+
+static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float* pos_d, const float* col_d, const float* emi_d, uint32_t nTriangles,
+									 const float origin[3], float dps, int gridRes, hako_octree** out )
+{
+	hako_build_stats& st = ctx->stats;
+	const uint64_t launches0 = ctx->launches.load();
+	hako_octree* o = new hako_octree();
+	initOctree( o, ctx, origin, dps, gridRes );
+	uint64_t *keys = nullptr, *values = nullptr, *keysTmp = nullptr, *valuesTmp = nullptr;
+	int r = 0;
+	do
+	{
+		cudaError_t e;
+#define CK( call )                                    \
+	if( ( e = ( call ) ) != cudaSuccess )             \
+	{                                                 \
+		r = cudaFail( e, #call, __FILE__, __LINE__ ); \
+		break;                                        \
+	}
+		CK( cudaEventRecord( ctx->ev[1], s ) );
+		uint64_t D = 0;
+		if( ( r = voxelizeDevice( ctx, s, pos_d, col_d, emi_d, nTriangles, o->lower, dps, gridRes, 1 /* sixSeparating: voxKernel.cu:68,109 */, &keys, &values, &D ) ) ) break;
+		st.dumpedVoxels = D;
+		CK( cudaEventRecord( ctx->ev[2], s ) );
+		uint64_t U = 0;
+		if( D )
+		{
+			if( ( r = dalloc( ctx, &keysTmp, D, s ) ) ) break;
+			if( ( r = dalloc( ctx, &valuesTmp, D, s ) ) ) break;
+			int inTmp = 0;
+			if( ( r = sortPairsDevice( ctx, s, keys, values, keysTmp, valuesTmp, D, 0, sortEndBit( gridRes ), &inTmp ) ) ) break;
+			CK( cudaEventRecord( ctx->ev[3], s ) );
+			uint64_t* sk = inTmp ? keysTmp : keys;
+			uint64_t* sv = inTmp ? valuesTmp : values;
+			uint64_t* uk = inTmp ? keys : keysTmp; // unique writes out of place into the idle buffers
+			uint64_t* ua = inTmp ? values : valuesTmp;
+			uint32_t he = 0;
+			if( ( r = uniqueMergeDevice( ctx, s, sk, sv, D, uk, (hako_voxel_attrib*)ua, &U, &he ) ) ) break;
+			o->hasEmission = he;
+			// keep exact-size copies resident; the D-sized work buffers go back to the pool
+			if( ( r = dalloc( ctx, &o->mortons, U, s ) ) ) break;
+			if( ( r = dalloc( ctx, &o->attrs, U, s ) ) ) break;
+			CK( cudaMemcpyAsync( o->mortons, uk, U * 8, cudaMemcpyDeviceToDevice, s ) );
+			CK( cudaMemcpyAsync( o->attrs, ua, U * 8, cudaMemcpyDeviceToDevice, s ) );
+		}
+		else
+		{
+			CK( cudaEventRecord( ctx->ev[3], s ) );
+		}
+		st.uniqueVoxels = U;
+		if( U >= 0xFFFFFFFFull )
+		{
+			setError( "build: %llu voxels exceed the 32-bit voxel index", (unsigned long long)U );
+			r = HAKO_E_LIMIT;
+			break;
+		}
+		o->numberOfVoxels = (uint32_t)U;
+		CK( cudaEventRecord( ctx->ev[4], s ) );
+		if( ( r = buildOctreeDevice( ctx, s, o->mortons, U, gridRes, 1, &o->nodes, &o->masks, &o->numberOfNodes, nullptr ) ) ) break;
+		st.numberOfNodes = o->numberOfNodes;
+		CK( cudaEventRecord( ctx->ev[5], s ) );
+		CK( cudaStreamSynchronize( s ) );
+		st.hostSyncs++;
+		cudaEventElapsedTime( &st.ms_voxelize, ctx->ev[1], ctx->ev[2] );
+		cudaEventElapsedTime( &st.ms_sort, ctx->ev[2], ctx->ev[3] );
+		cudaEventElapsedTime( &st.ms_unique, ctx->ev[3], ctx->ev[4] );
+		cudaEventElapsedTime( &st.ms_octree, ctx->ev[4], ctx->ev[5] );
+		cudaEventElapsedTime( &st.ms_h2d, ctx->ev[0], ctx->ev[1] );
+		cudaEventElapsedTime( &st.ms_total, ctx->ev[0], ctx->ev[5] );
+#undef CK
+	} while( 0 );
+	dfree( keys, s ), dfree( values, s ), dfree( keysTmp, s ), dfree( valuesTmp, s );
+	st.kernelLaunches = (uint32_t)( ctx->launches.load() - launches0 );
+	if( r )
+	{
+		hako_octree_destroy( o );
+		return r;
+	}
+	*out = o;
+	return HAKO_OK;
+}
+
+extern "C" {
+
+int hako_octree_build_device( hako_ctx* ctx, hako_stream stream, const float* pos_d, const float* col_d, const float* emi_d,
+							  uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out )
+{
+	CHECK_ARG( ctx && out && origin, "hako_octree_build_device: null argument" );
+	CHECK_ARG( nTriangles == 0 || ( pos_d && col_d && emi_d ), "hako_octree_build_device: null vertex data" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build: gridRes must be a power of two <= 2^21 (IntersectorOctreeGPU.hpp:48-51 aborts)" );
+	CHECK_ARG( dps > 0.0f, "hako_octree_build: dps must be positive" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	ctx->stats.nTriangles = nTriangles;
+	HAKO_CUDA( cudaEventRecord( ctx->ev[0], s ) );
+	return buildFromDeviceTriangles( ctx, s, pos_d, col_d, emi_d, nTriangles, origin, dps, gridRes, out );
+}
+
+int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi,
+					   uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out )
+{
+	CHECK_ARG( ctx && out && origin, "hako_octree_build: null argument" );
+	CHECK_ARG( nTriangles == 0 || ( pos && col && emi ), "hako_octree_build: null vertex data" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build: gridRes must be a power of two <= 2^21 (IntersectorOctreeGPU.hpp:48-51 aborts)" );
+	CHECK_ARG( dps > 0.0f, "hako_octree_build: dps must be positive" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	ctx->stats.nTriangles = nTriangles;
+	HAKO_CUDA( cudaEventRecord( ctx->ev[0], s ) );
+	// IntersectorOctreeGPU.hpp:68-70: the three vertex arrays go up with the call
+	float* d = nullptr;
+	const uint64_t nf = (uint64_t)nTriangles * 9;
+	HAKO_TRY( dalloc( ctx, &d, nf * 3, s ) );
+	int r = 0;
+	if( nf )
+	{
+		cudaError_t e = cudaMemcpyAsync( d, pos, nf * 4, cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( d + nf, col, nf * 4, cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( d + 2 * nf, emi, nf * 4, cudaMemcpyHostToDevice, s );
+		if( e != cudaSuccess ) r = cudaFail( e, "H2D vertices", __FILE__, __LINE__ );
+	}
+	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out );
+	dfree( d, s );
+	return r;
+}
+
+int hako_octree_build_from_morton( hako_ctx* ctx, hako_stream stream, const uint64_t* mortons, const hako_voxel_attrib* attrs,
+								   uint64_t n, const float origin[3], float dps, int gridRes, int dag, hako_octree** out )
+{
+	CHECK_ARG( ctx && out && origin && ( n == 0 || mortons ), "hako_octree_build_from_morton: null argument" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build_from_morton: gridRes must be a power of two <= 2^21" );
+	CHECK_ARG( n < 0xFFFFFFFFull, "hako_octree_build_from_morton: more than 2^32 - 1 voxels" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	hako_octree* o = new hako_octree();
+	initOctree( o, ctx, origin, dps, gridRes );
+	o->numberOfVoxels = (uint32_t)n;
+	int r = 0;
+	do
+	{
+		cudaError_t e;
+		if( ( r = dalloc( ctx, &o->mortons, n, s ) ) ) break;
+		if( n && ( e = cudaMemcpyAsync( o->mortons, mortons, n * 8, cudaMemcpyHostToDevice, s ) ) != cudaSuccess )
+		{
+			r = cudaFail( e, "H2D mortons", __FILE__, __LINE__ );
+			break;
+		}
+		if( attrs && n )
+		{
+			if( ( r = dalloc( ctx, &o->attrs, n, s ) ) ) break;
+			if( ( e = cudaMemcpyAsync( o->attrs, attrs, n * 8, cudaMemcpyHostToDevice, s ) ) != cudaSuccess )
+			{
+				r = cudaFail( e, "H2D attrs", __FILE__, __LINE__ );
+				break;
+			}
+			for( uint64_t i = 0; i < n && !o->hasEmission; i++ ) o->hasEmission = ( attrs[i].emission[0] | attrs[i].emission[1] | attrs[i].emission[2] ) != 0;
+		}
+		uint32_t launches = 0;
+		if( ( r = buildOctreeDevice( ctx, s, o->mortons, n, gridRes, dag, &o->nodes, &o->masks, &o->numberOfNodes, &launches ) ) ) break;
+		ctx->stats.uniqueVoxels = n;
+		ctx->stats.numberOfNodes = o->numberOfNodes;
+		ctx->stats.kernelLaunches = launches;
+		if( ( e = cudaStreamSynchronize( s ) ) != cudaSuccess ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+	} while( 0 );
+	if( r )
+	{
+		hako_octree_destroy( o );
+		return r;
+	}
+	*out = o;
+	return HAKO_OK;
+}
+
+int hako_voxelize( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+				   const float origin[3], float dps, int gridRes, int sixSeparating,
+				   uint64_t* keys, hako_voxel_attrib* attrs, uint64_t capacity, uint64_t* D )
+{
+	CHECK_ARG( ctx && origin && D, "hako_voxelize: null argument" );
+	CHECK_ARG( nTriangles == 0 || pos, "hako_voxelize: null vertex data" );
+	CHECK_ARG( gridRes > 0 && dps > 0.0f, "hako_voxelize: bad grid" );
+	CHECK_ARG( !keys || ( col && emi && attrs ), "hako_voxelize: emitting needs colours, emissions and an attribute buffer" );
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	*D = 0;
+	const uint64_t nf = (uint64_t)nTriangles * 9;
+	float* d = nullptr;
+	HAKO_TRY( dalloc( ctx, &d, nf * 3, s ) );
+	uint64_t *k_d = nullptr, *v_d = nullptr;
+	int r = 0;
+	do
+	{
+		cudaError_t e = cudaSuccess;
+		if( nf )
+		{
+			e = cudaMemcpyAsync( d, pos, nf * 4, cudaMemcpyHostToDevice, s );
+			if( e == cudaSuccess && keys ) e = cudaMemcpyAsync( d + nf, col, nf * 4, cudaMemcpyHostToDevice, s );
+			if( e == cudaSuccess && keys ) e = cudaMemcpyAsync( d + 2 * nf, emi, nf * 4, cudaMemcpyHostToDevice, s );
+		}
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "H2D vertices", __FILE__, __LINE__ );
+			break;
+		}
+		const V3 org = { origin[0], origin[1], origin[2] };
+		if( ( r = voxelizeDevice( ctx, s, d, d + nf, d + 2 * nf, nTriangles, org, dps, gridRes, sixSeparating, keys ? &k_d : nullptr, keys ? &v_d : nullptr, D ) ) ) break;
+		if( keys && *D )
+		{
+			if( *D > capacity )
+			{
+				setError( "hako_voxelize: capacity %llu < %llu dumped voxels", (unsigned long long)capacity, (unsigned long long)*D );
+				r = HAKO_E_INVALID;
+				break;
+			}
+			e = cudaMemcpyAsync( keys, k_d, *D * 8, cudaMemcpyDeviceToHost, s );
+			if( e == cudaSuccess ) e = cudaMemcpyAsync( attrs, v_d, *D * 8, cudaMemcpyDeviceToHost, s );
+			if( e != cudaSuccess )
+			{
+				r = cudaFail( e, "D2H voxels", __FILE__, __LINE__ );
+				break;
+			}
+		}
+		if( ( e = cudaStreamSynchronize( s ) ) != cudaSuccess ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+	} while( 0 );
+	dfree( d, s ), dfree( k_d, s ), dfree( v_d, s );
+	return r;
+}
+
+int hako_sort_pairs_device( hako_ctx* ctx, hako_stream stream, uint64_t* keys_d, uint64_t* values_d, uint64_t n, int beginBit, int endBit )
+{
+	CHECK_ARG( ctx && ( n == 0 || keys_d ), "hako_sort_pairs_device: null argument" );
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	if( n == 0 ) return HAKO_OK;
+	uint64_t *kt = nullptr, *vt = nullptr;
+	int r = dalloc( ctx, &kt, n, s );
+	if( !r && values_d ) r = dalloc( ctx, &vt, n, s );
+	if( !r ) r = sortPairsDevice( ctx, s, keys_d, values_d, kt, vt, n, beginBit, endBit, nullptr );
+	dfree( kt, s ), dfree( vt, s );
+	return r;
+}
+
+int hako_sort_pairs( hako_ctx* ctx, hako_stream stream, uint64_t* keys, uint64_t* values, uint64_t n, int beginBit, int endBit )
+{
+	CHECK_ARG( ctx && ( n == 0 || keys ), "hako_sort_pairs: null argument" );
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	if( n == 0 ) return HAKO_OK;
+	uint64_t *k_d = nullptr, *v_d = nullptr;
+	int r = dalloc( ctx, &k_d, n, s );
+	if( !r && values ) r = dalloc( ctx, &v_d, n, s );
+	do
+	{
+		if( r ) break;
+		cudaError_t e = cudaMemcpyAsync( k_d, keys, n * 8, cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess && values ) e = cudaMemcpyAsync( v_d, values, n * 8, cudaMemcpyHostToDevice, s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "H2D", __FILE__, __LINE__ );
+			break;
+		}
+		if( ( r = hako_sort_pairs_device( ctx, stream, k_d, v_d, n, beginBit, endBit ) ) ) break;
+		e = cudaMemcpyAsync( keys, k_d, n * 8, cudaMemcpyDeviceToHost, s );
+		if( e == cudaSuccess && values ) e = cudaMemcpyAsync( values, v_d, n * 8, cudaMemcpyDeviceToHost, s );
+		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
+		if( e != cudaSuccess ) r = cudaFail( e, "D2H", __FILE__, __LINE__ );
+	} while( 0 );
+	dfree( k_d, s ), dfree( v_d, s );
+	return r;
+}
+
+int hako_unique_merge( hako_ctx* ctx, hako_stream stream, uint64_t* keys, hako_voxel_attrib* attrs, uint64_t n, uint64_t* U, uint32_t* hasEmission )
+{
+	CHECK_ARG( ctx && U && ( n == 0 || ( keys && attrs ) ), "hako_unique_merge: null argument" );
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	*U = 0;
+	if( hasEmission ) *hasEmission = 0;
+	if( n == 0 ) return HAKO_OK;
+	uint64_t *k_d = nullptr, *v_d = nullptr, *ko_d = nullptr, *vo_d = nullptr;
+	int r = dalloc( ctx, &k_d, n, s );
+	if( !r ) r = dalloc( ctx, &v_d, n, s );
+	if( !r ) r = dalloc( ctx, &ko_d, n, s );
+	if( !r ) r = dalloc( ctx, &vo_d, n, s );
+	do
+	{
+		if( r ) break;
+		cudaError_t e = cudaMemcpyAsync( k_d, keys, n * 8, cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( v_d, attrs, n * 8, cudaMemcpyHostToDevice, s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "H2D", __FILE__, __LINE__ );
+			break;
+		}
+		uint32_t he = 0;
+		if( ( r = uniqueMergeDevice( ctx, s, k_d, v_d, n, ko_d, (hako_voxel_attrib*)vo_d, U, &he ) ) ) break;
+		if( hasEmission ) *hasEmission = he;
+		e = cudaMemcpyAsync( keys, ko_d, *U * 8, cudaMemcpyDeviceToHost, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( attrs, vo_d, *U * 8, cudaMemcpyDeviceToHost, s );
+		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
+		if( e != cudaSuccess ) r = cudaFail( e, "D2H", __FILE__, __LINE__ );
+	} while( 0 );
+	dfree( k_d, s ), dfree( v_d, s ), dfree( ko_d, s ), dfree( vo_d, s );
+	return r;
+}
+}

@@ -64,10 +64,12 @@ int launchIntersectBatch( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, co
 						  float* t, int32_t* nMajor, uint32_t* vIndex )
 {
 	if( n == 0 ) return 0;
+	auto kShadow = intersectBatchKernel<true>;
+	auto kClosest = intersectBatchKernel<false>;
 	if( shadow )
-		HAKO_LAUNCH( ctx, intersectBatchKernel<true>, divUp( n, 256 ), 256, 0, s, v, ro, rd, n, t, nMajor, vIndex );
+		HAKO_LAUNCH( ctx, kShadow, divUp( n, 256 ), 256, 0, s, v, ro, rd, n, t, nMajor, vIndex );
 	else
-		HAKO_LAUNCH( ctx, intersectBatchKernel<false>, divUp( n, 256 ), 256, 0, s, v, ro, rd, n, t, nMajor, vIndex );
+		HAKO_LAUNCH( ctx, kClosest, divUp( n, 256 ), 256, 0, s, v, ro, rd, n, t, nMajor, vIndex );
 	return 0;
 }
 

@@ -1,0 +1,301 @@
+// sort.cu -- stable LSD radix sort of (u64 key, u64 value) pairs on a bit window, "onesweep" style.
+//
+// Stands in for thrs::RadixSort::sortPairs / sortKeys (tinyhipradixsort.hpp:849-944), which runs three kernels per
+// 8-bit digit (blockCount :119-149, a chained prefix scan over 256 x nBlocks counters :182-250, reorderKeyPair :252-475)
+// and therefore reads the keys twice per pass.  Here:
+//   - ONE histogram kernel reads the keys once and produces the digit histograms of all passes;
+//   - each pass is ONE kernel: a tile ranks its keys (warp match + popc, stable), publishes its per-digit counts,
+//     resolves its global offsets by decoupled look-back over the preceding tiles, and scatters through shared
+//     memory so that global stores are runs of consecutive addresses.
+// Algorithmic traffic: n * (8 + P * 32) bytes for pairs, vs n * P * (8 + 32) for the reference.
+#include "internal.cuh"
+
+namespace hako
+{
+namespace
+{
+constexpr int SORT_BLOCK = 256;
+constexpr int SORT_WARPS = SORT_BLOCK / 32;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_BLOCK * SORT_ITEMS; // 4096 pairs
+constexpr int RADIX = 256;
+constexpr int MAX_PASSES = 8;
+
+#define LB_FLAG_AGG ( 1ull << 62 )
+#define LB_FLAG_INC ( 2ull << 62 )
+#define LB_VALUE_MASK ( ( 1ull << 62 ) - 1 )
+
+__device__ __forceinline__ uint32_t digitOf( uint64_t key, int shift, uint32_t mask ) { return (uint32_t)( key >> shift ) & mask; }
+
+// ---- histograms of every pass in one read of the keys ----
+__global__ void __launch_bounds__( SORT_BLOCK ) sortHistogramKernel( const uint64_t* __restrict__ keys, uint64_t n, int beginBit, int endBit, int passes,
+																	 unsigned long long* __restrict__ hist /* [passes][256] */ )
+{
+	__shared__ uint32_t s_hist[MAX_PASSES * RADIX];
+	for( int i = threadIdx.x; i < passes * RADIX; i += SORT_BLOCK ) s_hist[i] = 0;
+	__syncthreads();
+	const uint64_t stride = (uint64_t)gridDim.x * SORT_BLOCK;
+	for( uint64_t i = (uint64_t)blockIdx.x * SORT_BLOCK + threadIdx.x; i < n; i += stride )
+	{
+		const uint64_t k = keys[i];
+		for( int p = 0; p < passes; p++ )
+		{
+			const int shift = beginBit + p * 8;
+			const int bits = min( 8, endBit - shift );
+			atomicAdd( &s_hist[p * RADIX + digitOf( k, shift, ( 1u << bits ) - 1u )], 1u );
+		}
+	}
+	__syncthreads();
+	for( int i = threadIdx.x; i < passes * RADIX; i += SORT_BLOCK )
+	{
+		const uint32_t c = s_hist[i];
+		if( c ) atomicAdd( &hist[i], (unsigned long long)c );
+	}
+}
+// exclusive scan of each pass's 256 bins (one block per pass)
+__global__ void __launch_bounds__( RADIX ) sortScanHistogramKernel( unsigned long long* __restrict__ hist )
+{
+	__shared__ unsigned long long s[RADIX];
+	unsigned long long* h = hist + (size_t)blockIdx.x * RADIX;
+	const unsigned long long v = h[threadIdx.x];
+	s[threadIdx.x] = v;
+	__syncthreads();
+	for( int o = 1; o < RADIX; o <<= 1 )
+	{
+		unsigned long long t = ( threadIdx.x >= o ) ? s[threadIdx.x - o] : 0ull;
+		__syncthreads();
+		s[threadIdx.x] += t;
+		__syncthreads();
+	}
+	h[threadIdx.x] = s[threadIdx.x] - v;
+}
+
+// ---- one pass ----
+template <bool PAIRS>
+__global__ void __launch_bounds__( SORT_BLOCK ) onesweepKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
+															   uint64_t* __restrict__ keysOut, uint64_t* __restrict__ valuesOut, uint64_t n,
+															   int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [256] exclusive */,
+															   unsigned long long* __restrict__ lookback /* [tiles][256], zeroed */, uint32_t* __restrict__ ticket )
+{
+	__shared__ uint64_t s_data[SORT_TILE];				   // 32 KB: keys, then values, in sorted-by-digit order
+	__shared__ uint32_t s_warpHist[SORT_WARPS][RADIX];	   // 8 KB: per-warp digit counts -> per-warp exclusive offsets
+	__shared__ uint32_t s_tileBase[RADIX];				   // exclusive offset of each digit inside the sorted tile
+	__shared__ unsigned long long s_globalBase[RADIX];	   // global output index of the tile's first key of each digit
+	__shared__ uint32_t s_tile;
+
+	if( threadIdx.x == 0 ) s_tile = atomicAdd( ticket, 1u );
+	for( int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_BLOCK ) ( &s_warpHist[0][0] )[i] = 0;
+	__syncthreads();
+	const uint32_t tile = s_tile;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint64_t tileStart = (uint64_t)tile * SORT_TILE;
+	const uint32_t tileCount = (uint32_t)min( (uint64_t)SORT_TILE, n - tileStart );
+
+	// warp-striped arrangement: warp w owns items [w * 512, (w + 1) * 512) of the tile, item i of lane l is w * 512 + i * 32 + l.
+	// Within a warp the index order (i, l) is the input order, across warps the warp order is -- ranking in that order is stable.
+	uint64_t key[SORT_ITEMS];
+	uint16_t rank[SORT_ITEMS]; // position inside the sorted tile
+	const uint32_t warpBase = warp * ( SORT_ITEMS * 32 );
+#pragma unroll
+	for( int i = 0; i < SORT_ITEMS; i++ )
+	{
+		const uint32_t idx = warpBase + i * 32 + lane;
+		key[i] = ( idx < tileCount ) ? keysIn[tileStart + idx] : ~0ull;
+	}
+	// rank inside the warp: keys with the same digit get consecutive ranks in (i, lane) order
+#pragma unroll
+	for( int i = 0; i < SORT_ITEMS; i++ )
+	{
+		const uint32_t idx = warpBase + i * 32 + lane;
+		const bool valid = idx < tileCount;
+		// invalid (padding) items take digit 255 + are ranked last in the last warps; they are never written
+		const uint32_t d = valid ? digitOf( key[i], shift, mask ) : ( RADIX - 1 );
+		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, d | ( valid ? 0u : 0x100u ) );
+		const uint32_t before = __popc( peers & ( ( 1u << lane ) - 1u ) );
+		uint32_t base = 0;
+		if( valid ) base = s_warpHist[warp][d];
+		__syncwarp();
+		if( valid && before == 0 ) s_warpHist[warp][d] = base + __popc( peers );
+		__syncwarp();
+		rank[i] = (uint16_t)( base + before );
+	}
+	__syncthreads();
+
+	// per digit (thread d): exclusive scan over the warps, tile total, look-back
+	{
+		const uint32_t d = threadIdx.x;
+		uint32_t total = 0;
+#pragma unroll
+		for( int w = 0; w < SORT_WARPS; w++ )
+		{
+			const uint32_t c = s_warpHist[w][d];
+			s_warpHist[w][d] = total;
+			total += c;
+		}
+		// publish this tile's count for digit d, then sum the predecessors
+		unsigned long long* my = lookback + (size_t)tile * RADIX + d;
+		unsigned long long excl = 0;
+		if( tile == 0 )
+		{
+			*(volatile unsigned long long*)my = LB_FLAG_INC | (unsigned long long)total;
+		}
+		else
+		{
+			*(volatile unsigned long long*)my = LB_FLAG_AGG | (unsigned long long)total;
+			int64_t t = (int64_t)tile - 1;
+			for( ;; )
+			{
+				unsigned long long v;
+				do
+				{
+					v = *(const volatile unsigned long long*)( lookback + (size_t)t * RADIX + d );
+				} while( ( v >> 62 ) == 0 );
+				excl += v & LB_VALUE_MASK;
+				if( ( v >> 62 ) == 2 ) break;
+				t--;
+			}
+			*(volatile unsigned long long*)my = LB_FLAG_INC | ( excl + total );
+		}
+		// block-wide exclusive scan of the tile totals over the 256 digits
+		uint32_t inc = total;
+#pragma unroll
+		for( int o = 1; o < 32; o <<= 1 )
+		{
+			const uint32_t nb = __shfl_up_sync( 0xFFFFFFFFu, inc, o );
+			if( lane >= o ) inc += nb;
+		}
+		__shared__ uint32_t s_warpTotals[SORT_WARPS];
+		if( lane == 31 ) s_warpTotals[warp] = inc;
+		__syncthreads();
+		uint32_t wbase = 0;
+#pragma unroll
+		for( int w = 0; w < SORT_WARPS; w++ )
+			if( w < (int)warp ) wbase += s_warpTotals[w];
+		const uint32_t tb = wbase + inc - total;
+		s_tileBase[d] = tb;
+		s_globalBase[d] = digitBase[d] + excl - tb; // so that output index = s_globalBase[digit] + position in sorted tile
+	}
+	__syncthreads();
+
+	// scatter keys into the sorted tile
+#pragma unroll
+	for( int i = 0; i < SORT_ITEMS; i++ )
+	{
+		const uint32_t idx = warpBase + i * 32 + lane;
+		if( idx < tileCount )
+		{
+			const uint32_t d = digitOf( key[i], shift, mask );
+			const uint32_t p = s_tileBase[d] + s_warpHist[warp][d] + rank[i];
+			rank[i] = (uint16_t)p;
+			s_data[p] = key[i];
+		}
+	}
+	__syncthreads();
+	// coalesced write-out; remember each position's destination for the values
+	uint64_t dst[SORT_ITEMS];
+#pragma unroll
+	for( int i = 0; i < SORT_ITEMS; i++ )
+	{
+		const uint32_t p = i * SORT_BLOCK + threadIdx.x;
+		if( p < tileCount )
+		{
+			const uint64_t k = s_data[p];
+			dst[i] = s_globalBase[digitOf( k, shift, mask )] + p;
+			keysOut[dst[i]] = k;
+		}
+	}
+	if( PAIRS )
+	{
+		__syncthreads();
+#pragma unroll
+		for( int i = 0; i < SORT_ITEMS; i++ )
+		{
+			const uint32_t idx = warpBase + i * 32 + lane;
+			if( idx < tileCount ) s_data[rank[i]] = valuesIn[tileStart + idx];
+		}
+		__syncthreads();
+#pragma unroll
+		for( int i = 0; i < SORT_ITEMS; i++ )
+		{
+			const uint32_t p = i * SORT_BLOCK + threadIdx.x;
+			if( p < tileCount ) valuesOut[dst[i]] = s_data[p];
+		}
+	}
+}
+} // namespace
+
+// Sorts in place from the caller's point of view unless resultInTmp is given: with an odd number of passes the result
+// lands in (keysTmp, valuesTmp); *resultInTmp tells the caller, otherwise it is copied back.
+int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* values, uint64_t* keysTmp, uint64_t* valuesTmp,
+					 uint64_t n, int beginBit, int endBit, int* resultInTmp )
+{
+	if( resultInTmp ) *resultInTmp = 0;
+	if( beginBit < 0 || endBit > 64 || endBit < beginBit )
+	{
+		setError( "sort: bad bit window [%d, %d)", beginBit, endBit );
+		return HAKO_E_INVALID;
+	}
+	const int passes = ( endBit - beginBit + 7 ) / 8;
+	ctx->stats.sortPasses = (uint32_t)passes;
+	if( n == 0 || passes == 0 ) return 0;
+	const uint64_t tiles = ( n + SORT_TILE - 1 ) / SORT_TILE;
+	if( tiles >= 0x7FFFFFFFull )
+	{
+		setError( "sort: too many tiles" );
+		return HAKO_E_LIMIT;
+	}
+	unsigned long long* hist = nullptr;
+	unsigned long long* lookback = nullptr;
+	uint32_t* tickets = nullptr;
+	int r = 0;
+	do
+	{
+		if( ( r = dalloc( ctx, &hist, (uint64_t)passes * RADIX, s ) ) ) break;
+		if( ( r = dalloc( ctx, &lookback, (uint64_t)passes * tiles * RADIX, s ) ) ) break;
+		if( ( r = dalloc( ctx, &tickets, (uint64_t)passes, s ) ) ) break;
+		cudaError_t e = cudaMemsetAsync( hist, 0, (size_t)passes * RADIX * 8, s );
+		if( e == cudaSuccess ) e = cudaMemsetAsync( lookback, 0, (size_t)passes * tiles * RADIX * 8, s );
+		if( e == cudaSuccess ) e = cudaMemsetAsync( tickets, 0, (size_t)passes * 4, s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "memset sort state", __FILE__, __LINE__ );
+			break;
+		}
+		const uint32_t histBlocks = (uint32_t)min( (uint64_t)ctx->smCount * 8, ( n + SORT_BLOCK * 8 - 1 ) / ( SORT_BLOCK * 8 ) );
+		HAKO_LAUNCH( ctx, sortHistogramKernel, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
+		HAKO_LAUNCH( ctx, sortScanHistogramKernel, passes, RADIX, 0, s, hist );
+		uint64_t *kin = keys, *vin = values, *kout = keysTmp, *vout = valuesTmp;
+		for( int p = 0; p < passes; p++ )
+		{
+			const int shift = beginBit + p * 8;
+			const int bits = ( endBit - shift < 8 ) ? ( endBit - shift ) : 8;
+			const uint32_t mask = ( 1u << bits ) - 1u;
+			auto kPairs = onesweepKernel<true>;
+			auto kKeys = onesweepKernel<false>;
+			if( values )
+				HAKO_LAUNCH( ctx, kPairs, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
+							 lookback + (size_t)p * tiles * RADIX, tickets + p );
+			else
+				HAKO_LAUNCH( ctx, kKeys, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
+							 lookback + (size_t)p * tiles * RADIX, tickets + p );
+			uint64_t* t = kin;
+			kin = kout, kout = t;
+			t = vin;
+			vin = vout, vout = t;
+		}
+		if( kin != keys )
+		{
+			if( resultInTmp )
+				*resultInTmp = 1;
+			else
+			{
+				e = cudaMemcpyAsync( keys, kin, n * 8, cudaMemcpyDeviceToDevice, s );
+				if( e == cudaSuccess && values ) e = cudaMemcpyAsync( values, vin, n * 8, cudaMemcpyDeviceToDevice, s );
+				if( e != cudaSuccess ) r = cudaFail( e, "copy back", __FILE__, __LINE__ );
+			}
+		}
+	} while( 0 );
+	dfree( hist, s ), dfree( lookback, s ), dfree( tickets, s );
+	return r;
+}
+} // namespace hako

@@ -2,13 +2,6 @@
 #include "internal.cuh"
 #define NOT_YET( name ) { hako::setError( name ": not implemented yet" ); return HAKO_E_STATE; }
 extern "C" {
-int hako_octree_build( hako_ctx*, hako_stream, const float*, const float*, const float*, uint32_t, const float*, float, int, hako_octree** ) NOT_YET( "hako_octree_build" )
-int hako_octree_build_device( hako_ctx*, hako_stream, const float*, const float*, const float*, uint32_t, const float*, float, int, hako_octree** ) NOT_YET( "hako_octree_build_device" )
-int hako_octree_build_from_morton( hako_ctx*, hako_stream, const uint64_t*, const hako_voxel_attrib*, uint64_t, const float*, float, int, int, hako_octree** ) NOT_YET( "hako_octree_build_from_morton" )
-int hako_voxelize( hako_ctx*, hako_stream, const float*, const float*, const float*, uint32_t, const float*, float, int, int, uint64_t*, hako_voxel_attrib*, uint64_t, uint64_t* ) NOT_YET( "hako_voxelize" )
-int hako_sort_pairs_device( hako_ctx*, hako_stream, uint64_t*, uint64_t*, uint64_t, int, int ) NOT_YET( "hako_sort_pairs_device" )
-int hako_sort_pairs( hako_ctx*, hako_stream, uint64_t*, uint64_t*, uint64_t, int, int ) NOT_YET( "hako_sort_pairs" )
-int hako_unique_merge( hako_ctx*, hako_stream, uint64_t*, hako_voxel_attrib*, uint64_t, uint64_t*, uint32_t* ) NOT_YET( "hako_unique_merge" )
 int hako_pt_create( hako_ctx*, hako_stream, hako_pt** ) NOT_YET( "hako_pt_create" )
 void hako_pt_destroy( hako_pt* ) {}
 int hako_pt_resize( hako_pt*, hako_stream, int, int ) NOT_YET( "hako_pt" )

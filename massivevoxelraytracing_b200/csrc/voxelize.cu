@@ -1,0 +1,470 @@
+// voxelize.cu -- triangle -> voxel 6-separating / conservative overlap + Morton keys + barycentric colour.
+//
+// Arithmetic follows VTContext (voxelization.hpp:124-337), the voxel loop of voxRT.cpp:198-240 (== voxCount / voxelize,
+// voxKernel.cu:58-166) and closestBarycentricCoordinateOnTriangle (vectorMath.hpp:249-284) operation for operation,
+// including the x86 float->int cast semantics the CPU path relies on (f2i_x86).
+//
+// Parallel decomposition (different from the reference, which runs one thread per triangle twice and reserves output
+// ranges with a global atomicAdd, so that its emission order is a race):
+//   1. triColumns     one thread per triangle: number of x-columns of its clamped bounding box
+//   2. scan           column offsets
+//   3. columnVoxels<false>  one thread per (triangle, x) column: count the voxels of the column
+//   4. scan           voxel offsets (+ total D, the single host read of this stage)
+//   5. columnVoxels<true>   same enumeration, emit key + packed attribute at offset
+// A column is a pure function of (triangle, x) (voxelization.hpp:230-336), so slicing by x is parity-safe, it bounds
+// the work per thread (a 4096^3 bunny triangle covers ~7k voxels) and the emission order is deterministic: triangle-major,
+// then x, y, z -- exactly the order of the CPU loop.
+#include "internal.cuh"
+#include "scan.cuh"
+
+namespace hako
+{
+namespace
+{
+// voxelization.hpp:15-48
+__device__ __forceinline__ V2 proj2( V3 p, int axis )
+{
+	if( axis == 0 ) return { p.x, p.y };
+	if( axis == 1 ) return { p.y, p.z };
+	return { p.z, p.x };
+}
+__device__ __forceinline__ float projR( V3 p, int axis ) { return axis == 0 ? p.z : ( axis == 1 ? p.x : p.y ); }
+__device__ __forceinline__ I2 proj2i( I3 p, int axis )
+{
+	if( axis == 0 ) return { p.x, p.y };
+	if( axis == 1 ) return { p.y, p.z };
+	return { p.z, p.x };
+}
+__device__ __forceinline__ int projRi( I3 p, int axis ) { return axis == 0 ? p.z : ( axis == 1 ? p.x : p.y ); }
+// voxelization.hpp:96-122
+__device__ __forceinline__ V3 unproj( V2 p, float r, int axis )
+{
+	if( axis == 0 ) return { p.x, p.y, r };
+	if( axis == 1 ) return { r, p.x, p.y };
+	return { p.y, r, p.x };
+}
+__device__ __forceinline__ I3 unproji( int px, int py, int r, int axis )
+{
+	if( axis == 0 ) return { px, py, r };
+	if( axis == 1 ) return { r, px, py };
+	return { py, r, px };
+}
+// voxelization.hpp:84-94
+__device__ __forceinline__ int majorAxis( V3 d )
+{
+	float x = sabs( d.x ), y = sabs( d.y ), z = sabs( d.z );
+	if( x < y ) return y < z ? 0 : 2;
+	return x < z ? 0 : 1;
+}
+
+struct Edges
+{
+	float nx[3], ny[3], dc[3];
+};
+// voxelization.hpp:162-199: edge normals and d constants of one 2-D projection
+__device__ __forceinline__ Edges edgeSetup( V3 v0, V3 v1, V3 v2, V3 n, int axis, bool sixSep, float dps )
+{
+	Edges E;
+	const V2 vs[3] = { proj2( v0, axis ), proj2( v1, axis ), proj2( v2, axis ) };
+	const float sgn = 0.0f < projR( n, axis ) ? 1.0f : -1.0f;
+#pragma unroll
+	for( int e = 0; e < 3; e++ )
+	{
+		const V2 a = vs[e];
+		const V2 b = vs[( e + 1 ) % 3];
+		const V2 d = { b.x - a.x, b.y - a.y };
+		const V2 ne = { -d.y * sgn, d.x * sgn };
+		E.nx[e] = ne.x;
+		E.ny[e] = ne.y;
+		float c;
+		if( !sixSep )
+		{
+			c = smax( ne.x * dps, 0.0f ) + smax( ne.y * dps, 0.0f ) - dot( ne, a );
+		}
+		else
+		{
+			const V2 h = { dps * 0.5f - a.x, dps * 0.5f - a.y };
+			c = dot( ne, h ) + 0.5f * dps * smax( sabs( ne.x ), sabs( ne.y ) );
+		}
+		E.dc[e] = c;
+	}
+	return E;
+}
+
+struct TriBox
+{
+	int major;
+	I2 lo_xy, hi_xy;
+	int lo_z, hi_z;
+	V3 n;
+};
+// voxelization.hpp:146-160: normal, major axis, clamped integer bounding box in projected coordinates
+__device__ __forceinline__ TriBox triBox( V3 v0, V3 v1, V3 v2, V3 origin, float dps, int gridRes )
+{
+	TriBox b;
+	const V3 e01 = v1 - v0;
+	const V3 e12 = v2 - v1;
+	b.n = cross( e01, e12 );
+	b.major = majorAxis( b.n );
+	const V3 bl = { smin( smin( v0.x, v1.x ), v2.x ), smin( smin( v0.y, v1.y ), v2.y ), smin( smin( v0.z, v1.z ), v2.z ) };
+	const V3 bu = { smax( smax( v0.x, v1.x ), v2.x ), smax( smax( v0.y, v1.y ), v2.y ), smax( smax( v0.z, v1.z ), v2.z ) };
+	I3 lo = { f2i_x86( floorf( ( bl.x - origin.x ) / dps ) ), f2i_x86( floorf( ( bl.y - origin.y ) / dps ) ), f2i_x86( floorf( ( bl.z - origin.z ) / dps ) ) };
+	I3 hi = { f2i_x86( floorf( ( bu.x - origin.x ) / dps ) ), f2i_x86( floorf( ( bu.y - origin.y ) / dps ) ), f2i_x86( floorf( ( bu.z - origin.z ) / dps ) ) };
+	lo = { smax( lo.x, 0 ), smax( lo.y, 0 ), smax( lo.z, 0 ) };
+	hi = { smin( hi.x, gridRes - 1 ), smin( hi.y, gridRes - 1 ), smin( hi.z, gridRes - 1 ) };
+	b.lo_xy = proj2i( lo, b.major );
+	b.hi_xy = proj2i( hi, b.major );
+	b.lo_z = projRi( lo, b.major );
+	b.hi_z = projRi( hi, b.major );
+	return b;
+}
+
+__device__ __forceinline__ V3 loadV3( const float* p, uint64_t i ) { return { p[i * 3], p[i * 3 + 1], p[i * 3 + 2] }; }
+
+// vectorMath.hpp:249-284
+__device__ __forceinline__ V3 closestBary( V3 v0, V3 v1, V3 v2, V3 P )
+{
+	const V3 d0 = v0 - P, d1 = v1 - P, d2 = v2 - P;
+	const V3 e0 = v2 - v0, e1 = v0 - v1, e2 = v1 - v2;
+	const V3 Ng = cross( e2, e0 );
+	float U = dot( cross( d2, d0 ), Ng );
+	float V = dot( cross( d0, d1 ), Ng );
+	float W = dot( cross( d1, d2 ), Ng );
+	if( U < 0.0f )
+	{
+		V = dot( -d0, e0 );
+		W = dot( d2, e0 );
+	}
+	else if( V < 0.0f )
+	{
+		W = dot( -d1, e1 );
+		U = dot( d0, e1 );
+	}
+	else if( W < 0.0f )
+	{
+		U = dot( -d2, e2 );
+		V = dot( d1, e2 );
+	}
+	const V3 bc = { smax( 0.0f, U ), smax( 0.0f, V ), smax( 0.0f, W ) };
+	const float s = bc.x + bc.y + bc.z;
+	return { bc.x / s, bc.y / s, bc.z / s };
+}
+
+__device__ __forceinline__ uint32_t packRGB255( V3 c )
+{
+	// (uint8_t)( v * 255.0f + 0.5f ) with x86 cast semantics; alpha = 255 (voxRT.cpp:230-234, voxKernel.cu:151-158)
+	return (uint32_t)f2u8_x86( c.x * 255.0f + 0.5f ) | ( (uint32_t)f2u8_x86( c.y * 255.0f + 0.5f ) << 8 ) | ( (uint32_t)f2u8_x86( c.z * 255.0f + 0.5f ) << 16 ) | 0xFF000000u;
+}
+} // namespace
+
+// ---- 1. columns per triangle ----
+__global__ void __launch_bounds__( 256 ) triColumnsKernel( const float* __restrict__ pos, uint32_t nTriangles, V3 origin, float dps, int gridRes, uint32_t* __restrict__ nCols )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if( i >= nTriangles ) return;
+	const TriBox b = triBox( loadV3( pos, (uint64_t)i * 3 ), loadV3( pos, (uint64_t)i * 3 + 1 ), loadV3( pos, (uint64_t)i * 3 + 2 ), origin, dps, gridRes );
+	nCols[i] = ( b.hi_xy.x >= b.lo_xy.x ) ? (uint32_t)( b.hi_xy.x - b.lo_xy.x + 1 ) : 0u;
+}
+
+// ---- generic u32 exclusive scan kernel (in place allowed), 256 threads x 8 items ----
+#define SCAN_ITEMS 8
+__global__ void __launch_bounds__( 256 ) scanU32Kernel( const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t n, ScanState st, uint64_t* __restrict__ totalOut )
+{
+	const uint32_t tile = scanTakeTicket( st );
+	const uint64_t base = (uint64_t)tile * ( 256 * SCAN_ITEMS ) + (uint64_t)threadIdx.x * SCAN_ITEMS;
+	uint32_t v[SCAN_ITEMS];
+	uint32_t sum = 0;
+#pragma unroll
+	for( int k = 0; k < SCAN_ITEMS; k++ )
+	{
+		v[k] = ( base + k < n ) ? in[base + k] : 0u;
+		sum += v[k];
+	}
+	uint32_t total;
+	const uint32_t excl = blockExclusiveScan<256>( sum, &total );
+	const uint64_t prefix = scanTilePrefix( st, tile, total );
+	uint32_t run = (uint32_t)prefix + excl;
+#pragma unroll
+	for( int k = 0; k < SCAN_ITEMS; k++ )
+	{
+		if( base + k < n ) out[base + k] = run;
+		run += v[k];
+	}
+	if( totalOut && tile == gridDim.x - 1 && threadIdx.x == 0 ) *totalOut = prefix + total;
+}
+int scanU32( hako_ctx* ctx, cudaStream_t s, const uint32_t* in, uint32_t* out, uint64_t n, uint64_t* totalOut_d )
+{
+	if( n == 0 )
+	{
+		if( totalOut_d ) HAKO_CUDA( cudaMemsetAsync( totalOut_d, 0, 8, s ) );
+		return 0;
+	}
+	const uint64_t tiles = ( n + 256 * SCAN_ITEMS - 1 ) / ( 256 * SCAN_ITEMS );
+	void* mem = nullptr;
+	HAKO_CUDA( cudaMallocFromPoolAsync( &mem, scanStateBytes( tiles ), ctx->pool, s ) );
+	HAKO_CUDA( cudaMemsetAsync( mem, 0, scanStateBytes( tiles ), s ) );
+	HAKO_LAUNCH( ctx, scanU32Kernel, (uint32_t)tiles, 256, 0, s, in, out, n, makeScanState( mem, tiles ), totalOut_d );
+	cudaFreeAsync( mem, s );
+	return 0;
+}
+
+// ---- 3./5. per-column enumeration ----
+template <bool EMIT>
+__global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
+															uint32_t nTriangles, const uint32_t* __restrict__ colOffset, uint32_t nColumns,
+															V3 origin, float dps, int gridRes, int sixSeparating,
+															uint32_t* __restrict__ colCount, const uint32_t* __restrict__ voxOffset,
+															uint64_t* __restrict__ keys, uint64_t* __restrict__ values )
+{
+	// column -> triangle: colOffset is the exclusive scan of columns per triangle; the owner of column c is the last
+	// triangle whose offset is <= c.  A 128-column block spans at most 128 owners, so their offsets are staged once
+	// in shared memory (zero-column triangles in between are handled by the global fallback search).
+	__shared__ uint32_t s_off[129];
+	__shared__ uint32_t s_triFirst;
+	const uint32_t c0 = blockIdx.x * 128u;
+	if( threadIdx.x == 0 )
+	{
+		uint32_t lo = 0, hi = nTriangles; // last tri with colOffset[tri] <= c0
+		while( hi - lo > 1 )
+		{
+			const uint32_t mid = ( lo + hi ) >> 1;
+			if( colOffset[mid] <= c0 )
+				lo = mid;
+			else
+				hi = mid;
+		}
+		s_triFirst = lo;
+	}
+	__syncthreads();
+	const uint32_t triFirst = s_triFirst;
+	for( uint32_t j = threadIdx.x; j < 129; j += 128 )
+	{
+		const uint32_t tIdx = triFirst + 1 + j;
+		s_off[j] = ( tIdx < nTriangles ) ? colOffset[tIdx] : 0xFFFFFFFFu;
+	}
+	__syncthreads();
+	const uint32_t c = c0 + threadIdx.x;
+	if( c >= nColumns ) return;
+
+	uint32_t tri;
+	if( c < s_off[128] )
+	{
+		// first j with s_off[j] > c  => owner = triFirst + j
+		uint32_t lo = 0, hi = 128;
+		while( lo < hi )
+		{
+			const uint32_t mid = ( lo + hi ) >> 1;
+			if( s_off[mid] > c )
+				hi = mid;
+			else
+				lo = mid + 1;
+		}
+		tri = triFirst + lo;
+	}
+	else
+	{
+		uint32_t lo = triFirst, hi = nTriangles;
+		while( hi - lo > 1 )
+		{
+			const uint32_t mid = ( lo + hi ) >> 1;
+			if( colOffset[mid] <= c )
+				lo = mid;
+			else
+				hi = mid;
+		}
+		tri = lo;
+	}
+
+	const V3 v0 = loadV3( pos, (uint64_t)tri * 3 ), v1 = loadV3( pos, (uint64_t)tri * 3 + 1 ), v2 = loadV3( pos, (uint64_t)tri * 3 + 2 );
+	const bool six = sixSeparating != 0;
+	const TriBox b = triBox( v0, v1, v2, origin, dps, gridRes );
+	const int major = b.major;
+	const int x = b.lo_xy.x + (int)( c - colOffset[tri] );
+
+	// edge functions: the major projection bounds y; the two others are the 2-D overlap tests (voxelization.hpp:311-336)
+	const int ax1 = ( major == 0 ) ? 1 : 0;
+	const int ax2 = ( major == 2 ) ? 1 : 2;
+	const Edges EM = edgeSetup( v0, v1, v2, b.n, major, six, dps );
+	const Edges EA = edgeSetup( v0, v1, v2, b.n, ax1, six, dps );
+	const Edges EB = edgeSetup( v0, v1, v2, b.n, ax2, six, dps );
+
+	// voxelization.hpp:200-223 plane coefficients
+	const V2 org_xy = proj2( origin, major );
+	const float org_z = projR( origin, major );
+	const V2 v0xy = proj2( v0, major );
+	const float v0z = projR( v0, major );
+	const V2 nxy = proj2( b.n, major );
+	const float nz = projR( b.n, major );
+	const float kx = -nxy.x / nz;
+	const float ky = -nxy.y / nz;
+	const float K = -kx * v0xy.x - ky * v0xy.y + v0z;
+	const float cmax = K + dps * ( smax( kx, 0.0f ) + smax( ky, 0.0f ) );
+	const float cmin = K + dps * ( smin( kx, 0.0f ) + smin( ky, 0.0f ) );
+	const float csix = K + 0.5f * dps * ( kx + ky );
+
+	// yRangeInclusive( x ), voxelization.hpp:230-269
+	int ly = 1, uy = -1;
+	{
+		const float xc = org_xy.x + x * dps;
+		float miny = -HAKO_MAX_FLOAT, maxy = HAKO_MAX_FLOAT;
+		bool empty = false;
+#pragma unroll
+		for( int e = 0; e < 3; e++ )
+		{
+			const float ex = EM.nx[e], ey = EM.ny[e], cc = EM.dc[e];
+			if( ey == 0.0f )
+			{
+				if( -ex * xc <= cc ) continue;
+				empty = true;
+				break;
+			}
+			const float k = -( xc * ex + cc ) / ey;
+			if( 0.0f < ey )
+				miny = smax( miny, k );
+			else
+				maxy = smin( maxy, k );
+		}
+		if( !empty )
+		{
+			const float minIf = smax( ( miny - org_xy.y ) / dps, -2147483648.0f );
+			const float maxIf = smin( ( maxy - org_xy.y ) / dps, 2147483520.0f );
+			ly = smax( f2i_x86( ceilf( minIf ) ), b.lo_xy.y );
+			uy = smin( f2i_x86( floorf( maxIf ) ), b.hi_xy.y );
+		}
+	}
+
+	V3 c0v, c1v, c2v, e0v, e1v, e2v;
+	uint32_t out = 0;
+	if( EMIT )
+	{
+		c0v = loadV3( col, (uint64_t)tri * 3 ), c1v = loadV3( col, (uint64_t)tri * 3 + 1 ), c2v = loadV3( col, (uint64_t)tri * 3 + 2 );
+		e0v = loadV3( emi, (uint64_t)tri * 3 ), e1v = loadV3( emi, (uint64_t)tri * 3 + 1 ), e2v = loadV3( emi, (uint64_t)tri * 3 + 2 );
+		out = voxOffset[c];
+	}
+	uint32_t count = 0;
+	const bool flat = b.lo_z == b.hi_z; // voxelization.hpp:313-316: a one-slab box overlaps by construction
+	for( int y = ly; y <= uy; y++ )
+	{
+		// zRangeInclusive( x, y ), voxelization.hpp:270-299 (no pre-clamp before the casts: x86 semantics)
+		const V2 o = { org_xy.x + dps * x, org_xy.y + dps * y };
+		const float var = kx * o.x + ky * o.y;
+		int zmin, zmax;
+		if( six )
+		{
+			const float idx = ( ( var + csix ) - org_z ) / dps;
+			const float zf = floorf( idx );
+			const int z = f2i_x86( zf );
+			zmin = ( idx == zf ) ? z - 1 : z;
+			zmax = z;
+		}
+		else
+		{
+			zmin = f2i_x86( floorf( ( ( var + cmin ) - org_z ) / dps ) );
+			zmax = f2i_x86( floorf( ( ( var + cmax ) - org_z ) / dps ) );
+		}
+		zmin = smax( zmin, b.lo_z );
+		zmax = smin( zmax, b.hi_z );
+		for( int z = zmin; z <= zmax; z++ )
+		{
+			const float r = org_z + (float)z * dps;
+			const V3 p = unproj( o, r, major ); // the voxel's lower corner (voxelization.hpp:300-305)
+			if( !flat )
+			{
+				const V2 pa = proj2( p, ax1 ), pb = proj2( p, ax2 );
+				bool ok = true;
+#pragma unroll
+				for( int e = 0; e < 3; e++ )
+				{
+					if( EA.nx[e] * pa.x + EA.ny[e] * pa.y + EA.dc[e] < 0.0f ) ok = false;
+					if( EB.nx[e] * pb.x + EB.ny[e] * pb.y + EB.dc[e] < 0.0f ) ok = false;
+				}
+				if( !ok ) continue;
+			}
+			if( EMIT )
+			{
+				const I3 ci = unproji( x, y, z, major );
+				const V3 bc = closestBary( v0, v1, v2, p );
+				// note the rotation: bc.x * c1 + bc.y * c2 + bc.z * c0 (voxKernel.cu:148, voxRT.cpp:229)
+				const V3 bcol = bc.x * c1v + bc.y * c2v + bc.z * c0v;
+				const V3 bemi = bc.x * e1v + bc.y * e2v + bc.z * e0v;
+				keys[out] = mortonEncode( (uint32_t)ci.x, (uint32_t)ci.y, (uint32_t)ci.z );
+				values[out] = (uint64_t)packRGB255( bcol ) | ( (uint64_t)packRGB255( bemi ) << 32 );
+				out++;
+			}
+			count++;
+		}
+	}
+	if( !EMIT ) colCount[c] = count;
+}
+
+int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D )
+{
+	*D = 0;
+	if( keysOut ) *keysOut = nullptr;
+	if( valuesOut ) *valuesOut = nullptr;
+	if( nTriangles == 0 ) return 0;
+	uint32_t* colOffset = nullptr;
+	uint32_t* colCount = nullptr;
+	uint64_t* totals = nullptr; // [0] columns, [1] voxels
+	int r = 0;
+	do
+	{
+		if( ( r = dalloc( ctx, &colOffset, (uint64_t)nTriangles + 1, s ) ) ) break;
+		if( ( r = dalloc( ctx, &totals, 2, s ) ) ) break;
+		HAKO_LAUNCH( ctx, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset );
+		if( ( r = scanU32( ctx, s, colOffset, colOffset, nTriangles, totals ) ) ) break;
+		cudaError_t e = cudaMemcpyAsync( ctx->pinned, totals, 8, cudaMemcpyDeviceToHost, s );
+		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
+		ctx->stats.hostSyncs++;
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "read column total", __FILE__, __LINE__ );
+			break;
+		}
+		const uint64_t nColumns = ctx->pinned[0];
+		if( nColumns >= 0xFFFFFFFFull )
+		{
+			setError( "voxelize: %llu (triangle, x) columns exceed the 32-bit work index", (unsigned long long)nColumns );
+			r = HAKO_E_LIMIT;
+			break;
+		}
+		if( nColumns == 0 ) break;
+		if( ( r = dalloc( ctx, &colCount, nColumns, s ) ) ) break;
+		auto kCount = columnVoxelsKernel<false>;
+		auto kEmit = columnVoxelsKernel<true>;
+		HAKO_LAUNCH( ctx, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
+					 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr );
+		if( ( r = scanU32( ctx, s, colCount, colCount, nColumns, totals + 1 ) ) ) break;
+		e = cudaMemcpyAsync( ctx->pinned, totals + 1, 8, cudaMemcpyDeviceToHost, s );
+		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
+		ctx->stats.hostSyncs++;
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "read voxel total", __FILE__, __LINE__ );
+			break;
+		}
+		const uint64_t total = ctx->pinned[0];
+		*D = total;
+		if( total >= 0xFFFFFFFFull )
+		{
+			// the reference counts dumped voxels in a uint32 (voxKernel.cu:86, IntersectorOctreeGPU.hpp:92)
+			setError( "voxelize: %llu dumped voxels exceed the reference's 32-bit voxel counters", (unsigned long long)total );
+			r = HAKO_E_LIMIT;
+			break;
+		}
+		if( total == 0 || !keysOut ) break;
+		if( ( r = dalloc( ctx, keysOut, total, s ) ) ) break;
+		if( ( r = dalloc( ctx, valuesOut, total, s ) ) ) break;
+		HAKO_LAUNCH( ctx, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
+					 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, *keysOut, *valuesOut );
+	} while( 0 );
+	dfree( colOffset, s ), dfree( colCount, s ), dfree( totals, s );
+	if( r && keysOut )
+	{
+		dfree( *keysOut, s ), dfree( *valuesOut, s );
+		*keysOut = *valuesOut = nullptr;
+	}
+	return r;
+}
+} // namespace hako

@@ -1,0 +1,237 @@
+"""GPU parity of the build path (voxelize -> sort -> unique -> octree) against the CPU oracle, stage by stage and end to end.
+Everything here is integer / byte work: the bar is bit-exact."""
+import numpy as np
+import pytest
+
+from scenes import scene_params, subdivide, vertex_colors
+
+pytestmark = pytest.mark.gpu
+FLT_MAX = np.float32(3.402823466e38)
+
+
+@pytest.fixture(scope="module")
+def hk():
+    import massivevoxelraytracing_b200 as h
+    return h
+
+
+@pytest.fixture(scope="module")
+def ctx(hk):
+    c = hk.Context(0)
+    yield c
+    c.close()
+
+
+def _attrs_to_arrays(a):
+    return a["color"], a["emission"]
+
+
+def _oracle_stages(oracle, tris, col, emi, grid):
+    origin, dps = scene_params(tris, grid)
+    keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), grid)
+    mk, mc, me = oracle.merge_voxels(keys, c, e)
+    tree = oracle.build_octree(mk, origin, float(dps), grid)
+    return origin, dps, keys, c, e, mk, mc, me, tree
+
+
+# ---------------------------------------------------------------- voxelize
+@pytest.mark.parametrize("grid", [16, 64, 256])
+def test_voxelize_matches_oracle(hk, ctx, oracle, bunny, grid):
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), grid)
+    gk, ga = ctx.voxelize(tris, col, emi, origin, float(dps), grid)
+    # emission order is deterministic here (triangle, x, y, z) == the CPU loop order (voxRT.cpp:198-240)
+    np.testing.assert_array_equal(gk, keys)
+    np.testing.assert_array_equal(ga["color"], c)
+    np.testing.assert_array_equal(ga["emission"], e)
+
+
+def test_voxelize_conservative_and_degenerate(hk, ctx, oracle, bunny, small_cases):
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, 64)
+    keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), 64, six=False)
+    gk, ga = ctx.voxelize(tris, col, emi, origin, float(dps), 64, sixSeparating=False)
+    np.testing.assert_array_equal(gk, keys)
+    np.testing.assert_array_equal(ga["color"], c)
+    deg = small_cases["deg_tris"]
+    for grid in (8, 32):
+        for six in (1, 0):
+            gk, _ = ctx.voxelize(deg, np.ones_like(deg), np.zeros_like(deg), np.zeros(3, np.float32), 1.0 / grid, grid, sixSeparating=bool(six))
+            np.testing.assert_array_equal(np.sort(gk), small_cases["deg_keys_%d_%d" % (grid, six)])
+    # empty input
+    gk, ga = ctx.voxelize(np.zeros((0, 3, 3), np.float32), np.zeros((0, 3, 3), np.float32), np.zeros((0, 3, 3), np.float32), np.zeros(3, np.float32), 1.0, 8)
+    assert gk.size == 0 and ga.size == 0
+
+
+def test_voxelize_out_of_range_colours(hk, ctx, oracle):
+    """(uint8_t)(c * 255 + 0.5) with colours outside [0,1] and huge values: x86 cast semantics"""
+    rng = np.random.default_rng(5)
+    tris = rng.random((64, 3, 3)).astype(np.float32)
+    col = (rng.standard_normal((64, 3, 3)) * 3).astype(np.float32)
+    emi = (rng.standard_normal((64, 3, 3)) * 1e12).astype(np.float32)
+    keys, c, e = oracle.voxelize(tris, col, emi, np.zeros(3, np.float32), 1.0 / 32, 32)
+    gk, ga = ctx.voxelize(tris, col, emi, np.zeros(3, np.float32), 1.0 / 32, 32)
+    np.testing.assert_array_equal(gk, keys)
+    np.testing.assert_array_equal(ga["color"], c)
+    np.testing.assert_array_equal(ga["emission"], e)
+
+
+# ---------------------------------------------------------------- sort
+@pytest.mark.parametrize("n", [0, 1, 31, 4096, 4097, 100000, 1 << 20])
+def test_sort_pairs_stable(hk, ctx, n):
+    """tinyhipradixsort unittest.cpp:356-424,426-488 (SortPairs K64V64): result == std::stable_sort, stability asserted"""
+    rng = np.random.default_rng(n)
+    keys = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+    if n > 100:
+        keys[: n // 2] = keys[n // 2: n // 2 + n // 2] & np.uint64(0xFFFF)     # many duplicates
+    vals = np.arange(n, dtype=np.uint64)
+    k, v = ctx.sort_pairs(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    np.testing.assert_array_equal(k, keys[order])
+    np.testing.assert_array_equal(v, vals[order])
+    k2 = ctx.sort_pairs(keys)
+    np.testing.assert_array_equal(k2, keys[order])
+
+
+@pytest.mark.parametrize("begin,end", [(0, 8), (0, 24), (8, 16), (3, 30), (0, 40), (16, 64), (0, 63)])
+def test_sort_bit_window(hk, ctx, begin, end):
+    """unittest.cpp:248-355 StartBits: only bits [begin, end) take part; the rest of the key rides along, stably"""
+    rng = np.random.default_rng(begin * 64 + end)
+    n = 50000
+    keys = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+    vals = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+    k, v = ctx.sort_pairs(keys, vals, begin, end)
+    sub = (keys >> np.uint64(begin)) & np.uint64((1 << (end - begin)) - 1)
+    order = np.argsort(sub, kind="stable")
+    np.testing.assert_array_equal(k, keys[order])
+    np.testing.assert_array_equal(v, vals[order])
+
+
+def test_sort_extreme(hk, ctx):
+    """unittest.cpp extremeCase: all-equal keys, already sorted, reversed"""
+    n = 70000
+    for keys in (np.full(n, 0xFFFFFFFFFFFFFFFF, np.uint64), np.zeros(n, np.uint64), np.arange(n, dtype=np.uint64), np.arange(n, dtype=np.uint64)[::-1].copy()):
+        vals = np.arange(n, dtype=np.uint64)
+        k, v = ctx.sort_pairs(keys, vals)
+        order = np.argsort(keys, kind="stable")
+        np.testing.assert_array_equal(k, keys[order])
+        np.testing.assert_array_equal(v, vals[order])
+
+
+# ---------------------------------------------------------------- unique
+@pytest.mark.parametrize("grid", [16, 64, 256])
+def test_unique_merge_matches_oracle(hk, ctx, oracle, bunny, grid):
+    tris, col, emi = bunny
+    origin, dps, keys, c, e, mk, mc, me, tree = _oracle_stages(oracle, tris, col, emi, grid)
+    attrs = np.zeros(keys.size, hk.VOXEL_ATTRIB)
+    attrs["color"], attrs["emission"] = c, e
+    sk, sv = ctx.sort_pairs(keys, attrs.view(np.uint64), 0, 24 if grid <= 256 else 32)
+    uk, ua, he = ctx.unique_merge(sk, sv.view(hk.VOXEL_ATTRIB))
+    np.testing.assert_array_equal(uk, mk)
+    np.testing.assert_array_equal(ua["color"], mc)          # includes alpha = n / n = 1 as mergeVoxels gives (voxRT.cpp:44-47)
+    np.testing.assert_array_equal(ua["emission"], me)
+    assert he == bool(me[:, :3].any())
+
+
+def test_unique_long_runs(hk, ctx, oracle):
+    rng = np.random.default_rng(9)
+    keys = np.sort(rng.integers(0, 50, 20000, dtype=np.uint64))
+    attrs = np.zeros(keys.size, hk.VOXEL_ATTRIB)
+    attrs["color"] = rng.integers(0, 256, (keys.size, 4), dtype=np.uint8)
+    attrs["emission"] = 0
+    mk, mc, me = oracle.merge_voxels(keys, attrs["color"], attrs["emission"])
+    uk, ua, he = ctx.unique_merge(keys, attrs)
+    np.testing.assert_array_equal(uk, mk)
+    np.testing.assert_array_equal(ua["color"][:, :3], mc[:, :3])
+    assert not he
+    uk, ua, he = ctx.unique_merge(np.zeros(0, np.uint64), np.zeros(0, hk.VOXEL_ATTRIB))
+    assert uk.size == 0
+
+
+# ---------------------------------------------------------------- octree
+def _cmp_nodes(a, b):
+    assert a.size == b.size
+    for f in ("mask", "children", "psum"):
+        np.testing.assert_array_equal(a[f], b[f], err_msg=f)
+
+
+@pytest.mark.parametrize("grid", [2, 4, 16, 64, 256])
+def test_octree_from_morton_matches_oracle(hk, ctx, oracle, bunny, grid):
+    tris, col, emi = bunny
+    origin, dps, keys, c, e, mk, mc, me, tree = _oracle_stages(oracle, tris, col, emi, grid)
+    g = hk.IntersectorOctree(ctx).buildDAGReference(mk, origin, float(dps), grid)
+    nodes, _, _ = g.export()
+    _cmp_nodes(nodes, tree.nodes())                       # byte-identical node array incl. the reference's numbering
+    lo, up = tree.bounds()
+    np.testing.assert_array_equal(g.m_lower, lo)
+    np.testing.assert_array_equal(g.m_upper, up)
+    naive = oracle.build_octree(mk, origin, float(dps), grid, dag=False)
+    g2 = hk.IntersectorOctree(ctx).build(mk, origin, float(dps), grid)
+    nodes2, _, _ = g2.export()
+    _cmp_nodes(nodes2, naive.nodes())
+
+
+def test_octree_random_sparse_and_single(hk, ctx, oracle):
+    rng = np.random.default_rng(11)
+    org = np.zeros(3, np.float32)
+    for grid, n in ((8, 1), (8, 512), (32, 700), (1024, 5000), (1 << 15, 20000)):
+        bits = 3 * int(np.log2(grid))
+        m = np.unique(rng.integers(0, 1 << bits, n, dtype=np.uint64)) if n < (1 << bits) else np.arange(1 << bits, dtype=np.uint64)
+        tree = oracle.build_octree(m, org, 1.0 / grid, grid)
+        g = hk.IntersectorOctree(ctx).buildDAGReference(m, org, 1.0 / grid, grid)
+        _cmp_nodes(g.export()[0], tree.nodes())
+    # empty voxel list: no nodes, every ray misses
+    g = hk.IntersectorOctree(ctx).buildDAGReference(np.zeros(0, np.uint64), org, 1.0 / 8, 8)
+    assert g.m_numberOfNodes == 0
+    t, _, _ = g.intersect(np.zeros((4, 3), np.float32) - 1, np.ones((4, 3), np.float32))
+    assert (t == FLT_MAX).all()
+
+
+# ---------------------------------------------------------------- end to end
+@pytest.mark.parametrize("grid,W,H", [(64, 256, 256), (256, 1024, 1024), (1024, 1920, 1080)])
+def test_build_end_to_end_matches_golden(hk, ctx, oracle, bunny, golden, grid, W, H):
+    """IntersectorOctreeGPU::build + render == the reference CPU path's golden values"""
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+    case = golden["cases"][str(grid)]
+    f = lambda a: "%016x" % oracle.fnv1a64(a)
+    nodes, mk, attrs = g.export(True, True, True)
+    st = ctx.build_stats()
+    assert st["dumpedVoxels"] == case["D"] and st["uniqueVoxels"] == case["U"] == mk.size
+    assert nodes.size == case["dag_nodes"]
+    assert f(mk) == case["fnv_merged_keys"]
+    assert f(np.ascontiguousarray(attrs["color"][:, :3])) == case["fnv_merged_rgb"]
+    assert f(np.ascontiguousarray(attrs["emission"][:, :3])) == case["fnv_merged_emission_rgb"]
+    assert f(np.ascontiguousarray(nodes["mask"])) == case["fnv_node_mask"]
+    assert f(np.ascontiguousarray(nodes["children"])) == case["fnv_node_children"]
+    assert f(np.ascontiguousarray(nodes["psum"])) == case["fnv_node_psum"]
+    assert case["image"] == [W, H]
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H)
+    assert bytes(cam).hex() == case["camera_bytes_hex"]
+    _, t, nm, vi = g.render(cam, W, H, rgba=False)
+    assert int((t != FLT_MAX).sum()) == case["hits"]
+    assert f(vi) == case["fnv_vindex"] and f(nm) == case["fnv_nmajor"] and f(t) == case["fnv_t"]
+    assert st["hostSyncs"] <= 6 and st["kernelLaunches"] > 0
+
+
+def test_build_subdivided_mesh_matches_oracle(hk, ctx, oracle, bunny):
+    """many small triangles (the dragon-like regime): 82k triangles at 512^3"""
+    tris = subdivide(bunny[0], 2, 0.15)
+    col, emi = vertex_colors(tris)
+    grid = 512
+    origin, dps, keys, c, e, mk, mc, me, tree = _oracle_stages(oracle, tris, col, emi, grid)
+    g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+    nodes, gk, ga = g.export(True, True, True)
+    np.testing.assert_array_equal(gk, mk)
+    np.testing.assert_array_equal(ga["color"], mc)
+    np.testing.assert_array_equal(ga["emission"], me)
+    _cmp_nodes(nodes, tree.nodes())
+    assert g.hasEmission() == bool(me[:, :3].any())
+
+
+def test_build_rejects_bad_grid(hk, ctx, bunny):
+    tris, col, emi = bunny
+    with pytest.raises(hk.HakoError):
+        hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, (0, 0, 0), 0.1, 100)      # not a power of two (reference abort()s)
