@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the massive-voxel hot path on B200.
+
+Metric (BASELINE.json): Mrays/s of primary-ray octree traversal; the voxelize + sort + unique + octree build time in ms is
+reported beside it.  Workload at N=1 = BASELINE config[1]: the (synthetic stand-in for the) xyzrgb dragon voxelized at
+4096^3, 1920x1080 pixel-centre primary rays.  A "step" casts VIEWS full frames from cameras orbiting the model (view 0 is
+voxRT's default camera, voxRT.cpp:69-72), so one step is ~33 M rays and is not launch-bound.
+
+  value      rays / s with the octree resident in HBM (device outputs), CUDA events on the launching stream
+  e2e        same rays through the host-buffer C-ABI call (hako_render_primary): per view the camera goes in by value
+             and t / nMajor / vIndex (12 B per ray) come back to pinned host memory inside the timed region
+  roofline   dominant kernel = renderPrimaryKernel; algorithmic bytes = rays * (12 + 8 * descents/ray)
+  cpu_baseline / --impl reference   the reference's own CPU traversal (oracle/_ref when present, else the oracle port)
+             on the box's host cores, on a bounded sample of the same views
+
+Multi-GPU (torchrun, one rank per GPU): the octree is built on rank 0 and broadcast over NCCL; every rank then casts its
+own VIEWS views (weak scaling: per-GPU work fixed, no data-path collective -- rays are independent).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+GRID = 4096
+W, H = 1920, 1080
+VIEWS = 16
+MESH_LEVELS = 5          # bunny x 4^5 = 5.23 M triangles (the dragon blob is missing: SURVEY.md 8d)
+
+
+def make_scene():
+    from scenes import dragon_standin, scene_params
+    t0 = time.time()
+    tris, col, emi = dragon_standin(MESH_LEVELS, 0.15)
+    origin, dps = scene_params(tris, GRID)
+    return tris, col, emi, origin, float(dps), time.time() - t0
+
+
+def view_eye(k, n_views_total):
+    """orbit of voxRT's default eye (4,4,4) about the y axis; view 0 is the reference camera"""
+    a = 2.0 * np.pi * k / n_views_total
+    c, s = np.cos(a), np.sin(a)
+    return (float(4 * c + 4 * s), 4.0, float(-4 * s + 4 * c))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.rows = []
+        self.stop_flag = False
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) >= 6 and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(self.rows)}
+
+
+def load_oracle():
+    """the CPU reference: oracle/_ref (the reference's own headers) when it travelled with the snapshot, else the port"""
+    from oracle import orc
+    port = orc.Oracle("port")
+    ref = orc.Oracle("reference") if orc.ref_available() else None
+    return port, ref
+
+
+def cpu_tree(port, ref, tris, col, emi, origin, dps):
+    """reference CPU pipeline (voxRT.cpp:198-270): voxelize -> mergeVoxels -> buildDAGReference, timed per stage"""
+    t = {}
+    t0 = time.time()
+    keys, c, e = port.voxelize(tris, col, emi, origin, dps, GRID)
+    t["voxelize_ms"] = (time.time() - t0) * 1e3
+    t0 = time.time()
+    mk, mc, me = port.merge_voxels(keys, c, e)
+    t["sort_unique_ms"] = (time.time() - t0) * 1e3
+    del keys, c, e
+    o = ref if ref is not None else port
+    t0 = time.time()
+    tree = o.build_octree(mk, origin, dps, GRID)
+    t["octree_ms"] = (time.time() - t0) * 1e3
+    t["total_ms"] = t["voxelize_ms"] + t["sort_unique_ms"] + t["octree_ms"]
+    return o, tree, mk, t
+
+
+def cpu_cast(o, tree, views_total, view_ids, threads, bands, stats=None):
+    """cast row band k of view k (bands=True: 1/VIEWS of each view) or whole views; returns rays, seconds.
+    Output buffers are allocated once, outside the timed calls."""
+    import ctypes as C
+    from oracle.orc import FLT_MAX
+    t = np.full(W * H, FLT_MAX, np.float32)
+    nm = np.full(W * H, -1, np.int32)
+    vi = np.full(W * H, 0xFFFFFFFF, np.uint32)
+    st = np.zeros(4, np.uint64)
+    rays = 0
+    secs = 0.0
+    for k in view_ids:
+        cam = o.camera_lookat(view_eye(k, views_total), (0, 0, 0), (0, 1, 0), None, W, H)
+        if bands:
+            j = k % VIEWS
+            y0, y1 = (H * j) // VIEWS, (H * (j + 1)) // VIEWS
+        else:
+            y0, y1 = 0, H
+        t0 = time.time()
+        o.lib.orc_render_primary(tree.h, C.byref(cam), W, H, y0, y1, threads, t, nm, vi, st.ctypes.data if stats is not None else None)
+        secs += time.time() - t0
+        rays += (y1 - y0) * W
+        if stats is not None:
+            stats[:3] += st[:3]
+            stats[3] = max(stats[3], st[3])
+    return rays, secs
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def base_config(n_gpus):
+    return {"workload": "config[1]: xyzrgb-dragon stand-in (bunny.obj midpoint-subdivided x%d + hash noise, %d triangles; the dragon blob is "
+                        "missing from the reference checkout) voxelized at %d^3, %dx%d pixel-centre primary rays, %d orbit views per step per GPU"
+                        % (MESH_LEVELS, 5110 * 4 ** MESH_LEVELS, GRID, W, H, VIEWS),
+            "grid": GRID, "image": [W, H], "views_per_step_per_gpu": VIEWS,
+            "parallelism": "octree built on rank 0 + NCCL broadcast; views sharded over %d GPU(s), no data-path collective" % n_gpus}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU traversal on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = host_threads()
+    tris, col, emi, origin, dps, _ = make_scene()
+    port, ref = load_oracle()
+    o, tree, mk, build = cpu_tree(port, ref, tris, col, emi, origin, dps)
+    views_total = VIEWS * args.gpus
+    # one step = a bounded sample of the workload's step: row band k of each of the VIEWS views (= one frame's worth of rays)
+    for _ in range(args.warmup):
+        cpu_cast(o, tree, views_total, range(VIEWS), threads, True)
+    rays = 0
+    secs = 0.0
+    for _ in range(args.steps):
+        r, s = cpu_cast(o, tree, views_total, range(VIEWS), threads, True)
+        rays += r
+        secs += s
+    value = rays / secs / 1e6
+    sample = "row band k of view k for the %d views of a step (%d rays per step), %d host threads over image rows" % (VIEWS, rays // max(args.steps, 1), threads)
+    line = {"impl": "reference", "metric": "Mrays/s (octree traversal, primary rays)", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(args.steps, 1) * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": base_config(args.gpus),
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "reference" if ref is not None else "port", "sample": sample,
+                             "cpu": cpu_model(), "build_ms": build},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "unique_voxels": int(mk.size), "octree_nodes": tree.num_nodes}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import massivevoxelraytracing_b200 as hk
+    from massivevoxelraytracing_b200 import dist as hdist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ctx = hk.Context(local)
+    views_total = VIEWS * world
+    nrays_view = W * H
+
+    # ---- build (rank 0), host-buffer call = the e2e build; then replicate ----
+    build = None
+    octree = None
+    scene = None
+    if rank == 0:
+        scene = make_scene()
+        tris, col, emi, origin, dps, gen_s = scene
+        wall = []
+        for i in range(3):
+            if octree is not None:
+                octree.cleanUp()
+            t0 = time.perf_counter()
+            octree = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, dps, GRID)
+            wall.append((time.perf_counter() - t0) * 1e3)
+        st = ctx.build_stats()
+        build = {"e2e_host_call_ms": min(wall), "e2e_host_call_ms_first": wall[0],
+                 "device_ms": {k: round(st[k], 3) for k in ("ms_h2d", "ms_voxelize", "ms_sort", "ms_unique", "ms_octree", "ms_total")},
+                 "triangles": int(st["nTriangles"]), "dumped_voxels": int(st["dumpedVoxels"]), "unique_voxels": int(st["uniqueVoxels"]),
+                 "octree_nodes": int(st["numberOfNodes"]), "sort_passes": int(st["sortPasses"]), "host_syncs": int(st["hostSyncs"]),
+                 "kernel_launches": int(st["kernelLaunches"]), "mesh_generation_s": round(gen_s, 2)}
+    if world > 1:
+        t0 = time.perf_counter()
+        octree = hdist.broadcast_octree(ctx, hk.IntersectorOctreeGPU, octree, 0)
+        dist.barrier()
+        if rank == 0:
+            build["nccl_broadcast_ms"] = (time.perf_counter() - t0) * 1e3
+    info = octree.info()
+
+    my_views = list(range(rank * VIEWS, (rank + 1) * VIEWS))
+    cams = [hk.camera_lookat(view_eye(k, views_total), (0, 0, 0), width=W, height=H) for k in my_views]
+    # one output set per view: 16 x 24.9 MB = 398 MB per step, larger than the 126 MB L2
+    t_d = torch.empty((VIEWS, nrays_view), dtype=torch.float32, device=dev)
+    nm_d = torch.empty((VIEWS, nrays_view), dtype=torch.int32, device=dev)
+    vi_d = torch.empty((VIEWS, nrays_view), dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream()
+
+    def step_device():
+        for i, cam in enumerate(cams):
+            octree.render_device(cam, W, H, t=t_d[i], nMajor=nm_d[i], vIndex=vi_d[i], stream=stream)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sampler = ClockSampler(local)
+    sync_all()
+    sampler.start()
+    l0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    sync_all()
+    launches = ctx.launch_count - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+
+    # ---- e2e: host-buffer C-ABI call, results into pinned host memory ----
+    t_h = torch.empty(nrays_view, dtype=torch.float32).pin_memory().numpy()
+    nm_h = torch.empty(nrays_view, dtype=torch.int32).pin_memory().numpy()
+    vi_h = torch.empty(nrays_view, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+    import ctypes as C
+
+    def step_host():
+        for cam in cams:
+            hk._abi.check(ctx.lib.hako_render_primary(octree.h, None, C.byref(cam), W, H, 0, H, 0, None, t_h.ctypes.data, nm_h.ctypes.data, vi_h.ctypes.data))
+
+    step_host()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    sync_all()
+    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_total = float(e2e_ms.item())
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    hits_view0 = int((t_d[0] != 3.402823466e38).sum().item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    rays_step_all = nrays_view * VIEWS * world
+    value = rays_step_all * args.steps / (ms_total * 1e-3) / 1e6
+    e2e_value = rays_step_all * args.steps / (e2e_total * 1e-3) / 1e6
+
+    # ---- CPU baseline + descents/ray + parity spot check (rank 0, N=1 only: bounded CPU work) ----
+    cpu = None
+    dbar = None
+    parity = None
+    if world == 1 and not args.no_cpu:
+        port, ref = load_oracle()
+        tris, col, emi, origin, dps, _ = scene
+        o, tree, mk, cpu_build = cpu_tree(port, ref, tris, col, emi, origin, dps)
+        threads = host_threads()
+        cpu_cast(o, tree, views_total, range(2), threads, True)
+        rays_c, secs_c = 0, 0.0
+        reps = 0
+        while secs_c < 3.0 and reps < 8:
+            r, s = cpu_cast(o, tree, views_total, range(VIEWS), threads, True)
+            rays_c += r
+            secs_c += s
+            reps += 1
+        r1, s1 = cpu_cast(o, tree, views_total, range(VIEWS), 1, True)
+        ptree = tree if o is port else port.build_octree(mk, origin, dps, GRID)
+        stats = np.zeros(4, np.uint64)
+        rs, _ = cpu_cast(port, ptree, views_total, range(VIEWS), threads, True, stats)
+        dbar = float(stats[1]) / rs
+        cpu = {"value": rays_c / secs_c / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference" if ref is not None else "port",
+               "sample": "row band k of view k for the %d views of a step (%d rays), repeated %d times; %d host threads over image rows" % (VIEWS, rs, reps, threads),
+               "single_thread_mrays": r1 / s1 / 1e6, "cpu": cpu_model(), "build_ms": {k: round(v, 1) for k, v in cpu_build.items()},
+               "traversal_stats_per_ray": {"loop_visits": float(stats[0]) / rs, "descents": dbar, "pushes": float(stats[2]) / rs, "max_stack": int(stats[3])}}
+        # parity spot check: view 0 complete, GPU (device buffers of the last step) vs the CPU reference
+        cam0 = o.camera_lookat(view_eye(0, views_total), (0, 0, 0), (0, 1, 0), None, W, H)
+        ct, cnm, cvi = tree.render_primary(cam0, W, H, 0, H, threads)
+        parity = bool((t_d[0].cpu().numpy().view(np.uint32) == ct.view(np.uint32)).all() and (vi_d[0].cpu().numpy().view(np.uint32) == cvi).all()
+                      and (nm_d[0].cpu().numpy() == cnm).all() and mk.size == info.numberOfVoxels and tree.num_nodes == info.numberOfNodes)
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    if dbar is None:
+        dbar = load_profile_value("descents_per_ray", 7.84)
+    bytes_per_ray = 12.0 + 8.0 * dbar
+    launch_ms = ms_total / max(launches, 1)
+    achieved = nrays_view * bytes_per_ray / (launch_ms * 1e-3) / 1e9
+    roofline = {"kernel": "renderPrimaryKernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
+                "traffic": load_profile_value("render_dram_bytes_per_launch", None),
+                "algorithmic_bytes_per_ray": bytes_per_ray, "descents_per_ray": dbar, "rays_per_launch": nrays_view, "avg_launch_ms": launch_ms,
+                "note": "pointer-chasing traversal: latency/issue-bound with the %.0f MB octree L2-resident; see profiles/ for L2 throughput, issue utilisation and warp efficiency"
+                        % (info.numberOfNodes * 64 / 1e6)}
+    cfg = base_config(world)
+    cfg["l2"] = "outputs of a step (%.0f MB) exceed the 126 MB L2; the octree (%.0f MB) is L2-resident by design; no explicit flush" % (
+        VIEWS * nrays_view * 12 / 1e6, info.numberOfNodes * 65 / 1e6)
+    line = {"metric": "Mrays/s (octree traversal, primary rays)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfg, "clocks": sampler.summary(),
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 60 * VIEWS, "d2h_bytes_per_step": 12 * nrays_view * VIEWS,
+                    "ms_per_step": e2e_total / args.steps, "call": "hako_render_primary (host buffers, pinned), one call per view"},
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "build": build, "hits_view0": hits_view0,
+            "parity_vs_cpu_reference_view0": parity, "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def load_profile_value(key, default):
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "latest.json"))).get(key, default)
+    except Exception:
+        return default
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,76 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads without a GPU, exports every function include/hako.h
+declares, the ctypes table matches the header, and calls fail loudly (no CPU fallback) when no device is usable."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_functions():
+    src = open(os.path.join(ROOT, "include", "hako.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(hako_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported_and_bound():
+    from massivevoxelraytracing_b200 import _abi
+    lib = _abi.load()
+    names = _header_functions()
+    assert len(names) >= 35
+    out = subprocess.run(["nm", "-D", "--defined-only", _abi.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    exported = set(re.findall(r" T (hako_[a-z0-9_]+)", out))
+    assert set(names) <= exported, sorted(set(names) - exported)
+    assert set(names) == set(_abi.SIGNATURES), (sorted(set(names) - set(_abi.SIGNATURES)), sorted(set(_abi.SIGNATURES) - set(names)))
+    for n in names:
+        assert hasattr(lib, n)
+    assert lib.hako_version() >= 100
+
+
+def test_struct_layouts_match_reference():
+    from massivevoxelraytracing_b200 import _abi, intersector
+    assert C.sizeof(_abi.Camera) == 60                 # CameraPinhole, renderCommon.hpp:77-83
+    assert intersector.NODE68.itemsize == 68           # OctreeNode, voxCommon.hpp:133-138
+    assert intersector.VOXEL_ATTRIB.itemsize == 8      # VoxelAttirb, voxCommon.hpp:121-125
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import massivevoxelraytracing_b200 as hk
+    with pytest.raises(hk.HakoError) as e:
+        hk.Context(0)
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_product_never_imports_oracle():
+    """the oracle is test infrastructure: nothing under the package (or include/) may reference it"""
+    pkg = os.path.join(ROOT, "massivevoxelraytracing_b200")
+    for base, _, files in os.walk(pkg):
+        if "build" in base.split(os.sep):
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", "Makefile")):
+                text = open(os.path.join(base, f)).read()
+                assert "liboracle" not in text and "hako_oracle" not in text and "from oracle" not in text and "import oracle" not in text, f
+
+
+def test_camera_matches_oracle(oracle):
+    import numpy as np
+    import massivevoxelraytracing_b200 as hk
+    for eye, ctr, w, h, fovy in (((4, 4, 4), (0, 0, 0), 1920, 1080, None), ((1, 2, 3), (0.5, 0, -1), 640, 480, 0.6), ((-3, 0.5, 9), (0, 1, 0), 33, 77, 1.2)):
+        a = hk.camera_lookat(eye, ctr, (0, 1, 0), fovy, w, h, focus=2.5, lensR=0.1)
+        b = oracle.camera_lookat(eye, ctr, (0, 1, 0), fovy, w, h, focus=2.5, lens_r=0.1)
+        assert bytes(a) == bytes(b)
+    # initFromPerspective from explicit matrices (column-major identity view, simple projection)
+    view = np.eye(4, dtype=np.float32)
+    view[3, :3] = (1, 2, 3)            # column 3 = translation (column-major: row index of numpy = column)
+    proj = np.zeros((4, 4), np.float32)
+    proj[1, 1] = 2.0
+    cam = hk.camera_from_matrices(view, proj, 1.5, 0.25)
+    assert tuple(cam.o) == (-1.0, -2.0, -3.0) and tuple(cam.front) == (-0.0, -0.0, -1.0) and cam.tanHthetaY == 0.5
+    assert cam.focus == 1.5 and cam.lensR == 0.25
