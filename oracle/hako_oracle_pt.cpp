@@ -1,1 +1,318 @@
-// filled in below (PMJ / HDRI / path-tracer restatement)
+/*
+ * hako_oracle_pt.cpp -- CPU ORACLE ("port"), path-tracing half.  TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * Restates, with the host-side math the reference's headers use on the CPU (cosf / sinf / sqrtf / powf,
+ * vectorMath.hpp:93-97):
+ *   voxCommon.hpp:45-109        MurmurHash32 / hashCombine
+ *   renderCommon.hpp:86-117     PCG32, uniformf
+ *   renderCommon.hpp:119-151    GetOrthonormalBasis, sampleLambertian
+ *   renderCommon.hpp:168-202    luminance, getSpherical, upper_bound_f
+ *   renderCommon.hpp:354-470    HDRI::sampleNearest / importanceSample / SAT accessors
+ *   pmjSampler.hpp:14-58        GetPMJ02Samples;  :62-102 Owen scrambling;  :114-134 table setup;  :158-173 sample2d
+ *   voxKernel.cu:485-608        HDRIstoreImportance / buildSATh / buildSATv / buildSAT2u32 (sequential double sums)
+ *   voxKernel.cu:610-777        renderPT (sample mapping, dimension order and estimator)
+ *   voxKernel.cu:779-795        renderResolve
+ *
+ * Parity status: the pieces the reference can run on the host (PMJ table, sample2d, scrambles, Murmur, importanceSample,
+ * sampleLambertian, camera) are PINNED against oracle/_ref (tests/test_oracle_pt.py).  HDRI::sampleNearest, the SAT build
+ * and renderPT exist only as device code in the reference (renderCommon.hpp:353-366, voxKernel.cu), so their restatement
+ * here is "parity unpinned" beyond those pieces; image parity is RMSE-level as BASELINE.json:north_star states.
+ */
+#include "hako_oracle.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+extern "C" {
+void orc_intersect_batch( const OrcOctree* o, const float* ro, const float* rd, uint64_t n, int isShadowRay,
+						  float* t, int* nMajor, uint32_t* vIndex, uint64_t* stats );
+}
+
+namespace
+{
+const float PI = 3.14159265358979323846f;
+
+struct F3
+{
+	float x, y, z;
+};
+inline F3 operator+( F3 a, F3 b ) { return { a.x + b.x, a.y + b.y, a.z + b.z }; }
+inline F3 operator*( F3 a, F3 b ) { return { a.x * b.x, a.y * b.y, a.z * b.z }; }
+inline F3 operator*( F3 a, float b ) { return { a.x * b, a.y * b, a.z * b }; }
+inline F3 operator/( F3 a, float b ) { return { a.x / b, a.y / b, a.z / b }; }
+inline float dot( F3 a, F3 b ) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline float smaxf( float x, float y ) { return ( x < y ) ? y : x; }
+inline float sminf( float x, float y ) { return ( y < x ) ? y : x; }
+inline float sclamp( float x, float a, float b ) { return sminf( smaxf( x, a ), b ); } // vectorMath.hpp ss_clamp
+inline float mixf( float a, float b, float t ) { return a + ( b - a ) * t; }
+
+inline uint32_t rotl32( uint32_t x, int r ) { return ( x << r ) | ( x >> ( 32 - r ) ); }
+inline uint32_t fmix32( uint32_t h )
+{
+	h ^= h >> 16;
+	h *= 0x85ebca6bu;
+	h ^= h >> 13;
+	h *= 0xc2b2ae35u;
+	h ^= h >> 16;
+	return h;
+}
+struct Murmur
+{
+	uint32_t h1, len;
+	explicit Murmur( uint32_t seed ) : h1( seed ), len( 0 ) {}
+	void combine( uint32_t k1 )
+	{
+		k1 *= 0xcc9e2d51u;
+		k1 = rotl32( k1, 15 );
+		k1 *= 0x1b873593u;
+		h1 ^= k1;
+		h1 = rotl32( h1, 13 );
+		h1 = h1 * 5 + 0xe6546b64u;
+		len++;
+	}
+	uint32_t getHash() const { return fmix32( h1 ^ ( len * 4 ) ); }
+};
+inline uint32_t hashCombine( uint32_t a, uint32_t b )
+{
+	Murmur h( a );
+	h.combine( b );
+	return h.getHash();
+}
+inline uint32_t hashCombine( uint32_t a, uint32_t b, uint32_t c )
+{
+	Murmur h( a );
+	h.combine( b );
+	h.combine( c );
+	return h.getHash();
+}
+
+struct PCG32
+{
+	uint64_t state, inc;
+	void setup( uint64_t seed, uint64_t stream )
+	{
+		state = 0;
+		inc = stream * 2 + 1;
+		nextU32();
+		state += seed;
+		nextU32();
+	}
+	uint32_t nextU32()
+	{
+		uint64_t old = state;
+		state = old * 6364136223846793005ULL + inc;
+		uint32_t xorshifted = (uint32_t)( ( ( old >> 18u ) ^ old ) >> 27u );
+		uint32_t rot = (uint32_t)( old >> 59u );
+		return ( xorshifted >> rot ) | ( xorshifted << ( ( -rot ) & 31 ) );
+	}
+};
+inline float uniformf( uint32_t x )
+{
+	uint32_t bits = ( x >> 9 ) | 0x3f800000u;
+	float v;
+	memcpy( &v, &bits, 4 );
+	return v - 1.0f;
+}
+
+// pmjSampler.hpp:14-58
+void pmj02( int num_samples, float* samples, PCG32& rng )
+{
+	static const uint32_t xors[2][32] = {
+		{ 0x0, 0x0, 0x2, 0x6, 0x6, 0xe, 0x36, 0x4e, 0x16, 0x2e, 0x276, 0x6ce, 0x716, 0xc2e, 0x3076, 0x40ce, 0x116, 0x22e, 0x20676, 0x60ece, 0x61716, 0xe2c2e, 0x367076, 0x4ec0ce, 0x170116, 0x2c022e, 0x2700676, 0x6c00ece, 0x7001716, 0xc002c2e, 0x30007076, 0x4000c0ce },
+		{ 0x0, 0x1, 0x3, 0x3, 0x7, 0x1b, 0x27, 0xb, 0x17, 0x13b, 0x367, 0x38b, 0x617, 0x183b, 0x2067, 0x8b, 0x117, 0x1033b, 0x30767, 0x30b8b, 0x71617, 0x1b383b, 0x276067, 0xb808b, 0x160117, 0x138033b, 0x3600767, 0x3800b8b, 0x6001617, 0x1800383b, 0x20006067, 0x808b } };
+	auto u = [&]() { return uniformf( rng.nextU32() ); };
+	for( int d = 0; d < 2; d++ ) samples[d] = u();
+	for( int log_n = 0; ( 1 << log_n ) < num_samples; log_n++ )
+	{
+		int prev_len = 1 << log_n;
+		int n_strata = prev_len * 2;
+		float i_strata = 1.0f / n_strata;
+		for( int i = 0; i < prev_len && ( prev_len + i ) < num_samples; i++ )
+		{
+			const int px = i ^ (int)xors[0][log_n];
+			const int pxs = (int)( samples[px * 2] * n_strata );
+			const int xs = pxs ^ 1;
+			const int py = i ^ (int)xors[1][log_n];
+			const int pys = (int)( samples[py * 2 + 1] * n_strata );
+			const int ys = pys ^ 1;
+			float* s = &samples[( prev_len + i ) * 2];
+			// argument evaluation order of GetPMJ02Point( ..., uniformFloat(), uniformFloat(), sample ): g++ evaluates
+			// right to left, so xi1 is drawn BEFORE xi0 (pinned against oracle/_ref)
+			float xi1 = u();
+			float xi0 = u();
+			s[0] = ( xi0 + xs ) * i_strata;
+			s[1] = ( xi1 + ys ) * i_strata;
+		}
+	}
+}
+
+inline uint32_t laine_karras( uint32_t x, uint32_t seed )
+{
+	x += seed;
+	x ^= x * 0x6c50b47cu;
+	x ^= x * 0xb82f1e52u;
+	x ^= x * 0xc7afe638u;
+	x ^= x * 0x8d22f6e6u;
+	return x;
+}
+inline uint32_t reverseBits( uint32_t v )
+{
+	v = ( ( v >> 1 ) & 0x55555555u ) | ( ( v & 0x55555555u ) << 1 );
+	v = ( ( v >> 2 ) & 0x33333333u ) | ( ( v & 0x33333333u ) << 2 );
+	v = ( ( v >> 4 ) & 0x0F0F0F0Fu ) | ( ( v & 0x0F0F0F0Fu ) << 4 );
+	v = ( ( v >> 8 ) & 0x00FF00FFu ) | ( ( v & 0x00FF00FFu ) << 8 );
+	v = ( v >> 16 ) | ( v << 16 );
+	return v;
+}
+inline uint32_t nus( uint32_t x, uint32_t seed ) { return reverseBits( laine_karras( reverseBits( x ), seed ) ); }
+inline float scramble_f32( float x, uint32_t seed )
+{
+	x += 1.0f;
+	uint32_t bits;
+	memcpy( &bits, &x, 4 );
+	uint32_t s = 0x3f800000u | ( nus( bits & 0x7FFFFFu, seed ) & 0x7FFFFFu );
+	float r;
+	memcpy( &r, &s, 4 );
+	return r - 1.0f;
+}
+// pmjSampler.hpp:158-173
+inline void sample2d( const float* table, uint32_t sampleIdx, uint32_t dimension, uint32_t stream, float* x, float* y )
+{
+	sampleIdx = nus( sampleIdx, hashCombine( stream, dimension, 31082745u ) ) & 4095u;
+	dimension = nus( dimension, hashCombine( stream, 54761983u ) ) & 127u;
+	uint32_t head = dimension * 2 * 4096;
+	float a = table[head + sampleIdx * 2 + 0];
+	float b = table[head + sampleIdx * 2 + 1];
+	*x = scramble_f32( a, hashCombine( stream, dimension, 83927105u ) );
+	*y = scramble_f32( b, hashCombine( stream, dimension, 12654890u ) );
+}
+
+// renderCommon.hpp:119-151
+inline void orthoBasis( F3 z, F3* xa, F3* ya )
+{
+	const float sign = copysignf( 1.0f, z.z );
+	const float a = -1.0f / ( sign + z.z );
+	const float b = z.x * z.y * a;
+	*xa = { 1.0f + sign * z.x * z.x * a, sign * b, -sign * z.x };
+	*ya = { b, sign + z.y * z.y * a, -z.y };
+}
+inline F3 sampleLambertian( float a, float b, F3 Ng )
+{
+	float r = sqrtf( a );
+	float theta = b * PI * 2.0f;
+	float x = r * cosf( theta );
+	float y = r * sinf( theta );
+	float z = sqrtf( smaxf( 1.0f - a, 0.0f ) );
+	F3 xa, ya;
+	orthoBasis( Ng, &xa, &ya );
+	return xa * x + ya * y + Ng * z;
+}
+inline float luminance( float r, float g, float b ) { return 0.2126f * r + 0.7152f * g + 0.0722f * b; }
+
+struct Hdri
+{
+	const float* pixels; // RGBA32F
+	const float* primary;
+	const uint32_t* sats; // [7][w*h]: global, +x, -x, +y, -y, +z, -z
+	int w, h, wP, hP;
+	float scale;
+	bool enabled() const { return 0.0f < scale && pixels; }
+	uint32_t psH( const uint32_t* sat, uint32_t x ) const { return x <= 0 ? 0 : sat[(size_t)w * ( h - 1 ) + x - 1]; }
+	uint32_t psV( const uint32_t* sat, uint32_t x, uint32_t y ) const
+	{
+		if( y <= 0 ) return 0;
+		uint32_t s0 = x <= 0 ? 0 : sat[(size_t)w * ( y - 1 ) + ( x - 1 )];
+		uint32_t s1 = sat[(size_t)w * ( y - 1 ) + x];
+		return s1 - s0;
+	}
+	uint32_t count( const uint32_t* sat, uint32_t x, uint32_t y ) const
+	{
+		uint32_t a = ( x <= 0 || y <= 0 ) ? 0 : sat[(size_t)w * ( y - 1 ) + ( x - 1 )];
+		uint32_t b = ( y <= 0 ) ? 0 : sat[(size_t)w * ( y - 1 ) + x];
+		uint32_t c = ( x <= 0 ) ? 0 : sat[(size_t)w * y + ( x - 1 )];
+		uint32_t d = sat[(size_t)w * y + x];
+		return ( d - b ) + ( a - c );
+	}
+	// renderCommon.hpp:367-435
+	void importanceSample( F3* dir, F3* L, float* srPDF, F3 N, bool axisAligned, float u0, float u1, float u2, float u3, uint32_t* XY ) const
+	{
+		const uint32_t* sat = sats;
+		const size_t n = (size_t)w * h;
+		if( axisAligned )
+		{
+			const float k = 0.8f;
+			if( k < N.x )
+				sat = sats + 1 * n;
+			else if( N.x < -k )
+				sat = sats + 2 * n;
+			else if( k < N.y )
+				sat = sats + 3 * n;
+			else if( N.y < -k )
+				sat = sats + 4 * n;
+			else if( k < N.z )
+				sat = sats + 5 * n;
+			else if( N.z < -k )
+				sat = sats + 6 * n;
+		}
+		int i = 0, j = w;
+		while( i < j )
+		{
+			const int m = ( i + j ) / 2;
+			const float v = (float)psH( sat, m ) / (float)0xFFFFFFFFu;
+			if( v <= u0 )
+				i = m + 1;
+			else
+				j = m;
+		}
+		uint32_t X = (uint32_t)i - 1;
+		uint32_t vol = psH( sat, X + 1 ) - psH( sat, X );
+		i = 0, j = h;
+		while( i < j )
+		{
+			const int m = ( i + j ) / 2;
+			const float v = (float)psV( sat, X, m ) / (float)vol;
+			if( v <= u1 )
+				i = m + 1;
+			else
+				j = m;
+		}
+		uint32_t Y = (uint32_t)i - 1;
+		float pSelection = (float)count( sat, X, Y ) / (float)0xFFFFFFFF;
+		float dTheta = PI / (float)h;
+		float dPhi = 2.0f * PI / (float)w;
+		float theta = Y * dTheta;
+		float dH = 2.0f * sinf( dTheta * 0.5f ) * sinf( dTheta * 0.5f + theta );
+		float sr = dH * dPhi;
+		float sY = mixf( cosf( theta ), cosf( theta + dTheta ), u2 );
+		float phi = dPhi * ( (float)X + u3 ) + PI;
+		float sX = cosf( phi );
+		float sZ = sinf( phi );
+		float sinTheta = sqrtf( smaxf( 1.0f - sY * sY, 0.0f ) );
+		*dir = { sX * sinTheta, sY, sZ * sinTheta };
+		*srPDF = pSelection / sr;
+		const float* c = pixels + ( (size_t)Y * w + X ) * 4;
+		*L = F3{ c[0], c[1], c[2] } * scale;
+		if( XY )
+		{
+			XY[0] = X;
+			XY[1] = Y;
+		}
+	}
+	// renderCommon.hpp:354-365 (device-only in the reference)
+	F3 sampleNearest( F3 d, bool isPrimary ) const
+	{
+		int ww = isPrimary ? wP : w;
+		int hh = isPrimary ? hP : h;
+		float phi = atan2f( d.z, d.x ) + PI;
+		float theta = atan2f( sqrtf( d.x * d.x + d.z * d.z ), d.y );
+		float u = phi / ( PI * 2.0f ), v = theta / PI;
+		int x = (int)sclamp( u * ww, 0.0f, (float)( ww - 1.0f ) );
+		int y = (int)sclamp( v * hh, 0.0f, (float)( hh - 1.0f ) );
+		size_t index = (size_t)y * ww + x;
+		const float* c = ( isPrimary && primary ) ? primary + index * 4 : pixels + index * 4;
+		return F3{ c[0], c[1], c[2] } * scale;
+	}
+};
