@@ -92,6 +92,27 @@ void orc_render_primary( const OrcOctree* o, const OrcCamera* cam, int w, int h,
 /* FNV-1a-64 over a byte buffer (used for the golden checksums in SURVEY.md section 8c). */
 uint64_t orc_fnv1a64( const void* p, uint64_t bytes );
 
+/* ---- path-tracing half (hako_oracle_pt.cpp / ref_driver_pt.cpp) ----
+ * Pieces the reference can run on the host are implemented by BOTH libraries (pinning); orc_hdri_build_sats,
+ * orc_hdri_sample_nearest, orc_pt_render and orc_pt_resolve restate device-only code (voxKernel.cu:485-795,
+ * renderCommon.hpp:353-366) and exist only in the port ("parity unpinned" for those). */
+uint32_t orc_murmur_combine( uint32_t seed, const uint32_t* values, int n );			  /* voxCommon.hpp:45-109 */
+void orc_pcg32_stream( uint64_t seed, uint64_t stream, int n, uint32_t* out );			  /* renderCommon.hpp:86-111 */
+uint32_t orc_nested_uniform_scramble( uint32_t x, uint32_t seed );						  /* pmjSampler.hpp:62-90 */
+float orc_scramble_f32( float x, uint32_t seed );										  /* pmjSampler.hpp:92-102 */
+void orc_pmj_table( float* out /* [128][4096][2] */ );									  /* pmjSampler.hpp:114-134 */
+void orc_pmj_sample2d( const float* table, uint32_t sampleIdx, uint32_t dimension, uint32_t stream, float* xy ); /* :158-173 */
+void orc_hdri_importance_sample( const float* rgba, const uint32_t* sats, int w, int h, float scale, const float* N, int axisAligned,
+								 float u0, float u1, float u2, float u3, float* dir, float* L, float* srPDF, uint32_t* XY ); /* renderCommon.hpp:367-435 */
+void orc_sample_lambertian( float a, float b, const float* Ng, float* out );			  /* renderCommon.hpp:119-151 */
+/* port only */
+void orc_hdri_build_sats( const float* rgba, int w, int h, uint32_t* sats /* [7][w*h] */ ); /* renderCommon.hpp:214-314 + voxKernel.cu:485-608 */
+void orc_hdri_sample_nearest( const float* rgba, int w, int h, float scale, const float* d, float* out );
+void orc_pt_render( const OrcOctree* octree, const uint8_t* attrs, uint32_t hasEmission, const OrcCamera* cam, int w, int h, int y0, int y1,
+					int iteration, const float* hdriRgba, const uint32_t* sats, int hw, int hh, float hdriScale,
+					const float* primaryRgba, int wP, int hP, const float* pmjTable, int maxDepth, float* accum, uint64_t* stats, int nThreads );
+void orc_pt_resolve( const float* accum, uint64_t n, uint8_t* rgba );
+
 #ifdef __cplusplus
 }
 #endif

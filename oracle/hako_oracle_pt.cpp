@@ -23,6 +23,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <immintrin.h>
 #include <thread>
 #include <vector>
 
@@ -316,3 +317,300 @@ struct Hdri
 		return F3{ c[0], c[1], c[2] } * scale;
 	}
 };
+
+// ---- SAT build: voxKernel.cu:485-608 ----
+// HDRIstoreImportance (:485-524) with host math
+void storeImportance( const float* rgba, int w, int h, double* sat, int cosWeighted, F3 axis )
+{
+	for( int pixelY = 0; pixelY < h; pixelY++ )
+		for( int pixelX = 0; pixelX < w; pixelX++ )
+		{
+			size_t pixelIdx = (size_t)pixelY * w + pixelX;
+			float dTheta = PI / (float)h;
+			float dPhi = 2.0f * PI / (float)w;
+			float theta = pixelY * dTheta;
+			float dH = 2.0f * sinf( dTheta * 0.5f ) * sinf( dTheta * 0.5f + theta );
+			float dW = dPhi;
+			float sr = dH * dW;
+			const float* c = rgba + pixelIdx * 4;
+			float wgt = 1.0f;
+			if( cosWeighted )
+			{
+				float sY = mixf( cosf( theta ), cosf( theta + dTheta ), 0.5f );
+				float phi = dPhi * ( (float)pixelX + 0.5f ) + PI;
+				float sX = cosf( phi );
+				float sZ = sinf( phi );
+				float sinTheta = sqrtf( smaxf( 1.0f - sY * sY, 0.0f ) );
+				F3 dirCenter = { sX * sinTheta, sY, sZ * sinTheta };
+				wgt = smaxf( dot( axis, dirCenter ), 0.0f );
+			}
+			sat[pixelIdx] = luminance( c[0], c[1], c[2] ) * sr * wgt; // float product, widened on store
+		}
+}
+// prefixSumInclusive<double,512> (:526-555): Hillis-Steele over one 512-element tile, in the reference's summation order
+const int SAT_BLOCK = 512;
+double scanTile( double prefix, double* s )
+{
+	double tmp[SAT_BLOCK];
+	for( int offset = 1; offset < SAT_BLOCK; offset <<= 1 )
+	{
+		for( int i = 0; i < SAT_BLOCK; i++ ) tmp[i] = ( offset <= i ) ? s[i] + s[i - offset] : s[i];
+		memcpy( s, tmp, sizeof( tmp ) );
+	}
+	double sum = s[SAT_BLOCK - 1];
+	for( int i = 0; i < SAT_BLOCK; i++ ) s[i] += prefix;
+	return sum;
+}
+// buildSATh / buildSATv (:557-598): `stride` walks a row (1) or a column (w)
+void scanLine( double* line, int n, size_t stride )
+{
+	double s[SAT_BLOCK];
+	double prefix = 0.0;
+	for( int i = 0; i < n; i += SAT_BLOCK )
+	{
+		for( int k = 0; k < SAT_BLOCK; k++ ) s[k] = ( i + k < n ) ? line[(size_t)( i + k ) * stride] : 0.0;
+		prefix += scanTile( prefix, s );
+		for( int k = 0; k < SAT_BLOCK && i + k < n; k++ ) line[(size_t)( i + k ) * stride] = s[k];
+	}
+}
+void buildSat( const float* rgba, int w, int h, uint32_t* out, int cosWeighted, F3 axis, int nThreads )
+{
+	std::vector<double> sat( (size_t)w * h );
+	storeImportance( rgba, w, h, sat.data(), cosWeighted, axis );
+	auto par = [&]( int n, auto fn ) {
+		std::vector<std::thread> th;
+		for( int k = 0; k < nThreads; k++ )
+			th.emplace_back( [&, k]() { for( int i = k; i < n; i += nThreads ) fn( i ); } );
+		for( auto& t : th ) t.join();
+	};
+	par( h, [&]( int y ) { scanLine( sat.data() + (size_t)y * w, w, 1 ); } );
+	par( w, [&]( int x ) { scanLine( sat.data() + x, h, (size_t)w ); } );
+	// buildSAT2u32 (:600-608)
+	size_t n = (size_t)w * h;
+	double sum = sat[n - 1];
+	for( size_t i = 0; i < n; i++ ) out[i] = (uint32_t)( sat[i] / ( sum ) * (double)0xFFFFFFFFu );
+}
+
+// getHitN, voxCommon.hpp:564-577
+inline F3 getHitN( int major, F3 rd )
+{
+	switch( major )
+	{
+	case 0:
+		return { 0.0f, 0.0f, 0.0f < rd.z ? -1.0f : 1.0f };
+	case 1:
+		return { 0.0f < rd.x ? -1.0f : 1.0f, 0.0f, 0.0f };
+	case 2:
+		return { 0.0f, 0.0f < rd.y ? -1.0f : 1.0f, 0.0f };
+	}
+	return { 0.0f, 0.0f, 0.0f };
+}
+inline F3 rawReflectance( const uint8_t* c ) { return { (float)c[0] / 255.0f, (float)c[1] / 255.0f, (float)c[2] / 255.0f }; } // renderCommon.hpp:160-166
+
+struct PtScene
+{
+	const OrcOctree* octree;
+	const uint8_t* attrs; // VoxelAttirb[nVoxels]: color uchar4, emission uchar4 (voxCommon.hpp:121-125)
+	uint32_t hasEmission;
+	float emissionScale; // IntersectorOctreeGPU.hpp:273
+	Hdri hdri;
+	const float* pmj;
+	int maxDepth;
+};
+inline void isect( const PtScene& s, F3 ro, F3 rd, bool shadow, float* t, int* nMajor, uint32_t* vIndex, uint64_t* rays )
+{
+	orc_intersect_batch( s.octree, &ro.x, &rd.x, 1, shadow ? 1 : 0, t, nMajor, vIndex, nullptr );
+	( *rays )++;
+}
+inline F3 voxelEmission( const PtScene& s, uint32_t vIndex, bool withScale )
+{
+	return rawReflectance( s.attrs + (size_t)vIndex * 8 + 4 ) * ( withScale ? s.emissionScale : 1.0f );
+}
+
+// one (pixel, spp) path of renderPT, voxKernel.cu:633-761; returns L
+F3 tracePath( const PtScene& s, const OrcCamera& cam, uint32_t x, uint32_t y, uint32_t pixelIdx, uint32_t spp, int w, int h, uint64_t* rays )
+{
+	Murmur hash( 0 );
+	hash.combine( pixelIdx );
+	int dim = 0;
+	const uint32_t stream = hash.getHash();
+	auto SAMPLE_2D = [&]( float* a, float* b ) { sample2d( s.pmj, spp, (uint32_t)( dim++ ), stream, a, b ); };
+
+	float c0, c1, l0, l1;
+	SAMPLE_2D( &c0, &c1 );
+	SAMPLE_2D( &l0, &l1 );
+	F3 ro, rd;
+	orc_camera_shoot_thin_lens( &cam, (int)x, (int)y, c0, c1, w, h, l0, l1, &ro.x, &rd.x );
+
+	F3 T = { 1.0f, 1.0f, 1.0f };
+	F3 L = { 0.0f, 0.0f, 0.0f };
+	float t = FLT_MAX;
+	int nMajor = 0;
+	uint32_t vIndex = 0;
+	isect( s, ro, rd, false, &t, &nMajor, &vIndex, rays );
+	if( t == FLT_MAX )
+		L = L + T * s.hdri.sampleNearest( rd, true );
+	else
+		L = L + T * voxelEmission( s, vIndex, false );
+
+	for( int depth = 0; depth < s.maxDepth && t != FLT_MAX; depth++ )
+	{
+		F3 R = rawReflectance( s.attrs + (size_t)vIndex * 8 );
+		F3 hitN = getHitN( nMajor, rd );
+		F3 hitP = ro + rd * t;
+		if( s.hdri.enabled() )
+		{
+			float u0, u1, u2, u3;
+			SAMPLE_2D( &u0, &u1 );
+			SAMPLE_2D( &u2, &u3 );
+			F3 dir, emissive;
+			float p;
+			s.hdri.importanceSample( &dir, &emissive, &p, hitN, true, u0, u1, u2, u3, nullptr );
+			float t2 = FLT_MAX;
+			int nm2 = 0;
+			uint32_t vi2 = 0;
+			isect( s, hitP, dir, true, &t2, &nm2, &vi2, rays );
+			if( t2 == FLT_MAX ) L = L + T * ( R / PI ) * smaxf( dot( hitN, dir ), 0.0f ) * emissive / p;
+		}
+		T = T * R;
+		const int nSampleExtraDirect = s.hasEmission ? 1 : 0; // EXTRA_IMPLICIT_SAMPLING, renderCommon.hpp:15
+		for( int k = 0; depth == 0 && k < nSampleExtraDirect; k++ )
+		{
+			float a, b;
+			SAMPLE_2D( &a, &b );
+			F3 dir = sampleLambertian( a, b, hitN );
+			float t2 = FLT_MAX;
+			int nm2 = 0;
+			uint32_t vi2 = 0;
+			isect( s, hitP, dir, false, &t2, &nm2, &vi2, rays );
+			if( t2 != FLT_MAX ) L = L + T * voxelEmission( s, vi2, true ) / (float)( 1 + nSampleExtraDirect );
+		}
+		float a, b;
+		SAMPLE_2D( &a, &b );
+		F3 dir = sampleLambertian( a, b, hitN );
+		ro = hitP;
+		rd = dir;
+		t = FLT_MAX;
+		isect( s, ro, rd, false, &t, &nMajor, &vIndex, rays );
+		if( t != FLT_MAX )
+		{
+			F3 Le = voxelEmission( s, vIndex, true );
+			L = L + T * Le * ( depth == 0 ? 1.0f / (float)( 1 + nSampleExtraDirect ) : 1.0f );
+		}
+	}
+	return L;
+}
+} // namespace
+
+extern "C" {
+uint32_t orc_murmur_combine( uint32_t seed, const uint32_t* values, int n )
+{
+	Murmur h( seed );
+	for( int i = 0; i < n; i++ ) h.combine( values[i] );
+	return h.getHash();
+}
+void orc_pcg32_stream( uint64_t seed, uint64_t stream, int n, uint32_t* out )
+{
+	PCG32 rng;
+	rng.setup( seed, stream );
+	for( int i = 0; i < n; i++ ) out[i] = rng.nextU32();
+}
+uint32_t orc_nested_uniform_scramble( uint32_t x, uint32_t seed ) { return nus( x, seed ); }
+float orc_scramble_f32( float x, uint32_t seed ) { return scramble_f32( x, seed ); }
+// PMJSampler::setup, pmjSampler.hpp:114-134: 128 sequences x 4096 samples x 2 floats from PCG32( 0, 2525 )
+void orc_pmj_table( float* out )
+{
+	PCG32 rng;
+	rng.setup( 0, 2525 );
+	for( int i = 0; i < 128; i++ ) pmj02( 4096, out + (size_t)2 * 4096 * i, rng );
+}
+void orc_pmj_sample2d( const float* table, uint32_t sampleIdx, uint32_t dimension, uint32_t stream, float* xy )
+{
+	sample2d( table, sampleIdx, dimension, stream, &xy[0], &xy[1] );
+}
+// HDRI::load, renderCommon.hpp:214-314: sats = [7][w*h] (global, +x, -x, +y, -y, +z, -z)
+void orc_hdri_build_sats( const float* rgba, int w, int h, uint32_t* sats )
+{
+	int nThreads = (int)std::thread::hardware_concurrency();
+	if( nThreads < 1 ) nThreads = 1;
+	const F3 axes[6] = { { 1, 0, 0 }, { -1, 0, 0 }, { 0, 1, 0 }, { 0, -1, 0 }, { 0, 0, 1 }, { 0, 0, -1 } };
+	const size_t n = (size_t)w * h;
+	buildSat( rgba, w, h, sats, 0, F3{ 0, 0, 0 }, nThreads );
+	for( int i = 0; i < 6; i++ ) buildSat( rgba, w, h, sats + n * ( i + 1 ), 1, axes[i], nThreads );
+}
+void orc_hdri_importance_sample( const float* rgba, const uint32_t* sats, int w, int h, float scale, const float* N, int axisAligned,
+								 float u0, float u1, float u2, float u3, float* dir, float* L, float* srPDF, uint32_t* XY )
+{
+	Hdri hd{ rgba, nullptr, sats, w, h, w, h, scale };
+	F3 d, l;
+	hd.importanceSample( &d, &l, srPDF, F3{ N[0], N[1], N[2] }, axisAligned != 0, u0, u1, u2, u3, XY );
+	dir[0] = d.x, dir[1] = d.y, dir[2] = d.z;
+	L[0] = l.x, L[1] = l.y, L[2] = l.z;
+}
+void orc_hdri_sample_nearest( const float* rgba, int w, int h, float scale, const float* d, float* out )
+{
+	Hdri hd{ rgba, nullptr, nullptr, w, h, w, h, scale };
+	F3 c = hd.sampleNearest( F3{ d[0], d[1], d[2] }, false );
+	out[0] = c.x, out[1] = c.y, out[2] = c.z;
+}
+void orc_sample_lambertian( float a, float b, const float* Ng, float* out )
+{
+	F3 d = sampleLambertian( a, b, F3{ Ng[0], Ng[1], Ng[2] } );
+	out[0] = d.x, out[1] = d.y, out[2] = d.z;
+}
+
+// renderPT (voxKernel.cu:610-777), rows [y0,y1) of one step (= 16 spp, spp = iteration*16 + localSpp).
+// accum: float4[w*h] (rgb sum, w = spp count), accumulated INTO (`+=`, :770-774).  The reference sums the 16 samples of a
+// pixel with shared-memory atomicAdd (order unspecified); here they are summed in localSpp order, then added to the pixel.
+// hdriRgba == NULL or hdriScale <= 0 disables the environment (HDRI::isEnabled).  stats (optional): [0] += rays traced.
+void orc_pt_render( const OrcOctree* octree, const uint8_t* attrs, uint32_t hasEmission, const OrcCamera* cam, int w, int h, int y0, int y1,
+					int iteration, const float* hdriRgba, const uint32_t* sats, int hw, int hh, float hdriScale,
+					const float* primaryRgba, int wP, int hP, const float* pmjTable, int maxDepth, float* accum, uint64_t* stats, int nThreads )
+{
+	PtScene s;
+	s.octree = octree;
+	s.attrs = attrs;
+	s.hasEmission = hasEmission;
+	s.emissionScale = 7.5f;
+	s.hdri = Hdri{ hdriRgba, primaryRgba, sats, hw, hh, primaryRgba ? wP : hw, primaryRgba ? hP : hh, hdriRgba ? hdriScale : 0.0f };
+	s.pmj = pmjTable;
+	s.maxDepth = maxDepth;
+	if( nThreads < 1 ) nThreads = 1;
+	std::vector<uint64_t> rays( nThreads, 0 );
+	std::vector<std::thread> th;
+	for( int k = 0; k < nThreads; k++ )
+		th.emplace_back( [&, k]() {
+			for( int y = y0 + k; y < y1; y += nThreads )
+				for( int x = 0; x < w; x++ )
+				{
+					const uint32_t pixelIdx = (uint32_t)y * w + x;
+					float lx = 0.0f, ly = 0.0f, lz = 0.0f;
+					for( uint32_t localSpp = 0; localSpp < 16; localSpp++ )
+					{
+						F3 L = tracePath( s, *cam, x, y, pixelIdx, (uint32_t)iteration * 16 + localSpp, w, h, &rays[k] );
+						lx += L.x, ly += L.y, lz += L.z;
+					}
+					float* px = accum + (size_t)pixelIdx * 4;
+					px[0] += lx, px[1] += ly, px[2] += lz, px[3] += 16.0f;
+				}
+		} );
+	for( auto& t : th ) t.join();
+	if( stats )
+		for( int k = 0; k < nThreads; k++ ) stats[0] += rays[k];
+}
+// renderResolve, voxKernel.cu:779-795 (powf on the host, vectorMath.hpp:93-97)
+void orc_pt_resolve( const float* accum, uint64_t n, uint8_t* rgba )
+{
+	for( uint64_t i = 0; i < n; i++ )
+	{
+		const float* v = accum + i * 4;
+		for( int c = 0; c < 3; c++ )
+		{
+			float f = 255 * powf( v[c] / v[3], 1.0f / 2.2f ) + 0.5f;
+			int q = _mm_cvttss_si32( _mm_set_ss( f ) );
+			rgba[i * 4 + c] = (uint8_t)( q < 255 ? q : 255 );
+		}
+		rgba[i * 4 + 3] = 255;
+	}
+}
+}

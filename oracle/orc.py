@@ -91,14 +91,84 @@ class Oracle:
         L.orc_nested_uniform_scramble.argtypes = [C.c_uint32, C.c_uint32]
         L.orc_scramble_f32.restype = C.c_float
         L.orc_scramble_f32.argtypes = [C.c_float, C.c_uint32]
-        L.orc_hdri_build_sats.argtypes = [f32p, C.c_int, C.c_int, u32p]
         L.orc_hdri_importance_sample.argtypes = [f32p, u32p, C.c_int, C.c_int, C.c_float, f32p, C.c_int,
                                                  C.c_float, C.c_float, C.c_float, C.c_float, f32p, f32p, f32p, u32p]
-        L.orc_hdri_sample_nearest.argtypes = [f32p, C.c_int, C.c_int, C.c_float, f32p, f32p]
         L.orc_sample_lambertian.argtypes = [C.c_float, C.c_float, f32p, f32p]
-        L.orc_pt_render.argtypes = [C.c_void_p, u8p, C.c_uint32, C.POINTER(Camera), C.c_int, C.c_int,
-                                    C.c_int, C.c_int, C.c_int, f32p, u32p, C.c_int, C.c_int, C.c_float,
-                                    C.c_void_p, C.c_int, C.c_int, f32p, C.c_int, f32p, C.c_void_p]
+        if not hasattr(L, "orc_pt_render"):
+            return  # the reference library: device-only pieces are not available on the host
+        L.orc_hdri_build_sats.argtypes = [f32p, C.c_int, C.c_int, u32p]
+        L.orc_hdri_sample_nearest.argtypes = [f32p, C.c_int, C.c_int, C.c_float, f32p, f32p]
+        L.orc_pt_render.argtypes = [C.c_void_p, u8p, C.c_uint32, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                    C.c_void_p, C.c_int, C.c_int, f32p, C.c_int, f32p, C.c_void_p, C.c_int]
+        L.orc_pt_resolve.argtypes = [f32p, C.c_uint64, u8p]
+
+    # ---- sampler / environment (path-tracing half) ----
+    def murmur(self, seed, values):
+        v = np.ascontiguousarray(values, np.uint32).reshape(-1)
+        return int(self.lib.orc_murmur_combine(seed, v, v.size))
+
+    def pcg32(self, seed, stream, n):
+        out = np.zeros(n, np.uint32)
+        self.lib.orc_pcg32_stream(seed, stream, n, out)
+        return out
+
+    def pmj_table(self):
+        out = np.zeros(128 * 4096 * 2, np.float32)
+        self.lib.orc_pmj_table(out)
+        return out
+
+    def pmj_sample2d(self, table, sample_idx, dim, stream):
+        xy = np.zeros(2, np.float32)
+        self.lib.orc_pmj_sample2d(table, sample_idx, dim, stream, xy)
+        return xy
+
+    def hdri_build_sats(self, rgba, w, h):
+        rgba = np.ascontiguousarray(rgba, np.float32).reshape(-1)
+        sats = np.zeros(7 * w * h, np.uint32)
+        self.lib.orc_hdri_build_sats(rgba, w, h, sats)
+        return sats
+
+    def hdri_importance_sample(self, rgba, sats, w, h, scale, n, axis_aligned, u):
+        d = np.zeros(3, np.float32)
+        l = np.zeros(3, np.float32)
+        p = np.zeros(1, np.float32)
+        xy = np.zeros(2, np.uint32)
+        self.lib.orc_hdri_importance_sample(np.ascontiguousarray(rgba, np.float32).reshape(-1), sats, w, h, scale,
+                                            np.asarray(n, np.float32), int(axis_aligned), u[0], u[1], u[2], u[3], d, l, p, xy)
+        return d, l, float(p[0]), xy
+
+    def hdri_sample_nearest(self, rgba, w, h, scale, d):
+        out = np.zeros(3, np.float32)
+        self.lib.orc_hdri_sample_nearest(np.ascontiguousarray(rgba, np.float32).reshape(-1), w, h, scale,
+                                         np.asarray(d, np.float32), out)
+        return out
+
+    def sample_lambertian(self, a, b, ng):
+        out = np.zeros(3, np.float32)
+        self.lib.orc_sample_lambertian(a, b, np.asarray(ng, np.float32), out)
+        return out
+
+    def pt_render(self, tree, colors, emissions, has_emission, cam, w, h, iteration, pmj, accum, hdri=None, sats=None,
+                  hdri_wh=(0, 0), hdri_scale=1.75, primary=None, primary_wh=(0, 0), max_depth=8, y0=0, y1=None, threads=0):
+        """One renderPT step (16 spp) accumulated into ``accum`` (float32 [h*w*4]); returns rays traced."""
+        attrs = np.ascontiguousarray(np.concatenate([np.asarray(colors, np.uint8).reshape(-1, 4),
+                                                     np.asarray(emissions, np.uint8).reshape(-1, 4)], axis=1)).reshape(-1)
+        st = np.zeros(1, np.uint64)
+        threads = threads or (os.cpu_count() or 1)
+        hp = np.ascontiguousarray(hdri, np.float32).reshape(-1) if hdri is not None else None
+        pp = np.ascontiguousarray(primary, np.float32).reshape(-1) if primary is not None else None
+        self.lib.orc_pt_render(tree.h, attrs, int(has_emission), C.byref(cam), w, h, y0, h if y1 is None else y1, iteration,
+                               hp.ctypes.data if hp is not None else None, sats.ctypes.data if sats is not None else None,
+                               hdri_wh[0], hdri_wh[1], hdri_scale, pp.ctypes.data if pp is not None else None,
+                               primary_wh[0], primary_wh[1], pmj, max_depth, accum, st.ctypes.data, threads)
+        return int(st[0])
+
+    def pt_resolve(self, accum):
+        accum = np.ascontiguousarray(accum, np.float32).reshape(-1)
+        out = np.zeros(accum.size, np.uint8)
+        self.lib.orc_pt_resolve(accum, accum.size // 4, out)
+        return out
 
     # ---- morton ----
     def morton_encode(self, x, y, z):

@@ -289,3 +289,7 @@ uint64_t orc_fnv1a64( const void* p, uint64_t bytes )
 	return h;
 }
 }
+
+// The reference headers define non-inline functions (embedMask, octreeTraverse_EfficientParametric), so the
+// path-tracing glue has to live in the same translation unit.
+#include "ref_driver_pt.cpp"

@@ -69,3 +69,26 @@ def dragon_standin(levels=5, noise=0.15):
     t = subdivide(tris, levels, noise)
     col, emi = vertex_colors(t)
     return t, col, emi
+
+
+def procedural_hdri(w=256, h=128, seed=0):
+    """Procedural lat-long sky + sun (RGBA32F, float32 [h,w,4]) standing in for the missing monks_forest_2k.hdr
+    (SURVEY.md section 8d): gradient sky, a bright sun lobe, hash noise so no two texels tie."""
+    y = (np.arange(h, dtype=np.float32) + np.float32(0.5)) / np.float32(h)
+    x = (np.arange(w, dtype=np.float32) + np.float32(0.5)) / np.float32(w)
+    X, Y = np.meshgrid(x, y)
+    theta = Y * np.float32(np.pi)
+    phi = X * np.float32(2 * np.pi)
+    d = np.stack([np.cos(phi) * np.sin(theta), np.cos(theta), np.sin(phi) * np.sin(theta)], -1).astype(np.float32)
+    sun = np.asarray([0.5, 0.7, 0.3], np.float32)
+    sun /= np.linalg.norm(sun)
+    c = np.clip((d * sun).sum(-1), 0, 1).astype(np.float32)
+    sky = np.float32(0.25) + np.float32(0.75) * np.clip(d[..., 1], 0, 1)
+    rng = np.random.default_rng(seed)
+    noise = rng.random((h, w), dtype=np.float32) * np.float32(0.05)
+    img = np.zeros((h, w, 4), np.float32)
+    img[..., 0] = sky * np.float32(0.6) + np.float32(40.0) * c ** 64 + noise
+    img[..., 1] = sky * np.float32(0.8) + np.float32(36.0) * c ** 64 + noise
+    img[..., 2] = sky * np.float32(1.0) + np.float32(30.0) * c ** 64 + noise
+    img[..., 3] = 1.0
+    return np.ascontiguousarray(img)
