@@ -1,0 +1,905 @@
+// pt.cu -- the path tracer behind hako_pt_* (PathTracer, PathTracer.hpp:14-170; renderPT / renderResolve / the HDRI
+// SAT kernels, voxKernel.cu:485-795; PMJSampler, pmjSampler.hpp; HDRI, renderCommon.hpp:204-481).
+//
+// What is kept from the reference: the sample mapping (stream = Murmur(pixelIdx), spp = iteration*16 + localSpp, the
+// dimension order of SURVEY.md appendix A 28-30), the estimator, and every fp32 expression in its operation order.
+// What is redesigned for B200:
+//   - no megakernel with four divergent traversal call sites and a 1 GiB global stack pool: a PERSISTENT kernel runs a
+//     per-lane path state machine in which every loop iteration traces exactly one ray per lane -- primary, shadow,
+//     extra-implicit and bounce rays of different lanes go through ONE traversal call site, so a warp stays converged
+//     across ray kinds;
+//   - lanes whose path ended are refilled at once: warp ballot -> rank by popc -> indices from a per-warp chunk that is
+//     fetched from a global work counter (one atomic per 256 paths);
+//   - radiance is written per path and reduced per pixel in localSpp order by a second kernel, so a step is
+//     DETERMINISTIC (the reference's shared-memory atomicAdd order is not) and equals the oracle's summation order;
+//   - theta-only trigonometry of the lat-long map is tabulated per row on the host (exactly the values the CPU code
+//     computes), the SAT build is bit-exact with the oracle (same fp32 products, same Hillis-Steele double sums).
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "internal.cuh"
+#include "traverse.cuh"
+
+using namespace hako;
+
+#define PT_SPP 16		  // nBatchSpp, voxKernel.cu:631
+#define PT_BLOCK 256
+#define PT_CHUNK 256	  // paths fetched from the global counter per warp-level atomic
+#define PMJ_LENGTH 4096	  // pmjSampler.hpp:107-111
+#define PMJ_NSEQ 128
+
+struct hako_pt
+{
+	hako_ctx* ctx = nullptr;
+	int w = 0, h = 0;
+	float4* accum = nullptr; // rgb sum, w = spp count (PathTracer.hpp:81-97)
+	uchar4* rgba8 = nullptr;
+	float* pmj = nullptr; // [128][4096][2]
+	// environment (HDRI, renderCommon.hpp:472-480)
+	float4* hdriPixels = nullptr;
+	float4* hdriPrimary = nullptr;
+	uint32_t* sats = nullptr; // [7][hw*hh]: global, +x, -x, +y, -y, +z, -z
+	float4* rowTab = nullptr; // per row: { sr, cos(theta), cos(theta+dTheta), 0 }
+	int hw = 0, hh = 0, wP = 0, hP = 0;
+	float hdriScale = 1.75f; // HDRI::m_scale, renderCommon.hpp:480
+	// per-path radiance of the step in flight
+	float4* pathL = nullptr;
+	uint64_t pathCap = 0;
+	unsigned long long* counters = nullptr; // [0] work counter, [1] rays traced
+};
+
+namespace
+{
+struct PtEnv
+{
+	const float4* pixels;
+	const float4* primary;
+	const uint32_t* sats;
+	const float4* rowTab;
+	int w, h, wP, hP;
+	float scale;
+};
+struct PtParams
+{
+	OctreeView tree;
+	PtEnv env;
+	hako_camera cam;
+	const float* pmj;
+	float4* pathL;
+	unsigned long long* counters;
+	int w, h, y0;
+	uint32_t nPaths;
+	uint32_t iteration;
+	int maxDepth;
+};
+
+// ---- PMJ02 lookup with Owen scrambling, pmjSampler.hpp:62-102,158-173 ----
+__device__ __forceinline__ uint32_t hashCombine3( uint32_t a, uint32_t b, uint32_t c )
+{
+	Murmur32 h( a );
+	h.combine( b );
+	h.combine( c );
+	return h.getHash();
+}
+__device__ __forceinline__ uint32_t laineKarras( uint32_t x, uint32_t seed )
+{
+	x += seed;
+	x ^= x * 0x6c50b47cu;
+	x ^= x * 0xb82f1e52u;
+	x ^= x * 0xc7afe638u;
+	x ^= x * 0x8d22f6e6u;
+	return x;
+}
+__device__ __forceinline__ uint32_t nestedUniformScramble( uint32_t x, uint32_t seed ) { return __brev( laineKarras( __brev( x ), seed ) ); }
+__device__ __forceinline__ float scrambleF32( float x, uint32_t seed )
+{
+	x += 1.0f;
+	const uint32_t bits = __float_as_uint( x );
+	return __uint_as_float( 0x3f800000u | ( nestedUniformScramble( bits & 0x7FFFFFu, seed ) & 0x7FFFFFu ) ) - 1.0f;
+}
+__device__ __forceinline__ float2 pmjSample2d( const float* __restrict__ table, uint32_t sampleIdx, uint32_t dimension, uint32_t stream )
+{
+	sampleIdx = nestedUniformScramble( sampleIdx, hashCombine3( stream, dimension, 31082745u ) ) & ( PMJ_LENGTH - 1 );
+	dimension = nestedUniformScramble( dimension, hashCombine( stream, 54761983u ) ) & ( PMJ_NSEQ - 1 );
+	const float2 s = __ldg( (const float2*)table + ( dimension * PMJ_LENGTH + sampleIdx ) );
+	return make_float2( scrambleF32( s.x, hashCombine3( stream, dimension, 83927105u ) ), scrambleF32( s.y, hashCombine3( stream, dimension, 12654890u ) ) );
+}
+
+// ---- sampleLambertian / GetOrthonormalBasis, renderCommon.hpp:119-151 ----
+__device__ __forceinline__ V3 sampleLambertian( float a, float b, V3 Ng )
+{
+	const float r = sqrtf( a );
+	const float theta = b * HAKO_PI * 2.0f;
+	const float x = r * cosf( theta );
+	const float y = r * sinf( theta );
+	const float z = sqrtf( smax( 1.0f - a, 0.0f ) );
+	const float sign = copysignf( 1.0f, Ng.z );
+	const float aa = -1.0f / ( sign + Ng.z );
+	const float bb = Ng.x * Ng.y * aa;
+	const V3 xaxis = { 1.0f + sign * Ng.x * Ng.x * aa, sign * bb, -sign * Ng.x };
+	const V3 yaxis = { bb, sign + Ng.y * Ng.y * aa, -Ng.y };
+	return xaxis * x + yaxis * y + Ng * z;
+}
+
+// ---- HDRI, renderCommon.hpp:354-470 ----
+__device__ __forceinline__ uint32_t satPsH( const PtEnv& e, const uint32_t* __restrict__ sat, uint32_t x )
+{
+	return x == 0 ? 0u : __ldg( sat + (size_t)e.w * ( e.h - 1 ) + x - 1 );
+}
+__device__ __forceinline__ uint32_t satPsV( const PtEnv& e, const uint32_t* __restrict__ sat, uint32_t x, uint32_t y )
+{
+	if( y == 0 ) return 0u;
+	const uint32_t s0 = x == 0 ? 0u : __ldg( sat + (size_t)e.w * ( y - 1 ) + ( x - 1 ) );
+	const uint32_t s1 = __ldg( sat + (size_t)e.w * ( y - 1 ) + x );
+	return s1 - s0;
+}
+__device__ __forceinline__ uint32_t satCount( const PtEnv& e, const uint32_t* __restrict__ sat, uint32_t x, uint32_t y )
+{
+	const uint32_t a = ( x == 0 || y == 0 ) ? 0u : __ldg( sat + (size_t)e.w * ( y - 1 ) + ( x - 1 ) );
+	const uint32_t b = ( y == 0 ) ? 0u : __ldg( sat + (size_t)e.w * ( y - 1 ) + x );
+	const uint32_t c = ( x == 0 ) ? 0u : __ldg( sat + (size_t)e.w * y + ( x - 1 ) );
+	const uint32_t d = __ldg( sat + (size_t)e.w * y + x );
+	return ( d - b ) + ( a - c );
+}
+__device__ __forceinline__ void hdriImportanceSample( const PtEnv& e, V3* dir, V3* L, float* srPDF, V3 N, float u0, float u1, float u2, float u3 )
+{
+	const size_t n = (size_t)e.w * e.h;
+	const uint32_t* sat = e.sats;
+	const float k = 0.8f; // axis-aligned tables, :372-399
+	if( k < N.x )
+		sat += 1 * n;
+	else if( N.x < -k )
+		sat += 2 * n;
+	else if( k < N.y )
+		sat += 3 * n;
+	else if( N.y < -k )
+		sat += 4 * n;
+	else if( k < N.z )
+		sat += 5 * n;
+	else if( N.z < -k )
+		sat += 6 * n;
+
+	// upper_bound_f (:187-202) over the marginal, then over the column
+	int i = 0, j = e.w;
+	while( i < j )
+	{
+		const int m = ( i + j ) / 2;
+		const float v = (float)satPsH( e, sat, m ) / (float)0xFFFFFFFFu;
+		if( v <= u0 )
+			i = m + 1;
+		else
+			j = m;
+	}
+	const uint32_t X = (uint32_t)i - 1;
+	const uint32_t vol = satPsH( e, sat, X + 1 ) - satPsH( e, sat, X );
+	i = 0, j = e.h;
+	while( i < j )
+	{
+		const int m = ( i + j ) / 2;
+		const float v = (float)satPsV( e, sat, X, m ) / (float)vol;
+		if( v <= u1 )
+			i = m + 1;
+		else
+			j = m;
+	}
+	const uint32_t Y = (uint32_t)i - 1;
+	const float pSelection = (float)satCount( e, sat, X, Y ) / (float)0xFFFFFFFFu;
+	const float dPhi = 2.0f * HAKO_PI / (float)e.w;
+	const float4 row = __ldg( e.rowTab + Y ); // sr, cos(theta), cos(theta+dTheta): theta-only terms, tabulated by the host
+	const float sY = mixf( row.y, row.z, u2 );
+	const float phi = dPhi * ( (float)X + u3 ) + HAKO_PI;
+	const float sX = cosf( phi );
+	const float sZ = sinf( phi );
+	const float sinTheta = sqrtf( smax( 1.0f - sY * sY, 0.0f ) );
+	*dir = { sX * sinTheta, sY, sZ * sinTheta };
+	*srPDF = pSelection / row.x;
+	const float4 c = __ldg( e.pixels + (size_t)Y * e.w + X );
+	*L = V3{ c.x, c.y, c.z } * e.scale;
+}
+__device__ __forceinline__ V3 hdriSampleNearest( const PtEnv& e, V3 d, bool isPrimary )
+{
+	const int w = isPrimary ? e.wP : e.w;
+	const int h = isPrimary ? e.hP : e.h;
+	const float phi = atan2f( d.z, d.x ) + HAKO_PI; // getSpherical, :176-181
+	const float theta = atan2f( sqrtf( d.x * d.x + d.z * d.z ), d.y );
+	const float u = phi / ( HAKO_PI * 2.0f ), v = theta / HAKO_PI;
+	const int x = f2i_x86( smin( smax( u * w, 0.0f ), (float)( w - 1.0f ) ) );
+	const int y = f2i_x86( smin( smax( v * h, 0.0f ), (float)( h - 1.0f ) ) );
+	const size_t index = (size_t)y * w + x;
+	const float4 c = ( isPrimary && e.primary ) ? __ldg( e.primary + index ) : __ldg( e.pixels + index );
+	return V3{ c.x, c.y, c.z } * e.scale;
+}
+// rawReflectance, renderCommon.hpp:160-166, on a packed uchar4
+__device__ __forceinline__ V3 rawReflectance( uint32_t c ) { return { (float)( c & 0xFFu ) / 255.0f, (float)( ( c >> 8 ) & 0xFFu ) / 255.0f, (float)( ( c >> 16 ) & 0xFFu ) / 255.0f }; }
+// VoxelAttirb (voxCommon.hpp:121-125) as one 8-byte read-only load: .x = color, .y = emission
+__device__ __forceinline__ uint2 loadAttrib( const OctreeView& v, uint32_t vIndex ) { return __ldg( (const uint2*)v.attrs + vIndex ); }
+} // namespace
+
+namespace
+{
+enum : uint32_t
+{
+	RAY_PRIMARY = 0,
+	RAY_SHADOW = 1,
+	RAY_EXTRA = 2,
+	RAY_BOUNCE = 3,
+	LANE_IDLE = 4
+};
+enum : uint32_t
+{
+	NEXT_TRACE = 0,
+	NEXT_SHADE,
+	NEXT_GEN_EXTRA,
+	NEXT_GEN_BOUNCE,
+	NEXT_FINISH
+};
+
+// renderPT, voxKernel.cu:610-777, as a persistent per-lane state machine (see the header of this file).
+// Path index -> (pixel, localSpp) keeps the reference's "16 adjacent threads share a pixel" (:635-637).
+__global__ void __launch_bounds__( PT_BLOCK ) pathTraceKernel( const PtParams p )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const bool envOn = 0.0f < p.env.scale && p.env.pixels != nullptr; // HDRI::isEnabled
+	const uint32_t nExtra = p.tree.hasEmission ? 1u : 0u;			  // EXTRA_IMPLICIT_SAMPLING, :720
+
+	// warp-uniform chunk of path indices
+	uint32_t wNext = 0, wEnd = 0;
+	bool drained = false;
+
+	// per-lane path state
+	uint32_t kind = LANE_IDLE;
+	uint32_t path = 0, spp = 0, stream = 0, dim = 0;
+	int depth = 0;
+	V3 o = {}, d = {};
+	V3 T = {}, L = {}, pending = {}, hitN = {};
+	unsigned long long rays = 0;
+
+	for( ;; )
+	{
+		// ---- refill idle lanes: ballot -> rank -> index (persistent-thread work fetch) ----
+		const uint32_t idleMask = __ballot_sync( 0xFFFFFFFFu, kind == LANE_IDLE );
+		if( idleMask && !drained )
+		{
+			if( wNext == wEnd )
+			{
+				uint32_t base = 0;
+				if( lane == 0 ) base = (uint32_t)atomicAdd( p.counters, (unsigned long long)PT_CHUNK );
+				base = __shfl_sync( 0xFFFFFFFFu, base, 0 );
+				if( base >= p.nPaths )
+					drained = true;
+				else
+				{
+					wNext = base;
+					wEnd = min( base + PT_CHUNK, p.nPaths );
+				}
+			}
+			if( !drained )
+			{
+				const uint32_t rank = __popc( idleMask & ( ( 1u << lane ) - 1u ) );
+				const uint32_t avail = wEnd - wNext;
+				if( kind == LANE_IDLE && rank < avail )
+				{
+					path = wNext + rank;
+					const uint32_t localPixel = path / PT_SPP, localSpp = path % PT_SPP;
+					const uint32_t x = localPixel % (uint32_t)p.w, y = (uint32_t)p.y0 + localPixel / (uint32_t)p.w;
+					const uint32_t pixelIdx = y * (uint32_t)p.w + x;
+					spp = p.iteration * PT_SPP + localSpp;
+					Murmur32 hs( 0 );
+					hs.combine( pixelIdx );
+					stream = hs.getHash();
+					dim = 0;
+					const float2 cam_u01 = pmjSample2d( p.pmj, spp, dim++, stream );
+					const float2 lens_u01 = pmjSample2d( p.pmj, spp, dim++, stream );
+					cameraShootThinLens( p.cam, (int)x, (int)y, cam_u01.x, cam_u01.y, p.w, p.h, lens_u01.x, lens_u01.y, &o, &d );
+					T = { 1.0f, 1.0f, 1.0f };
+					L = { 0.0f, 0.0f, 0.0f };
+					depth = 0;
+					kind = RAY_PRIMARY;
+				}
+				wNext += min( (uint32_t)__popc( idleMask ), avail );
+			}
+		}
+		if( __all_sync( 0xFFFFFFFFu, kind == LANE_IDLE ) )
+		{
+			if( drained ) break;
+			continue;
+		}
+
+		// ---- extend: ONE traversal call site for every ray kind ----
+		float t = HAKO_MAX_FLOAT;
+		int nMajor = 0;
+		uint32_t vIndex = 0;
+		bool hit = false;
+		if( kind != LANE_IDLE )
+		{
+			hit = octreeTraverseImpl( p.tree, o, d, kind == RAY_SHADOW, &t, &nMajor, &vIndex );
+			rays++;
+		}
+
+		// ---- shade ----
+		if( kind == LANE_IDLE ) continue;
+		uint32_t next;
+		if( kind == RAY_PRIMARY )
+		{
+			if( !hit )
+			{
+				if( p.env.pixels ) L = L + T * hdriSampleNearest( p.env, d, true ); // :678-683
+				next = NEXT_FINISH;
+			}
+			else
+			{
+				L = L + T * rawReflectance( loadAttrib( p.tree, vIndex ).y ); // unscaled, :686-688
+				next = NEXT_SHADE;
+			}
+		}
+		else if( kind == RAY_SHADOW )
+		{
+			if( !hit ) L = L + pending; // :712-715
+			next = ( depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
+		}
+		else if( kind == RAY_EXTRA )
+		{
+			if( hit ) // :733-736
+				L = L + T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) / (float)( 1u + nExtra );
+			next = NEXT_GEN_BOUNCE;
+		}
+		else
+		{
+			if( hit ) // :750-758
+				L = L + T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) * ( depth == 0 ? 1.0f / (float)( 1u + nExtra ) : 1.0f );
+			depth++;
+			next = ( hit && depth < p.maxDepth ) ? NEXT_SHADE : NEXT_FINISH;
+		}
+
+		if( next == NEXT_SHADE )
+		{
+			// surface point of the path ray (o, d) that just hit: :693-695
+			const V3 R = rawReflectance( loadAttrib( p.tree, vIndex ).x );
+			hitN = getHitN( nMajor, d );
+			o = o + d * t; // hitP: every following ray of this vertex starts here, without an epsilon
+			if( envOn )
+			{
+				const float2 u01 = pmjSample2d( p.pmj, spp, dim++, stream );
+				const float2 u23 = pmjSample2d( p.pmj, spp, dim++, stream );
+				V3 dir, emissive;
+				float pdf;
+				hdriImportanceSample( p.env, &dir, &emissive, &pdf, hitN, u01.x, u01.y, u23.x, u23.y );
+				pending = T * ( R / HAKO_PI ) * smax( dot( hitN, dir ), 0.0f ) * emissive / pdf;
+				T = T * R;
+				d = dir;
+				kind = RAY_SHADOW;
+				next = NEXT_TRACE;
+			}
+			else
+			{
+				T = T * R;
+				next = ( depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
+			}
+		}
+		if( next == NEXT_GEN_EXTRA || next == NEXT_GEN_BOUNCE )
+		{
+			const float2 u01 = pmjSample2d( p.pmj, spp, dim++, stream );
+			d = sampleLambertian( u01.x, u01.y, hitN );
+			kind = ( next == NEXT_GEN_EXTRA ) ? RAY_EXTRA : RAY_BOUNCE;
+		}
+		else if( next == NEXT_FINISH )
+		{
+			p.pathL[path] = make_float4( L.x, L.y, L.z, 0.0f );
+			kind = LANE_IDLE;
+		}
+	}
+
+	// one atomic per warp for the ray counter
+	for( int off = 16; off; off >>= 1 ) rays += __shfl_down_sync( 0xFFFFFFFFu, rays, off );
+	if( lane == 0 && rays ) atomicAdd( p.counters + 1, rays );
+}
+
+// per-pixel reduction in localSpp order, then `frameBuffer += `, voxKernel.cu:763-774
+__global__ void __launch_bounds__( 256 ) accumulateKernel( const float4* __restrict__ pathL, float4* __restrict__ accum, uint32_t nPixels )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if( i >= nPixels ) return;
+	float x = 0.0f, y = 0.0f, z = 0.0f;
+#pragma unroll
+	for( int k = 0; k < PT_SPP; k++ )
+	{
+		const float4 l = __ldcs( pathL + (size_t)i * PT_SPP + k );
+		x += l.x, y += l.y, z += l.z;
+	}
+	float4 a = accum[i];
+	a.x += x, a.y += y, a.z += z, a.w += (float)PT_SPP;
+	accum[i] = a;
+}
+
+// renderResolve, voxKernel.cu:779-795
+__global__ void __launch_bounds__( 256 ) resolveKernel( uchar4* __restrict__ out, const float4* __restrict__ accum, uint32_t n )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if( i >= n ) return;
+	const float4 v = accum[i];
+	const int r = f2i_x86( 255 * powf( v.x / v.w, 1.0f / 2.2f ) + 0.5f );
+	const int g = f2i_x86( 255 * powf( v.y / v.w, 1.0f / 2.2f ) + 0.5f );
+	const int b = f2i_x86( 255 * powf( v.z / v.w, 1.0f / 2.2f ) + 0.5f );
+	out[i] = make_uchar4( (uint8_t)min( r, 255 ), (uint8_t)min( g, 255 ), (uint8_t)min( b, 255 ), 255 );
+}
+} // namespace
+
+// ---- HDRI::load, renderCommon.hpp:214-314: 1 + 6 summed-area tables ----
+namespace
+{
+#define SAT_BLOCK 512 // SAT_BLOCK_SIZE, voxKernel.cu:555
+
+// prefixSumInclusive<double, 512> (voxKernel.cu:526-553): Hillis-Steele over one 512-element tile, double-buffered in
+// shared memory.  The summation ORDER is the reference's (and the oracle's), so the tables are bit-identical.
+__device__ __forceinline__ double scanTile( double prefix, double value, double ( *buf )[SAT_BLOCK], double* sumOut )
+{
+	int cur = 0;
+	buf[0][threadIdx.x] = value;
+	__syncthreads();
+	for( uint32_t offset = 1; offset < SAT_BLOCK; offset <<= 1 )
+	{
+		double x = buf[cur][threadIdx.x];
+		if( offset <= threadIdx.x ) x += buf[cur][threadIdx.x - offset];
+		buf[cur ^ 1][threadIdx.x] = x;
+		cur ^= 1;
+		__syncthreads();
+	}
+	*sumOut = buf[cur][SAT_BLOCK - 1];
+	const double r = buf[cur][threadIdx.x] + prefix;
+	__syncthreads();
+	return r;
+}
+
+// HDRIstoreImportance (voxKernel.cu:485-524) fused into buildSATh (:557-577): one block per row.
+// rowTab: { sr, sY = mix(cos(theta), cos(theta+dTheta), 0.5), sinTheta(sY), - };  colTab: { cos(phi), sin(phi) } of the
+// texel centre -- host-computed so the importance is the same fp32 value the CPU code produces.
+__global__ void __launch_bounds__( SAT_BLOCK ) satRowKernel( const float4* __restrict__ pixels, int w, int h, const float4* __restrict__ rowImp,
+															 const float2* __restrict__ colTab, int cosWeighted, V3 axis, double* __restrict__ sat )
+{
+	__shared__ double buf[2][SAT_BLOCK];
+	const int Y = blockIdx.x;
+	const float4 row = rowImp[Y];
+	double prefix = 0.0;
+	for( int i = 0; i < w; i += SAT_BLOCK )
+	{
+		const int X = i + (int)threadIdx.x;
+		double v = 0.0;
+		if( X < w )
+		{
+			const float4 c = pixels[(size_t)Y * w + X];
+			float wgt = 1.0f;
+			if( cosWeighted )
+			{
+				const float2 cs = colTab[X];
+				const V3 dirCenter = { cs.x * row.z, row.y, cs.y * row.z };
+				wgt = smax( dot( axis, dirCenter ), 0.0f );
+			}
+			v = (double)( ( 0.2126f * c.x + 0.7152f * c.y + 0.0722f * c.z ) * row.x * wgt );
+		}
+		double sum;
+		const double r = scanTile( prefix, v, buf, &sum );
+		prefix += sum;
+		if( X < w ) sat[(size_t)Y * w + X] = r;
+	}
+}
+// buildSATv (:578-598): one block per column
+__global__ void __launch_bounds__( SAT_BLOCK ) satColKernel( int w, int h, double* __restrict__ sat )
+{
+	__shared__ double buf[2][SAT_BLOCK];
+	const int X = blockIdx.x;
+	double prefix = 0.0;
+	for( int i = 0; i < h; i += SAT_BLOCK )
+	{
+		const int Y = i + (int)threadIdx.x;
+		const double v = Y < h ? sat[(size_t)Y * w + X] : 0.0;
+		double sum;
+		const double r = scanTile( prefix, v, buf, &sum );
+		prefix += sum;
+		if( Y < h ) sat[(size_t)Y * w + X] = r;
+	}
+}
+// buildSAT2u32 (:600-608)
+__global__ void __launch_bounds__( 256 ) satToU32Kernel( uint32_t* __restrict__ out, const double* __restrict__ sat, uint32_t n )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const double sum = sat[n - 1];
+	if( i < n )
+	{
+		const double q = sat[i] / ( sum ) * (double)0xFFFFFFFFu;
+		// (uint32_t)double on x86-64 is cvttsd2si to 64 bits + truncation: NaN / out of range -> low word of INT64_MIN = 0
+		out[i] = ( q >= 0.0 && q < 9223372036854775808.0 ) ? (uint32_t)(unsigned long long)q : 0u;
+	}
+}
+} // namespace
+
+// ---- host side: PMJ02 table (PMJSampler::setup, pmjSampler.hpp:114-134; GetPMJ02Samples :14-58) ----
+namespace
+{
+struct HostPCG32 // renderCommon.hpp:86-111
+{
+	uint64_t state, inc;
+	void setup( uint64_t seed, uint64_t stream )
+	{
+		state = 0;
+		inc = stream * 2 + 1;
+		nextU32();
+		state += seed;
+		nextU32();
+	}
+	uint32_t nextU32()
+	{
+		const uint64_t old = state;
+		state = old * 6364136223846793005ULL + inc;
+		const uint32_t xorshifted = (uint32_t)( ( ( old >> 18u ) ^ old ) >> 27u );
+		const uint32_t rot = (uint32_t)( old >> 59u );
+		return ( xorshifted >> rot ) | ( xorshifted << ( ( 0u - rot ) & 31u ) );
+	}
+	float uniformf() // renderCommon.hpp:112-117
+	{
+		const uint32_t bits = ( nextU32() >> 9 ) | 0x3f800000u;
+		float v;
+		memcpy( &v, &bits, 4 );
+		return v - 1.0f;
+	}
+};
+// one (0,2)-sequence: each new sample goes to the unoccupied half of the sub-stratum of an earlier sample, chosen by
+// the xor tables of Helmer's stochastic generation (the table values are the published constants of that method)
+void generatePMJ02( int nSamples, float* samples, HostPCG32& rng )
+{
+	static const uint32_t xors[2][32] = {
+		{ 0x0, 0x0, 0x2, 0x6, 0x6, 0xe, 0x36, 0x4e, 0x16, 0x2e, 0x276, 0x6ce, 0x716, 0xc2e, 0x3076, 0x40ce, 0x116, 0x22e, 0x20676, 0x60ece, 0x61716, 0xe2c2e, 0x367076, 0x4ec0ce, 0x170116, 0x2c022e, 0x2700676, 0x6c00ece, 0x7001716, 0xc002c2e, 0x30007076, 0x4000c0ce },
+		{ 0x0, 0x1, 0x3, 0x3, 0x7, 0x1b, 0x27, 0xb, 0x17, 0x13b, 0x367, 0x38b, 0x617, 0x183b, 0x2067, 0x8b, 0x117, 0x1033b, 0x30767, 0x30b8b, 0x71617, 0x1b383b, 0x276067, 0xb808b, 0x160117, 0x138033b, 0x3600767, 0x3800b8b, 0x6001617, 0x1800383b, 0x20006067, 0x808b } };
+	samples[0] = rng.uniformf();
+	samples[1] = rng.uniformf();
+	for( int logN = 0; ( 1 << logN ) < nSamples; logN++ )
+	{
+		const int prevLen = 1 << logN;
+		const int nStrata = prevLen * 2;
+		const float invStrata = 1.0f / nStrata;
+		for( int i = 0; i < prevLen && ( prevLen + i ) < nSamples; i++ )
+		{
+			const int xs = (int)( samples[( i ^ (int)xors[0][logN] ) * 2] * nStrata ) ^ 1;
+			const int ys = (int)( samples[( i ^ (int)xors[1][logN] ) * 2 + 1] * nStrata ) ^ 1;
+			// the reference passes two uniformFloat() calls as function arguments; with the ABI it is built for here the
+			// second one is evaluated first, which is what the oracle is pinned to
+			const float xi1 = rng.uniformf();
+			const float xi0 = rng.uniformf();
+			samples[( prevLen + i ) * 2 + 0] = ( xi0 + xs ) * invStrata;
+			samples[( prevLen + i ) * 2 + 1] = ( xi1 + ys ) * invStrata;
+		}
+	}
+}
+
+int ptFreeHdri( hako_pt* pt, cudaStream_t s )
+{
+	dfree( pt->hdriPixels, s );
+	dfree( pt->hdriPrimary, s );
+	dfree( pt->sats, s );
+	dfree( pt->rowTab, s );
+	pt->hdriPixels = pt->hdriPrimary = nullptr;
+	pt->sats = nullptr;
+	pt->rowTab = nullptr;
+	pt->hw = pt->hh = pt->wP = pt->hP = 0;
+	return 0;
+}
+} // namespace
+
+#define PT_ARG( cond, msg )              \
+	do                                   \
+	{                                    \
+		if( !( cond ) )                  \
+		{                                \
+			hako::setError( "%s", msg ); \
+			return HAKO_E_INVALID;       \
+		}                                \
+	} while( 0 )
+
+extern "C" {
+
+int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out )
+{
+	PT_ARG( ctx && out, "hako_pt_create: null argument" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	hako_pt* pt = new hako_pt();
+	pt->ctx = ctx;
+	std::vector<float> table( (size_t)2 * PMJ_LENGTH * PMJ_NSEQ );
+	HostPCG32 rng;
+	rng.setup( 0, 2525 ); // pmjSampler.hpp:116-117
+	for( int i = 0; i < PMJ_NSEQ; i++ ) generatePMJ02( PMJ_LENGTH, table.data() + (size_t)2 * PMJ_LENGTH * i, rng );
+	int r = dalloc( ctx, &pt->pmj, table.size(), s );
+	if( r == 0 ) r = dalloc( ctx, &pt->counters, 2, s );
+	if( r == 0 )
+	{
+		cudaError_t e = cudaMemcpyAsync( pt->pmj, table.data(), table.size() * sizeof( float ), cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, 2 * sizeof( unsigned long long ), s );
+		if( e == cudaSuccess ) e = cudaStreamSynchronize( s ); // `table` dies with this scope
+		if( e != cudaSuccess ) r = cudaFail( e, "PMJ upload", __FILE__, __LINE__ );
+	}
+	if( r )
+	{
+		hako_pt_destroy( pt );
+		return r;
+	}
+	*out = pt;
+	return HAKO_OK;
+}
+
+void hako_pt_destroy( hako_pt* pt )
+{
+	if( !pt ) return;
+	cudaSetDevice( pt->ctx->device );
+	cudaStream_t s = nullptr;
+	ptFreeHdri( pt, s );
+	dfree( pt->accum, s );
+	dfree( pt->rgba8, s );
+	dfree( pt->pmj, s );
+	dfree( pt->pathL, s );
+	dfree( pt->counters, s );
+	cudaStreamSynchronize( s );
+	delete pt;
+}
+
+int hako_pt_clear( hako_pt* pt, hako_stream stream )
+{
+	PT_ARG( pt, "hako_pt_clear: null path tracer" );
+	if( !pt->accum )
+	{
+		hako::setError( "hako_pt_clear: no frame buffer (call hako_pt_resize first)" );
+		return HAKO_E_STATE;
+	}
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	HAKO_CUDA( cudaMemsetAsync( pt->accum, 0, (size_t)pt->w * pt->h * sizeof( float4 ), (cudaStream_t)stream ) );
+	return HAKO_OK;
+}
+
+int hako_pt_resize( hako_pt* pt, hako_stream stream, int w, int h )
+{
+	PT_ARG( pt && w > 0 && h > 0, "hako_pt_resize: bad argument" );
+	if( (uint64_t)w * h * PT_SPP > 0xFFFFFFFFull )
+	{
+		hako::setError( "hako_pt_resize: %dx%d x 16 spp exceeds the 32-bit path index", w, h );
+		return HAKO_E_LIMIT;
+	}
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	if( pt->accum && pt->w == w && pt->h == h ) return HAKO_OK;
+	dfree( pt->accum, s );
+	dfree( pt->rgba8, s );
+	pt->accum = nullptr;
+	pt->rgba8 = nullptr;
+	HAKO_TRY( dalloc( pt->ctx, &pt->accum, (uint64_t)w * h, s ) );
+	HAKO_TRY( dalloc( pt->ctx, &pt->rgba8, (uint64_t)w * h, s ) );
+	pt->w = w;
+	pt->h = h;
+	return hako_pt_clear( pt, stream ); // PathTracer.hpp:84-88
+}
+
+int hako_pt_load_hdri( hako_pt* pt, hako_stream stream, const float* rgba, int w, int h, const float* rgbaPrimary, int wP, int hP )
+{
+	PT_ARG( pt && rgba && w > 0 && h > 0, "hako_pt_load_hdri: bad argument" );
+	PT_ARG( !rgbaPrimary || ( wP > 0 && hP > 0 ), "hako_pt_load_hdri: bad primary image size" );
+	hako_ctx* ctx = pt->ctx;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ptFreeHdri( pt, s );
+	const size_t n = (size_t)w * h;
+
+	// theta-only and phi-only terms, with the host's libm exactly as the CPU code evaluates them
+	// (voxKernel.cu:495-518 for the tables, renderCommon.hpp:414-424 for sampling)
+	std::vector<float4> rowTab( h ), rowImp( h );
+	std::vector<float2> colTab( w );
+	const float dTheta = HAKO_PI / (float)h;
+	const float dPhi = 2.0f * HAKO_PI / (float)w;
+	for( uint32_t Y = 0; Y < (uint32_t)h; Y++ )
+	{
+		const float theta = Y * dTheta;
+		const float dH = 2.0f * sinf( dTheta * 0.5f ) * sinf( dTheta * 0.5f + theta );
+		const float sr = dH * dPhi;
+		const float c0 = cosf( theta ), c1 = cosf( theta + dTheta );
+		const float sY = mixf( c0, c1, 0.5f );
+		rowTab[Y] = make_float4( sr, c0, c1, 0.0f );
+		rowImp[Y] = make_float4( sr, sY, sqrtf( smax( 1.0f - sY * sY, 0.0f ) ), 0.0f );
+	}
+	for( int X = 0; X < w; X++ )
+	{
+		const float phi = dPhi * ( (float)X + 0.5f ) + HAKO_PI;
+		colTab[X] = make_float2( cosf( phi ), sinf( phi ) );
+	}
+
+	float4* rowImp_d = nullptr;
+	float2* colTab_d = nullptr;
+	double* satF64 = nullptr;
+	int r = 0;
+	do
+	{
+		if( ( r = dalloc( ctx, &pt->hdriPixels, n, s ) ) ) break;
+		if( ( r = dalloc( ctx, &pt->sats, 7 * n, s ) ) ) break;
+		if( ( r = dalloc( ctx, &pt->rowTab, (uint64_t)h, s ) ) ) break;
+		if( ( r = dalloc( ctx, &rowImp_d, (uint64_t)h, s ) ) ) break;
+		if( ( r = dalloc( ctx, &colTab_d, (uint64_t)w, s ) ) ) break;
+		if( ( r = dalloc( ctx, &satF64, n, s ) ) ) break;
+		cudaError_t e = cudaMemcpyAsync( pt->hdriPixels, rgba, n * sizeof( float4 ), cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( pt->rowTab, rowTab.data(), h * sizeof( float4 ), cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( rowImp_d, rowImp.data(), h * sizeof( float4 ), cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( colTab_d, colTab.data(), w * sizeof( float2 ), cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess && rgbaPrimary )
+		{
+			if( ( r = dalloc( ctx, &pt->hdriPrimary, (uint64_t)wP * hP, s ) ) ) break;
+			e = cudaMemcpyAsync( pt->hdriPrimary, rgbaPrimary, (size_t)wP * hP * sizeof( float4 ), cudaMemcpyHostToDevice, s ); // loadPrimary, :315-325
+		}
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "H2D environment", __FILE__, __LINE__ );
+			break;
+		}
+		const V3 axes[7] = { { 0, 0, 0 }, { 1, 0, 0 }, { -1, 0, 0 }, { 0, 1, 0 }, { 0, -1, 0 }, { 0, 0, 1 }, { 0, 0, -1 } }; // :272-279
+		r = [&]() -> int {
+			for( int k = 0; k < 7; k++ )
+			{
+				HAKO_LAUNCH( ctx, satRowKernel, h, SAT_BLOCK, 0, s, pt->hdriPixels, w, h, rowImp_d, colTab_d, k == 0 ? 0 : 1, axes[k], satF64 );
+				HAKO_LAUNCH( ctx, satColKernel, w, SAT_BLOCK, 0, s, w, h, satF64 );
+				HAKO_LAUNCH( ctx, satToU32Kernel, divUp( n, 256 ), 256, 0, s, pt->sats + n * k, satF64, (uint32_t)n );
+			}
+			return 0;
+		}();
+	} while( 0 );
+	dfree( rowImp_d, s );
+	dfree( colTab_d, s );
+	dfree( satF64, s );
+	if( r == 0 )
+	{
+		cudaError_t e = cudaStreamSynchronize( s ); // renderCommon.hpp:313; also: the host tables above die with this scope
+		if( e != cudaSuccess ) r = cudaFail( e, "environment build", __FILE__, __LINE__ );
+	}
+	if( r )
+	{
+		cudaStreamSynchronize( s );
+		ptFreeHdri( pt, s );
+		return r;
+	}
+	pt->hw = w, pt->hh = h;
+	pt->wP = rgbaPrimary ? wP : w;
+	pt->hP = rgbaPrimary ? hP : h;
+	return HAKO_OK;
+}
+
+int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const hako_camera* cam, int iteration, int y0, int y1, int maxDepth )
+{
+	PT_ARG( pt && o && cam, "hako_pt_step: null argument" );
+	if( !pt->accum )
+	{
+		hako::setError( "hako_pt_step: no frame buffer (call hako_pt_resize first)" );
+		return HAKO_E_STATE;
+	}
+	PT_ARG( 0 <= y0 && y0 <= y1 && y1 <= pt->h, "hako_pt_step: row range outside the frame" );
+	PT_ARG( iteration >= 0 && maxDepth >= 0, "hako_pt_step: negative iteration / maxDepth" );
+	if( o->numberOfVoxels && !o->attrs )
+	{
+		hako::setError( "hako_pt_step: the octree has no voxel attributes (imported without attrs)" );
+		return HAKO_E_STATE;
+	}
+	if( y0 == y1 ) return HAKO_OK;
+	hako_ctx* ctx = pt->ctx;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+
+	const uint32_t nPixels = (uint32_t)( y1 - y0 ) * (uint32_t)pt->w;
+	const uint64_t nPaths = (uint64_t)nPixels * PT_SPP;
+	if( pt->pathCap < nPaths )
+	{
+		dfree( pt->pathL, s );
+		pt->pathL = nullptr;
+		pt->pathCap = 0;
+		HAKO_TRY( dalloc( ctx, &pt->pathL, nPaths, s ) );
+		pt->pathCap = nPaths;
+	}
+	HAKO_CUDA( cudaMemsetAsync( pt->counters, 0, sizeof( unsigned long long ), s ) ); // the work counter; [1] keeps counting rays
+
+	PtParams p;
+	p.tree = o->view();
+	p.env = PtEnv{ pt->hdriPixels, pt->hdriPrimary, pt->sats, pt->rowTab, pt->hw, pt->hh, pt->wP, pt->hP, pt->hdriPixels ? pt->hdriScale : 0.0f };
+	p.cam = *cam;
+	p.pmj = pt->pmj;
+	p.pathL = pt->pathL;
+	p.counters = pt->counters;
+	p.w = pt->w, p.h = pt->h, p.y0 = y0;
+	p.nPaths = (uint32_t)nPaths;
+	p.iteration = (uint32_t)iteration;
+	p.maxDepth = maxDepth;
+
+	// persistent grid: as many CTAs as are co-resident on the chip
+	static int ctasPerSm = 0;
+	if( ctasPerSm == 0 )
+	{
+		HAKO_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &ctasPerSm, pathTraceKernel, PT_BLOCK, 0 ) );
+		if( ctasPerSm < 1 ) ctasPerSm = 1;
+	}
+	const uint32_t grid = (uint32_t)std::min<uint64_t>( (uint64_t)ctasPerSm * ctx->smCount, ( nPaths + PT_BLOCK - 1 ) / PT_BLOCK );
+	HAKO_LAUNCH( ctx, pathTraceKernel, grid, PT_BLOCK, 0, s, p );
+	HAKO_LAUNCH( ctx, accumulateKernel, divUp( nPixels, 256 ), 256, 0, s, pt->pathL, pt->accum + (size_t)y0 * pt->w, nPixels );
+	return HAKO_OK;
+}
+
+int hako_pt_resolve( hako_pt* pt, hako_stream stream )
+{
+	PT_ARG( pt, "hako_pt_resolve: null path tracer" );
+	if( !pt->accum )
+	{
+		hako::setError( "hako_pt_resolve: no frame buffer" );
+		return HAKO_E_STATE;
+	}
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	const uint32_t n = (uint32_t)pt->w * pt->h;
+	HAKO_LAUNCH( pt->ctx, resolveKernel, divUp( n, 256 ), 256, 0, (cudaStream_t)stream, pt->rgba8, pt->accum, n );
+	return HAKO_OK;
+}
+
+int hako_pt_read_rgba8( hako_pt* pt, hako_stream stream, uint8_t* rgba )
+{
+	PT_ARG( pt && rgba, "hako_pt_read_rgba8: null argument" );
+	HAKO_TRY( hako_pt_resolve( pt, stream ) ); // toImageAsync = resolve + D2H, PathTracer.hpp:128-137
+	HAKO_CUDA( cudaMemcpyAsync( rgba, pt->rgba8, (size_t)pt->w * pt->h * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	return HAKO_OK;
+}
+
+int hako_pt_read_accum( hako_pt* pt, hako_stream stream, float* rgbw )
+{
+	PT_ARG( pt && rgbw, "hako_pt_read_accum: null argument" );
+	if( !pt->accum )
+	{
+		hako::setError( "hako_pt_read_accum: no frame buffer" );
+		return HAKO_E_STATE;
+	}
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	HAKO_CUDA( cudaMemcpyAsync( rgbw, pt->accum, (size_t)pt->w * pt->h * sizeof( float4 ), cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	return HAKO_OK;
+}
+
+int hako_pt_accum_device( hako_pt* pt, void** accum_d, uint64_t* bytes )
+{
+	PT_ARG( pt && accum_d && bytes, "hako_pt_accum_device: null argument" );
+	*accum_d = pt->accum;
+	*bytes = (uint64_t)pt->w * pt->h * sizeof( float4 );
+	return HAKO_OK;
+}
+
+int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, int reset )
+{
+	PT_ARG( pt && raysTraced, "hako_pt_ray_count: null argument" );
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	unsigned long long v = 0;
+	HAKO_CUDA( cudaMemcpyAsync( &v, pt->counters + 1, sizeof( v ), cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+	if( reset ) HAKO_CUDA( cudaMemsetAsync( pt->counters + 1, 0, sizeof( v ), (cudaStream_t)stream ) );
+	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	*raysTraced = v;
+	return HAKO_OK;
+}
+
+int hako_pt_pmj_table( hako_pt* pt, hako_stream stream, float* samples )
+{
+	PT_ARG( pt && samples, "hako_pt_pmj_table: null argument" );
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	HAKO_CUDA( cudaMemcpyAsync( samples, pt->pmj, sizeof( float ) * 2 * PMJ_LENGTH * PMJ_NSEQ, cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	return HAKO_OK;
+}
+
+int hako_pt_hdri_sats( hako_pt* pt, hako_stream stream, uint32_t* sats )
+{
+	PT_ARG( pt && sats, "hako_pt_hdri_sats: null argument" );
+	if( !pt->sats )
+	{
+		hako::setError( "hako_pt_hdri_sats: no environment loaded" );
+		return HAKO_E_STATE;
+	}
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	HAKO_CUDA( cudaMemcpyAsync( sats, pt->sats, sizeof( uint32_t ) * 7 * pt->hw * pt->hh, cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	return HAKO_OK;
+}
+}

@@ -22,8 +22,9 @@ namespace hako
 __device__ __forceinline__ float levelScale( uint32_t level ) { return __uint_as_float( ( 127u - level ) << 23 ); }
 
 // returns true on a hit (and then writes t / nMajor / vIndex); a miss leaves the outputs untouched (voxRT.cpp:313-325)
-template <bool SHADOW>
-__device__ __forceinline__ bool octreeTraverse( const OctreeView& v, V3 ro, V3 rd, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
+// `shadow` may be a compile-time constant (the template wrapper below) or a per-lane runtime value (the path tracer
+// traces closest-hit and shadow rays of different lanes through ONE call site so the warp stays converged).
+__device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, V3 rd, const bool shadow, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
 {
 	if( v.numberOfNodes == 0 ) return false;
 
@@ -128,7 +129,7 @@ __device__ __forceinline__ bool octreeTraverse( const OctreeView& v, V3 ro, V3 r
 					c_tz1 = z1;
 					c_level++;
 					c_childMask = 0xFFu;
-					if( !SHADOW ) c_skipped += slot.y; // :388-391
+					if( !shadow ) c_skipped += slot.y; // :388-391
 					descended = true;
 					break;
 				}
@@ -155,6 +156,12 @@ __device__ __forceinline__ bool octreeTraverse( const OctreeView& v, V3 ro, V3 r
 		c_level = b.x >> 8;
 		c_skipped = b.y;
 	}
+}
+
+template <bool SHADOW>
+__device__ __forceinline__ bool octreeTraverse( const OctreeView& v, V3 ro, V3 rd, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
+{
+	return octreeTraverseImpl( v, ro, rd, SHADOW, tOut, nMajorOut, vIndexOut );
 }
 
 // getHitN, voxCommon.hpp:564-577

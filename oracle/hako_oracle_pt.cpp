@@ -305,6 +305,7 @@ struct Hdri
 	// renderCommon.hpp:354-365 (device-only in the reference)
 	F3 sampleNearest( F3 d, bool isPrimary ) const
 	{
+		if( !pixels ) return F3{ 0.0f, 0.0f, 0.0f }; // no environment loaded (the reference would dereference null)
 		int ww = isPrimary ? wP : w;
 		int hh = isPrimary ? hP : h;
 		float phi = atan2f( d.z, d.x ) + PI;
