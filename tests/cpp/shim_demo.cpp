@@ -1,0 +1,131 @@
+// shim_demo.cpp -- a voxRTGPU / voxPTGPU-style caller written against the drop-in C++ shims (include/*.hpp):
+// the same calls, in the same order, as voxRTGPU.cpp:104-209 and voxPTGPU.cpp:88-193, headless (no window).
+// Built and linked by tests/test_abi.py (CPU) and executed by tests/test_gpu_shim.py (GPU).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "IntersectorOctreeGPU.hpp"
+#include "PathTracer.hpp"
+
+struct vec3 // stand-in for glm::vec3
+{
+	float x, y, z;
+};
+
+// a small closed shape: an octahedron with a bright top, plus a ground quad
+static void makeScene( std::vector<vec3>& v, std::vector<vec3>& c, std::vector<vec3>& e )
+{
+	const vec3 P[6] = { { 1, 0, 0 }, { -1, 0, 0 }, { 0, 1, 0 }, { 0, -1, 0 }, { 0, 0, 1 }, { 0, 0, -1 } };
+	const int F[8][3] = { { 0, 2, 4 }, { 4, 2, 1 }, { 1, 2, 5 }, { 5, 2, 0 }, { 4, 3, 0 }, { 1, 3, 4 }, { 5, 3, 1 }, { 0, 3, 5 } };
+	for( int f = 0; f < 8; f++ )
+		for( int k = 0; k < 3; k++ )
+		{
+			const vec3 p = P[F[f][k]];
+			v.push_back( p );
+			c.push_back( { 0.5f + 0.5f * p.x, 0.5f + 0.5f * p.y, 0.5f + 0.5f * p.z } );
+			e.push_back( p.y > 0.5f ? vec3{ 0.9f, 0.8f, 0.6f } : vec3{ 0, 0, 0 } );
+		}
+	const vec3 Q[4] = { { -1.5f, -1.0f, -1.5f }, { 1.5f, -1.0f, -1.5f }, { 1.5f, -1.0f, 1.5f }, { -1.5f, -1.0f, 1.5f } };
+	const int G[2][3] = { { 0, 1, 2 }, { 0, 2, 3 } };
+	for( int f = 0; f < 2; f++ )
+		for( int k = 0; k < 3; k++ )
+		{
+			v.push_back( Q[G[f][k]] );
+			c.push_back( { 0.7f, 0.7f, 0.7f } );
+			e.push_back( { 0, 0, 0 } );
+		}
+}
+
+int main( int argc, char** argv )
+{
+	const int gridRes = 128, W = 256, H = 192;
+	try
+	{
+		hako::Context ctx( 0 );
+		std::vector<vec3> vertices, vcolors, vemissions;
+		makeScene( vertices, vcolors, vemissions );
+		const vec3 origin = { -1.5f, -1.0f, -1.5f };
+		const float dps = 3.0f / gridRes;
+
+		// ---- voxRTGPU: build + primary rays ----
+		IntersectorOctreeGPU intersector( &ctx );
+		intersector.build( vertices, vcolors, vemissions, (Shader*)nullptr, nullptr, origin, dps, gridRes );
+		const float eye[3] = { 4, 4, 4 }, center[3] = { 0, 0, 0 }, up[3] = { 0, 1, 0 };
+		hako_camera cam;
+		hako::check( hako_camera_lookat( eye, center, up, 45.0f * 3.14159265f / 180.0f, W, H, 0.01f, 1000.0f, 6.0f, 0.02f, &cam ) );
+		std::vector<uint8_t> image( (size_t)W * H * 4 );
+		std::vector<uint32_t> ids( (size_t)W * H );
+		intersector.render( nullptr, cam, W, H, true, image.data(), ids.data() );
+		size_t hits = 0;
+		for( uint32_t id : ids ) hits += id != 0xFFFFFFFFu;
+		printf( "voxels %u nodes %u hits %zu hasEmission %d\n", intersector.m_numberOfVoxels, intersector.m_numberOfNodes, hits, (int)intersector.hasEmission() );
+
+		// ---- IntersectorOctree (CPU class surface): rebuild from the sorted unique Morton list, cast one ray ----
+		std::vector<uint64_t> mortons;
+		std::vector<hako_node68> nodes;
+		intersector.download( &nodes, &mortons );
+		IntersectorOctree cpuStyle( &ctx );
+		cpuStyle.buildDAGReference( mortons, origin, dps, gridRes );
+		const float ro[3] = { 4, 4, 4 }, rd[3] = { -1, -1, -1 };
+		float t = FLT_MAX;
+		int nMajor = -1;
+		uint32_t vIndex = 0xFFFFFFFFu;
+		cpuStyle.intersect( ro, rd, &t, &nMajor, &vIndex );
+		printf( "dag nodes %u (gpu build %u) centre ray t %.6f nMajor %d vIndex %u\n", cpuStyle.m_numberOfNodes, (unsigned)nodes.size(), t, nMajor, vIndex );
+		if( cpuStyle.m_numberOfNodes != nodes.size() || t == FLT_MAX ) return 2;
+
+		// ---- voxPTGPU: setup, environment, scene, 4 steps (= 64 spp), resolve ----
+		PathTracer pt( &ctx );
+		pt.setup( nullptr );
+		pt.resizeFrameBufferIfNeeded( nullptr, W, H );
+		const int ew = 64, eh = 32;
+		std::vector<float> env( (size_t)ew * eh * 4 );
+		for( int y = 0; y < eh; y++ )
+			for( int x = 0; x < ew; x++ )
+			{
+				float* p = &env[( (size_t)y * ew + x ) * 4];
+				const float sky = 0.2f + 0.8f * ( 1.0f - (float)y / eh );
+				p[0] = 0.6f * sky, p[1] = 0.8f * sky, p[2] = sky, p[3] = 1.0f;
+			}
+		pt.loadHDRI( nullptr, env.data(), ew, eh );
+		pt.updateScene( vertices, vcolors, vemissions, nullptr, origin, dps, gridRes );
+		for( int i = 0; i < 4; i++ ) pt.step( nullptr, cam );
+		pt.toImageAsync( nullptr, image.data() );
+		std::vector<float> acc( (size_t)W * H * 4 );
+		pt.readAccumulators( nullptr, acc.data() );
+		double sum = 0;
+		for( size_t i = 0; i < (size_t)W * H; i++ ) sum += acc[i * 4] + acc[i * 4 + 1] + acc[i * 4 + 2];
+		printf( "steps %d spp %.0f mean radiance %.6f\n", pt.getSteps(), acc[3], sum / ( 3.0 * W * H * acc[3] ) );
+		if( acc[3] != 64.0f || !( sum > 0 ) ) return 3;
+		if( argc > 1 )
+		{
+			FILE* f = fopen( argv[1], "wb" );
+			if( f )
+			{
+				fprintf( f, "P6\n%d %d\n255\n", W, H );
+				for( size_t i = 0; i < (size_t)W * H; i++ ) fwrite( &image[i * 4], 1, 3, f );
+				fclose( f );
+			}
+		}
+		// error behaviour: gridRes must be a power of two (IntersectorOctreeGPU.hpp:48-51 abort()) -> hako::Error here
+		try
+		{
+			intersector.build( vertices, vcolors, vemissions, (Shader*)nullptr, nullptr, origin, dps, 100 );
+			return 4;
+		}
+		catch( const hako::Error& err )
+		{
+			printf( "expected error: %s\n", err.what() );
+		}
+		pt.cleanUp();
+	}
+	catch( const hako::Error& err )
+	{
+		fprintf( stderr, "hako error %d: %s\n", err.code, err.what() );
+		return 1;
+	}
+	printf( "shim demo ok\n" );
+	return 0;
+}

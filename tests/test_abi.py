@@ -74,3 +74,23 @@ def test_camera_matches_oracle(oracle):
     cam = hk.camera_from_matrices(view, proj, 1.5, 0.25)
     assert tuple(cam.o) == (-1.0, -2.0, -3.0) and tuple(cam.front) == (-0.0, -0.0, -1.0) and cam.tanHthetaY == 0.5
     assert cam.focus == 1.5 and cam.lensR == 0.25
+
+
+def build_shim_demo(out_dir):
+    """compile tests/cpp/shim_demo.cpp against include/*.hpp and link it with libhako_b200.so"""
+    exe = os.path.join(str(out_dir), "shim_demo")
+    pkg = os.path.join(ROOT, "massivevoxelraytracing_b200")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cpp", "shim_demo.cpp"),
+                    "-o", exe, "-L" + pkg, "-lhako_b200", "-Wl,-rpath," + pkg], check=True)
+    return exe
+
+
+def test_cpp_shims_compile_and_fail_loudly_without_gpu(tmp_path):
+    """the C++ drop-in headers (IntersectorOctreeGPU.hpp / PathTracer.hpp) build with plain g++; with no device the
+    demo exits through hako::Error (no CPU fallback)"""
+    import torch
+    exe = build_shim_demo(tmp_path)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present (the demo itself runs in tests/test_gpu_shim.py)")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CPU fallback" in r.stderr
