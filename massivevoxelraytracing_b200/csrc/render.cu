@@ -92,9 +92,10 @@ __global__ void __launch_bounds__( 256 ) renderPrimaryKernel( OctreeView v, hako
 	const bool hit = octreeTraverse<false>( v, ro, rd, &t, &nMajor, &vIndex );
 
 	const uint64_t p = (uint64_t)( y - y0 ) * w + x;
-	if( tOut ) tOut[p] = t;
-	if( nMajorOut ) nMajorOut[p] = nMajor;
-	if( vIndexOut ) vIndexOut[p] = vIndex;
+	// streaming stores: the outputs are write-once and must not evict octree nodes from L2
+	if( tOut ) __stcs( tOut + p, t );
+	if( nMajorOut ) __stcs( nMajorOut + p, nMajor );
+	if( vIndexOut ) __stcs( vIndexOut + p, vIndex );
 	if( rgba )
 	{
 		uchar4 c = make_uchar4( 0, 0, 0, 255 );
@@ -113,7 +114,7 @@ __global__ void __launch_bounds__( 256 ) renderPrimaryKernel( OctreeView v, hako
 				c = make_uchar4( (uint8_t)( 255 * col.x + 0.5f ), (uint8_t)( 255 * col.y + 0.5f ), (uint8_t)( 255 * col.z + 0.5f ), 255 );
 			}
 		}
-		rgba[p] = c;
+		__stcs( rgba + p, c );
 	}
 }
 int launchRenderPrimary( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, const hako_camera& cam, int w, int h, int y0, int y1,

@@ -71,6 +71,10 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 	uint32_t c_childMask = 0xFFu; // "not chosen yet" (reference: 0xFFFFFFFF)
 	uint32_t c_skipped = 0;
 
+	// One uniform step per iteration (instead of the reference's visit loop + inner sibling loop + pop): every lane of a
+	// warp executes the same straight-line body whatever its depth in the tree, so the warp does not split into the
+	// "computing t0 / walking siblings / popping" groups the nested form produces.  Each value below is the same fp32
+	// expression of ( t1, dt, level, childMask ) as in voxCommon.hpp:317-411, so recomputing it per step is bit-neutral.
 	for( ;; )
 	{
 		const float scale = levelScale( c_level );
@@ -80,7 +84,7 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 		const float tz0 = c_tz1 - dtz * scale;
 		const float lmax = max3( tx0, ty0, tz0 );
 
-		bool descended = false;
+		bool pop = false;
 		if( c_node == 0xFFFFFFFFu )
 		{
 			// :322-336 leaf voxel
@@ -91,6 +95,7 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 				*vIndexOut = c_skipped;
 				return true;
 			}
+			pop = true;
 		}
 		else
 		{
@@ -98,63 +103,51 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 			const float txM = 0.5f * ( tx0 + c_tx1 );
 			const float tyM = 0.5f * ( ty0 + c_ty1 );
 			const float tzM = 0.5f * ( tz0 + c_tz1 );
-			if( c_childMask == 0xFFu )
+			if( c_childMask == 0xFFu ) c_childMask = ( txM < lmax ? 1u : 0u ) | ( tyM < lmax ? 2u : 0u ) | ( tzM < lmax ? 4u : 0u );
+			const float x1 = ( c_childMask & 1u ) ? c_tx1 : txM;
+			const float y1 = ( c_childMask & 2u ) ? c_ty1 : tyM;
+			const float z1 = ( c_childMask & 4u ) ? c_tz1 : tzM;
+			// :365-411 the child the ray is in now; the exit plane decides the next sibling
+			const float umin = min3( x1, y1, z1 );
+			const uint32_t mv = ( umin == x1 ) ? 1u : ( ( umin == y1 ) ? 2u : 4u );
+			const bool hasNext = ( c_childMask & mv ) == 0;
+			const uint32_t ci = c_childMask ^ vMask;
+			c_childMask |= mv;
+			if( ( ( c_node >> ( 24 + ci ) ) & 1u ) && !( umin < 0.0f ) )
 			{
-				c_childMask = ( txM < lmax ? 1u : 0u ) | ( tyM < lmax ? 2u : 0u ) | ( tzM < lmax ? 4u : 0u );
-			}
-			const uint32_t mask = c_node >> 24;
-			float x1 = ( c_childMask & 1u ) ? c_tx1 : txM;
-			float y1 = ( c_childMask & 2u ) ? c_ty1 : tyM;
-			float z1 = ( c_childMask & 4u ) ? c_tz1 : tzM;
-			// :365-411 walk the (at most 4) children the ray crosses inside this node
-			for( ;; )
-			{
-				const float umin = min3( x1, y1, z1 );
-				const uint32_t mv = ( umin == x1 ) ? 1u : ( ( umin == y1 ) ? 2u : 4u );
-				const bool hasNext = ( c_childMask & mv ) == 0;
-				const uint32_t ci = c_childMask ^ vMask;
-				c_childMask |= mv;
-				if( ( ( mask >> ci ) & 1u ) && !( umin < 0.0f ) )
+				if( hasNext )
 				{
-					if( hasNext )
-					{
-						stackA[sp] = make_uint4( c_node, __float_as_uint( c_tx1 ), __float_as_uint( c_ty1 ), __float_as_uint( c_tz1 ) );
-						stackB[sp] = make_uint2( c_childMask | ( c_level << 8 ), c_skipped );
-						sp++;
-					}
-					const uint2 slot = ldg_u2( &v.nodes[c_node & 0xFFFFFFu].slot[ci] );
-					c_node = slot.x;
-					c_tx1 = x1;
-					c_ty1 = y1;
-					c_tz1 = z1;
-					c_level++;
-					c_childMask = 0xFFu;
-					if( !shadow ) c_skipped += slot.y; // :388-391
-					descended = true;
-					break;
+					stackA[sp] = make_uint4( c_node, __float_as_uint( c_tx1 ), __float_as_uint( c_ty1 ), __float_as_uint( c_tz1 ) );
+					stackB[sp] = make_uint2( c_childMask | ( c_level << 8 ), c_skipped );
+					sp++;
 				}
-				if( !hasNext ) break;
-				if( mv == 1u )
-					x1 = c_tx1;
-				else if( mv == 2u )
-					y1 = c_ty1;
-				else
-					z1 = c_tz1;
+				const uint2 slot = ldg_u2( &v.nodes[c_node & 0xFFFFFFu].slot[ci] );
+				c_node = slot.x;
+				c_tx1 = x1;
+				c_ty1 = y1;
+				c_tz1 = z1;
+				c_level++;
+				c_childMask = 0xFFu;
+				if( !shadow ) c_skipped += slot.y; // :388-391
 			}
+			else
+				pop = !hasNext; // otherwise stay in this node: the next step looks at the sibling behind plane `mv`
 		}
-		if( descended ) continue;
-		// :414-422 pop
-		if( sp == 0 ) return false;
-		sp--;
-		const uint4 a = stackA[sp];
-		const uint2 b = stackB[sp];
-		c_node = a.x;
-		c_tx1 = __uint_as_float( a.y );
-		c_ty1 = __uint_as_float( a.z );
-		c_tz1 = __uint_as_float( a.w );
-		c_childMask = b.x & 0xFFu;
-		c_level = b.x >> 8;
-		c_skipped = b.y;
+		if( pop )
+		{
+			// :414-422
+			if( sp == 0 ) return false;
+			sp--;
+			const uint4 a = stackA[sp];
+			const uint2 b = stackB[sp];
+			c_node = a.x;
+			c_tx1 = __uint_as_float( a.y );
+			c_ty1 = __uint_as_float( a.z );
+			c_tz1 = __uint_as_float( a.w );
+			c_childMask = b.x & 0xFFu;
+			c_level = b.x >> 8;
+			c_skipped = b.y;
+		}
 	}
 }
 
