@@ -295,6 +295,10 @@ def run_ours(args):
     sampler.join(timeout=2)
     hits_view0 = int((t_d[0] != 3.402823466e38).sum().item())
 
+    # ---- path tracing leg (BASELINE config[2] shape): same octree, 1920x1080, 4 bounces, procedural 2k environment;
+    # samples-per-pixel sharded over ranks (rank r renders iterations r, r+G, ...), ONE ncclReduce of the accumulators ----
+    pt_res = run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -360,11 +364,90 @@ def run_ours(args):
             "config": cfg, "clocks": sampler.summary(),
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 60 * VIEWS, "d2h_bytes_per_step": 12 * nrays_view * VIEWS,
                     "ms_per_step": e2e_total / args.steps, "call": "hako_render_primary (host buffers, pinned), one call per view"},
-            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "build": build, "hits_view0": hits_view0,
+            "gpu_launches": int(launches), "roofline": roofline, "path_tracing": pt_res, "cpu_baseline": cpu, "build": build, "hits_view0": hits_view0,
             "parity_vs_cpu_reference_view0": parity, "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+PT_STEPS = 4            # PathTracer::step calls per rank inside the timed region (16 spp each)
+PT_DEPTH = 4            # BASELINE config[2]: 4 bounces (the reference's literal is 8, voxKernel.cu:691)
+
+
+def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
+    import torch
+    import torch.distributed as dist
+    from scenes import procedural_hdri
+    pt = hk.PathTracer(ctx).setup()
+    own = pt.m_intersectorOctreeGPU
+    pt.m_intersectorOctreeGPU = octree          # share the resident octree (no rebuild)
+    pt.maxDepth = PT_DEPTH
+    pt.resizeFrameBufferIfNeeded(None, W, H)
+    pt.loadHDRI(None, procedural_hdri(2048, 1024))
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR=0.0)
+    ptr, nbytes = pt.accum_device()
+    acc = hdist.as_tensor(ptr, nbytes, dev).view(torch.float32)
+    stream = torch.cuda.current_stream()
+    iters = hdist.spp_shard(PT_STEPS * world, rank, world)
+
+    def frame():
+        pt.clearFrameBuffer()
+        for it in iters:
+            pt.step(None, cam, iteration=it)
+        if world > 1:
+            hdist.reduce_accum(acc, 0)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    frame()
+    sync_all()
+    pt.ray_count(reset=True)
+    l0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 3
+    e0.record(stream)
+    for _ in range(reps):
+        frame()
+    e1.record(stream)
+    sync_all()
+    ms = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+    rays = torch.tensor([pt.ray_count() / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(rays, op=dist.ReduceOp.SUM)
+    launches = (ctx.launch_count - l0) // reps
+    # e2e: the PathTracer calls a voxPTGPU frame makes (clear, steps, reduce, toImageAsync = resolve + D2H of the RGBA8 frame)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        frame()
+        if rank == 0:
+            img = pt.toImageAsync()
+    sync_all()
+    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    res = None
+    if rank == 0:
+        spp = 16 * PT_STEPS * world
+        a = pt.accumulators()
+        ok = bool((a[..., 3] == spp).all())
+        paths = W * H * spp
+        res = {"workload": "stand-in dragon %d^3, %dx%d, maxDepth %d, procedural 2048x1024 environment (monks_forest_2k.hdr is missing), %d spp per frame = %d steps x 16 spp per GPU"
+                           % (GRID, W, H, PT_DEPTH, spp, PT_STEPS),
+               "ms_per_frame": float(ms.item()), "ms_per_spp_per_gpu": float(ms.item()) / (16 * PT_STEPS), "mpaths_per_s": paths / (float(ms.item()) * 1e-3) / 1e6,
+               "mrays_per_s": float(rays.item()) / (float(ms.item()) * 1e-3) / 1e6, "rays_per_path": float(rays.item()) / paths,
+               "e2e_ms_per_frame": float(e2e_ms.item()), "e2e_mpaths_per_s": paths / (float(e2e_ms.item()) * 1e-3) / 1e6, "d2h_bytes_per_frame": W * H * 4,
+               "launches_per_frame_per_gpu": int(launches), "spp_count_ok": ok, "mean_radiance": float(a[..., :3].mean() / spp),
+               "collective": "ncclReduce(sum) of %d MB float4 accumulators" % (W * H * 16 // 1000000) if world > 1 else "none (1 GPU)",
+               "published_reference": "12.5 ms/spp at 1920x1080, 8 bounces, 4096^3 scene, RX 7900 XTX (seminar slide 67); different scene and hardware"}
+    pt.m_intersectorOctreeGPU = own
+    pt.cleanUp()
+    return res
 
 
 def load_profile_value(key, default):

@@ -64,6 +64,9 @@ int hako_ctx_create( int device, hako_ctx** out )
 	HAKO_CUDA( cudaMemPoolSetAttribute( c->pool, cudaMemPoolAttrReleaseThreshold, &keep ) );
 	for( int i = 0; i < 8; i++ ) HAKO_CUDA( cudaEventCreate( &c->ev[i] ) );
 	HAKO_CUDA( cudaMallocHost( (void**)&c->pinned, 64 * sizeof( uint64_t ) ) );
+	HAKO_CUDA( cudaStreamCreateWithFlags( &c->copyStream, cudaStreamNonBlocking ) );
+	for( int i = 0; i < 2; i++ ) HAKO_CUDA( cudaStreamCreateWithFlags( &c->bandStream[i], cudaStreamNonBlocking ) );
+	for( int i = 0; i < 17; i++ ) HAKO_CUDA( cudaEventCreateWithFlags( &c->bandEv[i], cudaEventDisableTiming ) );
 	*out = c;
 	return HAKO_OK;
 }
@@ -76,6 +79,11 @@ void hako_ctx_destroy( hako_ctx* c )
 	for( int i = 0; i < 8; i++ )
 		if( c->ev[i] ) cudaEventDestroy( c->ev[i] );
 	if( c->pinned ) cudaFreeHost( c->pinned );
+	for( int i = 0; i < 17; i++ )
+		if( c->bandEv[i] ) cudaEventDestroy( c->bandEv[i] );
+	if( c->copyStream ) cudaStreamDestroy( c->copyStream );
+	for( int i = 0; i < 2; i++ )
+		if( c->bandStream[i] ) cudaStreamDestroy( c->bandStream[i] );
 	delete c;
 }
 

@@ -17,6 +17,10 @@ struct hako_ctx
 	cudaEvent_t ev[8] = {};
 	// pinned staging word(s) for the few device->host counter reads a build needs
 	uint64_t* pinned = nullptr; // 64 x u64
+	// device->host pipeline of the host-buffer entry points: band k is copied on copyStream while band k+1 is traced
+	cudaStream_t copyStream = nullptr;
+	cudaStream_t bandStream[2] = {}; // band kernels alternate between these so that one band's tail overlaps the next band
+	cudaEvent_t bandEv[17] = {};
 };
 
 struct hako_octree

@@ -1,5 +1,6 @@
 // octree_api.cu -- C ABI for the octree object: import / export / info / intersect / primary rays.
 // (IntersectorOctreeGPU.hpp:21-275 and IntersectorOctree.hpp:214-266 are the reference surfaces.)
+#include <cstdlib>
 #include <cstring>
 
 #include "internal.cuh"
@@ -260,6 +261,7 @@ int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_ca
 {
 	CHECK_ARG( o && cam, "hako_render_primary: null argument" );
 	CHECK_ARG( w > 0 && h > 0 && 0 <= y0 && y0 <= y1 && y1 <= h, "hako_render_primary: bad image / row range" );
+	CHECK_ARG( !( showVertexColor && rgba && !o->attrs ), "hako_render_primary: showVertexColor needs voxel attributes" );
 	hako_ctx* ctx = o->ctx;
 	cudaStream_t s = (cudaStream_t)stream;
 	HAKO_CUDA( cudaSetDevice( ctx->device ) );
@@ -276,13 +278,39 @@ int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_ca
 		if( t && ( r = dalloc( ctx, &t_d, n, s ) ) ) break;
 		if( nMajor && ( r = dalloc( ctx, &nm_d, n, s ) ) ) break;
 		if( vIndex && ( r = dalloc( ctx, &vi_d, n, s ) ) ) break;
-		if( ( r = hako_render_primary_device( o, stream, cam, w, h, y0, y1, showVertexColor, rgba_d, t_d, nm_d, vi_d ) ) ) break;
-		cudaError_t e;
-		if( rgba ) CP( rgba, rgba_d, n * 4, cudaMemcpyDeviceToHost );
-		if( t ) CP( t, t_d, n * 4, cudaMemcpyDeviceToHost );
-		if( nMajor ) CP( nMajor, nm_d, n * 4, cudaMemcpyDeviceToHost );
-		if( vIndex ) CP( vIndex, vi_d, n * 4, cudaMemcpyDeviceToHost );
-		if( ( e = cudaStreamSynchronize( s ) ) != cudaSuccess ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+		// Row bands: band k is copied to the host on ctx->copyStream while later bands are being traced, so the call costs
+		// about max( trace, D2H ) instead of their sum.  Band kernels alternate between two internal streams: a band is a
+		// single wave of CTAs whose tail would otherwise serialise with the next band.
+		static const int bandsEnv = getenv( "HAKO_BANDS" ) ? atoi( getenv( "HAKO_BANDS" ) ) : 0;
+		int bands = bandsEnv > 0 ? bandsEnv : ( y1 - y0 ) / 256;
+		bands = bands < 1 ? 1 : ( bands > 16 ? 16 : bands );
+		const int rowsPerBand = ( ( y1 - y0 + bands - 1 ) / bands + 15 ) / 16 * 16; // whole 16-row tiles
+		cudaError_t e = cudaEventRecord( ctx->bandEv[16], s );						 // the device buffers were allocated on `s`
+		for( int i = 0; i < 2 && e == cudaSuccess; i++ ) e = cudaStreamWaitEvent( ctx->bandStream[i], ctx->bandEv[16], 0 );
+		int k = 0;
+		for( int b0 = y0; b0 < y1 && r == 0 && e == cudaSuccess; b0 += rowsPerBand, k++ )
+		{
+			const int b1 = b0 + rowsPerBand < y1 ? b0 + rowsPerBand : y1;
+			const uint64_t off = (uint64_t)( b0 - y0 ) * w, cnt = (uint64_t)( b1 - b0 ) * w;
+			cudaStream_t bs = ctx->bandStream[k & 1];
+			if( ( r = launchRenderPrimary( ctx, bs, o->view(), *cam, w, h, b0, b1, showVertexColor, rgba_d ? rgba_d + off * 4 : nullptr, t_d ? t_d + off : nullptr,
+										   nm_d ? nm_d + off : nullptr, vi_d ? vi_d + off : nullptr ) ) )
+				break;
+			if( ( e = cudaEventRecord( ctx->bandEv[k], bs ) ) != cudaSuccess ) break;
+			if( ( e = cudaStreamWaitEvent( ctx->copyStream, ctx->bandEv[k], 0 ) ) != cudaSuccess ) break;
+			if( rgba && ( e = cudaMemcpyAsync( rgba + off * 4, rgba_d + off * 4, cnt * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( t && ( e = cudaMemcpyAsync( t + off, t_d + off, cnt * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( nMajor && ( e = cudaMemcpyAsync( nMajor + off, nm_d + off, cnt * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( vIndex && ( e = cudaMemcpyAsync( vIndex + off, vi_d + off, cnt * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+		}
+		// every band kernel is ordered before its copy, so the last copy closes the call; the frees below are ordered on `s`
+		if( e == cudaSuccess ) e = cudaEventRecord( ctx->bandEv[16], ctx->copyStream );
+		if( e == cudaSuccess ) e = cudaStreamWaitEvent( s, ctx->bandEv[16], 0 );
+		if( e != cudaSuccess && r == 0 ) r = cudaFail( e, "band pipeline", __FILE__, __LINE__ );
+		for( int i = 0; i < 2; i++ )
+			if( ( e = cudaStreamSynchronize( ctx->bandStream[i] ) ) != cudaSuccess && r == 0 ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+		if( ( e = cudaStreamSynchronize( ctx->copyStream ) ) != cudaSuccess && r == 0 ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+		if( ( e = cudaStreamSynchronize( s ) ) != cudaSuccess && r == 0 ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
 	} while( 0 );
 #undef CP
 	dfree( rgba_d, s ), dfree( t_d, s ), dfree( nm_d, s ), dfree( vi_d, s );

@@ -21,114 +21,134 @@ namespace hako
 // 2^-level, exact (what `scale *= 0.5f` per descent produces, voxCommon.hpp:385)
 __device__ __forceinline__ float levelScale( uint32_t level ) { return __uint_as_float( ( 127u - level ) << 23 ); }
 
-// returns true on a hit (and then writes t / nMajor / vIndex); a miss leaves the outputs untouched (voxRT.cpp:313-325)
-// `shadow` may be a compile-time constant (the template wrapper below) or a per-lane runtime value (the path tracer
-// traces closest-hit and shadow rays of different lanes through ONE call site so the warp stays converged).
-__device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, V3 rd, const bool shadow, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
+// The traversal as a resumable object: begin() sets a ray up (mirroring, clamped 1/rd, root slab test), step() advances it
+// by ONE uniform step.  Persistent kernels keep one Traversal per lane and refill a lane the moment its ray ends, so a warp
+// never waits for its slowest ray; octreeTraverseImpl() below is the plain "run to completion" wrapper.
+//
+// One uniform step per call (instead of the reference's visit loop + inner sibling loop + pop): every lane of a warp
+// executes the same straight-line body whatever its depth in the tree, so the warp does not split into the "computing t0 /
+// walking siblings / popping" groups the nested form produces.  Each value is the same fp32 expression of ( t1, dt, level,
+// childMask ) as in voxCommon.hpp:317-411, so recomputing it per step is bit-neutral.
+enum : int
 {
-	if( v.numberOfNodes == 0 ) return false;
+	TRAV_CONTINUE = 0,
+	TRAV_HIT = 1,
+	TRAV_MISS = 2
+};
+// the per-thread stack lives in its own object (local memory); keeping it out of Traversal lets the scalar state stay in registers
+struct TravStack
+{
+	uint4 a[HAKO_STACK_DEPTH]; // node, tx1, ty1, tz1
+	uint2 b[HAKO_STACK_DEPTH]; // childMask | level << 8, nVoxelSkipped
+};
+struct Traversal
+{
+	int sp;
+	float dtx, dty, dtz;
+	float tx1, ty1, tz1;
+	uint32_t node, level, childMask, skipped, vMask;
+	// results of a TRAV_HIT step
+	float t;
+	int nMajor;
 
-	// voxCommon.hpp:240-260: mirror negative directions
-	V3 inv = { 1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z };
-	uint32_t vMask = 0;
-	if( inv.x < 0.0f )
+	// false: the ray misses the root box (or the tree is empty)
+	__device__ __forceinline__ bool begin( const OctreeView& v, V3 ro, V3 rd )
 	{
-		vMask |= 1u;
-		inv.x = -inv.x;
-		ro.x = v.lower.x + v.upper.x - ro.x;
+		if( v.numberOfNodes == 0 ) return false;
+		// voxCommon.hpp:240-260: mirror negative directions
+		V3 inv = { 1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z };
+		vMask = 0;
+		if( inv.x < 0.0f )
+		{
+			vMask |= 1u;
+			inv.x = -inv.x;
+			ro.x = v.lower.x + v.upper.x - ro.x;
+		}
+		if( inv.y < 0.0f )
+		{
+			vMask |= 2u;
+			inv.y = -inv.y;
+			ro.y = v.lower.y + v.upper.y - ro.y;
+		}
+		if( inv.z < 0.0f )
+		{
+			vMask |= 4u;
+			inv.z = -inv.z;
+			ro.z = v.lower.z + v.upper.z - ro.z;
+		}
+		// :265-269: clamp 1/rd so that (bound - ro) * inv never overflows to inf (no inf * 0)
+		const V3 lo = v.lower - ro, up = v.upper - ro;
+		inv.x = smin( inv.x, HAKO_MAX_FLOAT / smax( smax( sabs( lo.x ), sabs( up.x ) ), 1.0f ) );
+		inv.y = smin( inv.y, HAKO_MAX_FLOAT / smax( smax( sabs( lo.y ), sabs( up.y ) ), 1.0f ) );
+		inv.z = smin( inv.z, HAKO_MAX_FLOAT / smax( smax( sabs( lo.z ), sabs( up.z ) ), 1.0f ) );
+		// :271-278 root slab test
+		const float t0x = lo.x * inv.x, t0y = lo.y * inv.y, t0z = lo.z * inv.z;
+		tx1 = up.x * inv.x, ty1 = up.y * inv.y, tz1 = up.z * inv.z;
+		if( min3( tx1, ty1, tz1 ) < max3( t0x, t0y, t0z ) ) return false;
+		dtx = tx1 - t0x, dty = ty1 - t0y, dtz = tz1 - t0z;
+		sp = 0;
+		const uint32_t root = v.numberOfNodes - 1; // the root is the last node (IntersectorOctree.hpp:252)
+		node = root | ( (uint32_t)__ldg( v.masks + root ) << 24 );
+		level = 0;
+		childMask = 0xFFu; // "not chosen yet" (reference: 0xFFFFFFFF)
+		skipped = 0;
+		return true;
 	}
-	if( inv.y < 0.0f )
+
+	// hit: t / nMajor are set, `skipped` is vIndex
+	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, TravStack& stk )
 	{
-		vMask |= 2u;
-		inv.y = -inv.y;
-		ro.y = v.lower.y + v.upper.y - ro.y;
-	}
-	if( inv.z < 0.0f )
-	{
-		vMask |= 4u;
-		inv.z = -inv.z;
-		ro.z = v.lower.z + v.upper.z - ro.z;
-	}
-	// :265-269: clamp 1/rd so that (bound - ro) * inv never overflows to inf (no inf * 0)
-	V3 lo = v.lower - ro, up = v.upper - ro;
-	inv.x = smin( inv.x, HAKO_MAX_FLOAT / smax( smax( sabs( lo.x ), sabs( up.x ) ), 1.0f ) );
-	inv.y = smin( inv.y, HAKO_MAX_FLOAT / smax( smax( sabs( lo.y ), sabs( up.y ) ), 1.0f ) );
-	inv.z = smin( inv.z, HAKO_MAX_FLOAT / smax( smax( sabs( lo.z ), sabs( up.z ) ), 1.0f ) );
-
-	// :271-278 root slab test
-	float t0x = lo.x * inv.x, t0y = lo.y * inv.y, t0z = lo.z * inv.z;
-	float c_tx1 = up.x * inv.x, c_ty1 = up.y * inv.y, c_tz1 = up.z * inv.z;
-	if( min3( c_tx1, c_ty1, c_tz1 ) < max3( t0x, t0y, t0z ) ) return false;
-	const float dtx = c_tx1 - t0x, dty = c_ty1 - t0y, dtz = c_tz1 - t0z;
-
-	uint4 stackA[HAKO_STACK_DEPTH]; // node, tx1, ty1, tz1
-	uint2 stackB[HAKO_STACK_DEPTH]; // childMask | level << 8, nVoxelSkipped
-	int sp = 0;
-
-	const uint32_t root = v.numberOfNodes - 1; // the root is the last node (IntersectorOctree.hpp:252)
-	uint32_t c_node = root | ( (uint32_t)__ldg( v.masks + root ) << 24 );
-	uint32_t c_level = 0;
-	uint32_t c_childMask = 0xFFu; // "not chosen yet" (reference: 0xFFFFFFFF)
-	uint32_t c_skipped = 0;
-
-	// One uniform step per iteration (instead of the reference's visit loop + inner sibling loop + pop): every lane of a
-	// warp executes the same straight-line body whatever its depth in the tree, so the warp does not split into the
-	// "computing t0 / walking siblings / popping" groups the nested form produces.  Each value below is the same fp32
-	// expression of ( t1, dt, level, childMask ) as in voxCommon.hpp:317-411, so recomputing it per step is bit-neutral.
-	for( ;; )
-	{
-		const float scale = levelScale( c_level );
+		const float scale = levelScale( level );
 		// :317-319 t0 is recomputed from t1 each visit
-		const float tx0 = c_tx1 - dtx * scale;
-		const float ty0 = c_ty1 - dty * scale;
-		const float tz0 = c_tz1 - dtz * scale;
+		const float tx0 = tx1 - dtx * scale;
+		const float ty0 = ty1 - dty * scale;
+		const float tz0 = tz1 - dtz * scale;
 		const float lmax = max3( tx0, ty0, tz0 );
 
 		bool pop = false;
-		if( c_node == 0xFFFFFFFFu )
+		if( node == 0xFFFFFFFFu )
 		{
 			// :322-336 leaf voxel
 			if( 0.0f < lmax )
 			{
-				*tOut = lmax;
-				*nMajorOut = ( lmax == tx0 ) ? 1 : ( ( lmax == ty0 ) ? 2 : 0 );
-				*vIndexOut = c_skipped;
-				return true;
+				t = lmax;
+				nMajor = ( lmax == tx0 ) ? 1 : ( ( lmax == ty0 ) ? 2 : 0 );
+				return TRAV_HIT;
 			}
 			pop = true;
 		}
 		else
 		{
 			// :338-348
-			const float txM = 0.5f * ( tx0 + c_tx1 );
-			const float tyM = 0.5f * ( ty0 + c_ty1 );
-			const float tzM = 0.5f * ( tz0 + c_tz1 );
-			if( c_childMask == 0xFFu ) c_childMask = ( txM < lmax ? 1u : 0u ) | ( tyM < lmax ? 2u : 0u ) | ( tzM < lmax ? 4u : 0u );
-			const float x1 = ( c_childMask & 1u ) ? c_tx1 : txM;
-			const float y1 = ( c_childMask & 2u ) ? c_ty1 : tyM;
-			const float z1 = ( c_childMask & 4u ) ? c_tz1 : tzM;
+			const float txM = 0.5f * ( tx0 + tx1 );
+			const float tyM = 0.5f * ( ty0 + ty1 );
+			const float tzM = 0.5f * ( tz0 + tz1 );
+			if( childMask == 0xFFu ) childMask = ( txM < lmax ? 1u : 0u ) | ( tyM < lmax ? 2u : 0u ) | ( tzM < lmax ? 4u : 0u );
+			const float x1 = ( childMask & 1u ) ? tx1 : txM;
+			const float y1 = ( childMask & 2u ) ? ty1 : tyM;
+			const float z1 = ( childMask & 4u ) ? tz1 : tzM;
 			// :365-411 the child the ray is in now; the exit plane decides the next sibling
 			const float umin = min3( x1, y1, z1 );
 			const uint32_t mv = ( umin == x1 ) ? 1u : ( ( umin == y1 ) ? 2u : 4u );
-			const bool hasNext = ( c_childMask & mv ) == 0;
-			const uint32_t ci = c_childMask ^ vMask;
-			c_childMask |= mv;
-			if( ( ( c_node >> ( 24 + ci ) ) & 1u ) && !( umin < 0.0f ) )
+			const bool hasNext = ( childMask & mv ) == 0;
+			const uint32_t ci = childMask ^ vMask;
+			childMask |= mv;
+			if( ( ( node >> ( 24 + ci ) ) & 1u ) && !( umin < 0.0f ) )
 			{
 				if( hasNext )
 				{
-					stackA[sp] = make_uint4( c_node, __float_as_uint( c_tx1 ), __float_as_uint( c_ty1 ), __float_as_uint( c_tz1 ) );
-					stackB[sp] = make_uint2( c_childMask | ( c_level << 8 ), c_skipped );
+					stk.a[sp] = make_uint4( node, __float_as_uint( tx1 ), __float_as_uint( ty1 ), __float_as_uint( tz1 ) );
+					stk.b[sp] = make_uint2( childMask | ( level << 8 ), skipped );
 					sp++;
 				}
-				const uint2 slot = ldg_u2( &v.nodes[c_node & 0xFFFFFFu].slot[ci] );
-				c_node = slot.x;
-				c_tx1 = x1;
-				c_ty1 = y1;
-				c_tz1 = z1;
-				c_level++;
-				c_childMask = 0xFFu;
-				if( !shadow ) c_skipped += slot.y; // :388-391
+				const uint2 slot = ldg_u2( &v.nodes[node & 0xFFFFFFu].slot[ci] );
+				node = slot.x;
+				tx1 = x1;
+				ty1 = y1;
+				tz1 = z1;
+				level++;
+				childMask = 0xFFu;
+				if( !shadow ) skipped += slot.y; // :388-391
 			}
 			else
 				pop = !hasNext; // otherwise stay in this node: the next step looks at the sibling behind plane `mv`
@@ -136,18 +156,38 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 		if( pop )
 		{
 			// :414-422
-			if( sp == 0 ) return false;
+			if( sp == 0 ) return TRAV_MISS;
 			sp--;
-			const uint4 a = stackA[sp];
-			const uint2 b = stackB[sp];
-			c_node = a.x;
-			c_tx1 = __uint_as_float( a.y );
-			c_ty1 = __uint_as_float( a.z );
-			c_tz1 = __uint_as_float( a.w );
-			c_childMask = b.x & 0xFFu;
-			c_level = b.x >> 8;
-			c_skipped = b.y;
+			const uint4 a = stk.a[sp];
+			const uint2 b = stk.b[sp];
+			node = a.x;
+			tx1 = __uint_as_float( a.y );
+			ty1 = __uint_as_float( a.z );
+			tz1 = __uint_as_float( a.w );
+			childMask = b.x & 0xFFu;
+			level = b.x >> 8;
+			skipped = b.y;
 		}
+		return TRAV_CONTINUE;
+	}
+};
+
+// returns true on a hit (and then writes t / nMajor / vIndex); a miss leaves the outputs untouched (voxRT.cpp:313-325).
+// `shadow` may be a compile-time constant (the template wrapper below) or a per-lane runtime value.
+__device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, V3 rd, const bool shadow, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
+{
+	Traversal tr;
+	TravStack stk;
+	if( !tr.begin( v, ro, rd ) ) return false;
+	for( ;; )
+	{
+		const int r = tr.step( v, shadow, stk );
+		if( r == TRAV_CONTINUE ) continue;
+		if( r == TRAV_MISS ) return false;
+		*tOut = tr.t;
+		*nMajorOut = tr.nMajor;
+		*vIndexOut = tr.skipped;
+		return true;
 	}
 }
 
