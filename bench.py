@@ -187,7 +187,7 @@ def run_reference(args):
                              "cpu": cpu_model(), "build_ms": build},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "unique_voxels": int(mk.size), "octree_nodes": tree.num_nodes}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
 def run_ours(args):
@@ -366,7 +366,7 @@ def run_ours(args):
                     "ms_per_step": e2e_total / args.steps, "call": "hako_render_primary (host buffers, pinned), one call per view"},
             "gpu_launches": int(launches), "roofline": roofline, "path_tracing": pt_res, "cpu_baseline": cpu, "build": build, "hits_view0": hits_view0,
             "parity_vs_cpu_reference_view0": parity, "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -450,6 +450,9 @@ def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
     return res
 
 
+_REAL_STDOUT = sys.stdout
+
+
 def load_profile_value(key, default):
     try:
         return json.load(open(os.path.join(ROOT, "profiles", "latest.json"))).get(key, default)
@@ -465,6 +468,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner there) go to stderr
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
