@@ -170,10 +170,8 @@ int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, cons
 	int r = 0;
 	if( nf )
 	{
-		cudaError_t e = cudaMemcpyAsync( d, pos, nf * 4, cudaMemcpyHostToDevice, s );
-		if( e == cudaSuccess ) e = cudaMemcpyAsync( d + nf, col, nf * 4, cudaMemcpyHostToDevice, s );
-		if( e == cudaSuccess ) e = cudaMemcpyAsync( d + 2 * nf, emi, nf * 4, cudaMemcpyHostToDevice, s );
-		if( e != cudaSuccess ) r = cudaFail( e, "H2D vertices", __FILE__, __LINE__ );
+		const H2DSegment segs[3] = { { d, pos, nf * 4 }, { d + nf, col, nf * 4 }, { d + 2 * nf, emi, nf * 4 } };
+		r = uploadSegments( ctx, s, segs, 3 );
 	}
 	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out );
 	dfree( d, s );

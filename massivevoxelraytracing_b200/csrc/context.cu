@@ -76,6 +76,7 @@ void hako_ctx_destroy( hako_ctx* c )
 	if( !c ) return;
 	cudaSetDevice( c->device );
 	cudaDeviceSynchronize();
+	hako::destroyStager( c );
 	for( int i = 0; i < 8; i++ )
 		if( c->ev[i] ) cudaEventDestroy( c->ev[i] );
 	if( c->pinned ) cudaFreeHost( c->pinned );

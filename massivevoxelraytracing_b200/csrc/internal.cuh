@@ -6,6 +6,11 @@
 
 #include "common.cuh"
 
+namespace hako
+{
+struct Stager;
+}
+
 struct hako_ctx
 {
 	int device = 0;
@@ -21,6 +26,8 @@ struct hako_ctx
 	cudaStream_t copyStream = nullptr;
 	cudaStream_t bandStream[2] = {}; // band kernels alternate between these so that one band's tail overlaps the next band
 	cudaEvent_t bandEv[17] = {};
+	// host->device staging of pageable caller memory (h2d.cu): HAKO_H2D_WORKERS threads, each with two pinned chunks and a stream
+	hako::Stager* stager = nullptr;
 };
 
 struct hako_octree
@@ -90,6 +97,17 @@ int launchIntersectBatch( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, co
 						  float* t, int32_t* nMajor, uint32_t* vIndex );
 int launchRenderPrimary( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, const hako_camera& cam, int w, int h, int y0, int y1,
 						 int showVertexColor, uint8_t* rgba, float* t, int32_t* nMajor, uint32_t* vIndex );
+
+// h2d.cu: upload `n` host segments; pageable sources go through worker threads that memcpy into pinned chunks while the
+// previous chunk is on the wire (a plain cudaMemcpyAsync from pageable memory runs at ~11 GB/s on this box).  Stream-ordered on s.
+struct H2DSegment
+{
+	void* dst;
+	const void* src;
+	size_t bytes;
+};
+int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n );
+void destroyStager( hako_ctx* ctx );
 
 // voxelize.cu
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,

@@ -15,6 +15,7 @@
 //   - theta-only trigonometry of the lat-long map is tabulated per row on the host (exactly the values the CPU code
 //     computes), the SAT build is bit-exact with the oracle (same fp32 products, same Hillis-Steele double sums).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -47,6 +48,10 @@ struct hako_pt
 	float4* pathL = nullptr;
 	uint64_t pathCap = 0;
 	unsigned long long* counters = nullptr; // [0] work counter, [1] rays traced
+	uint32_t* hitQueue = nullptr;			// path indices whose primary ray hit (wavefront mode), capacity pathCap
+	// 1: wavefront -- primaryWaveKernel + pathTraceKernel<true>; 0 (default): single persistent kernel (pathTraceKernel<false>).
+	// HAKO_PT_WAVEFRONT overrides (A/B knob, read at create time).
+	int wavefront = 0;
 };
 
 namespace
@@ -67,7 +72,8 @@ struct PtParams
 	hako_camera cam;
 	const float* pmj;
 	float4* pathL;
-	unsigned long long* counters;
+	unsigned long long* counters; // [0] work counter, [1] rays traced, [2] hit-queue length
+	uint32_t* hitQueue;
 	int w, h, y0;
 	uint32_t nPaths;
 	uint32_t iteration;
@@ -235,164 +241,239 @@ enum : uint32_t
 	NEXT_FINISH
 };
 
-// renderPT, voxKernel.cu:610-777, as a persistent per-lane state machine (see the header of this file).
-// Path index -> (pixel, localSpp) keeps the reference's "16 adjacent threads share a pixel" (:635-637).
+// per-lane path state of the persistent kernels
+struct PathState
+{
+	uint32_t kind, path, spp, stream, dim;
+	int depth;
+	V3 o, d, T, L, pending, hitN;
+};
+
+// path index -> (pixel, localSpp) keeps the reference's "16 adjacent threads share a pixel" (voxKernel.cu:635-637);
+// camera + lens dimensions, thin-lens primary ray (:640-672)
+__device__ __forceinline__ void startPath( const PtParams& p, PathState& s, uint32_t path )
+{
+	s.path = path;
+	const uint32_t localPixel = path / PT_SPP, localSpp = path % PT_SPP;
+	const uint32_t x = localPixel % (uint32_t)p.w, y = (uint32_t)p.y0 + localPixel / (uint32_t)p.w;
+	const uint32_t pixelIdx = y * (uint32_t)p.w + x;
+	s.spp = p.iteration * PT_SPP + localSpp;
+	Murmur32 hs( 0 );
+	hs.combine( pixelIdx );
+	s.stream = hs.getHash();
+	s.dim = 0;
+	const float2 cam_u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+	const float2 lens_u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+	cameraShootThinLens( p.cam, (int)x, (int)y, cam_u01.x, cam_u01.y, p.w, p.h, lens_u01.x, lens_u01.y, &s.o, &s.d );
+	s.T = { 1.0f, 1.0f, 1.0f };
+	s.L = { 0.0f, 0.0f, 0.0f };
+	s.depth = 0;
+	s.kind = RAY_PRIMARY;
+}
+
+// consume the result of the ray a lane just traced and set up its next ray (or finish the path: kind = LANE_IDLE)
+__device__ __forceinline__ void shadeVertex( const PtParams& p, const bool envOn, const uint32_t nExtra, PathState& s, const bool hit, const float t,
+											 const int nMajor, const uint32_t vIndex )
+{
+	uint32_t next;
+	if( s.kind == RAY_PRIMARY )
+	{
+		if( !hit )
+		{
+			if( p.env.pixels ) s.L = s.L + s.T * hdriSampleNearest( p.env, s.d, true ); // :678-683
+			next = NEXT_FINISH;
+		}
+		else
+		{
+			s.L = s.L + s.T * rawReflectance( loadAttrib( p.tree, vIndex ).y ); // unscaled, :686-688
+			next = NEXT_SHADE;
+		}
+	}
+	else if( s.kind == RAY_SHADOW )
+	{
+		if( !hit ) s.L = s.L + s.pending; // :712-715
+		next = ( s.depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
+	}
+	else if( s.kind == RAY_EXTRA )
+	{
+		if( hit ) // :733-736
+			s.L = s.L + s.T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) / (float)( 1u + nExtra );
+		next = NEXT_GEN_BOUNCE;
+	}
+	else
+	{
+		if( hit ) // :750-758
+			s.L = s.L + s.T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) * ( s.depth == 0 ? 1.0f / (float)( 1u + nExtra ) : 1.0f );
+		s.depth++;
+		next = ( hit && s.depth < p.maxDepth ) ? NEXT_SHADE : NEXT_FINISH;
+	}
+
+	if( next == NEXT_SHADE )
+	{
+		// surface point of the path ray (o, d) that just hit: :693-695
+		const V3 R = rawReflectance( loadAttrib( p.tree, vIndex ).x );
+		s.hitN = getHitN( nMajor, s.d );
+		s.o = s.o + s.d * t; // hitP: every following ray of this vertex starts here, without an epsilon
+		if( envOn )
+		{
+			const float2 u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+			const float2 u23 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+			V3 dir, emissive;
+			float pdf;
+			hdriImportanceSample( p.env, &dir, &emissive, &pdf, s.hitN, u01.x, u01.y, u23.x, u23.y );
+			s.pending = s.T * ( R / HAKO_PI ) * smax( dot( s.hitN, dir ), 0.0f ) * emissive / pdf;
+			s.T = s.T * R;
+			s.d = dir;
+			s.kind = RAY_SHADOW;
+			next = NEXT_TRACE;
+		}
+		else
+		{
+			s.T = s.T * R;
+			next = ( s.depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
+		}
+	}
+	if( next == NEXT_GEN_EXTRA || next == NEXT_GEN_BOUNCE )
+	{
+		const float2 u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+		s.d = sampleLambertian( u01.x, u01.y, s.hitN );
+		s.kind = ( next == NEXT_GEN_EXTRA ) ? RAY_EXTRA : RAY_BOUNCE;
+	}
+	else if( next == NEXT_FINISH )
+	{
+		p.pathL[s.path] = make_float4( s.L.x, s.L.y, s.L.z, 0.0f );
+		s.kind = LANE_IDLE;
+	}
+}
+
+// warp-ballot refill with persistent work fetch: idle lanes are ranked by popc and take consecutive work indices from a
+// per-warp chunk fetched with one atomicAdd on the global work counter.  Warp-collective (all 32 lanes must call it).
+// FROM_QUEUE = false: work index = path index, the lane starts the path's primary ray.
+// FROM_QUEUE = true : work index -> hitQueue[] -> a path whose primary ray already hit (primaryWaveKernel left the hit record
+//                     in pathL[path]); the lane re-derives the camera ray and goes straight to shading that vertex.
+template <bool FROM_QUEUE>
+__device__ __forceinline__ void refillIdleLanes( const PtParams& p, const bool envOn, const uint32_t nExtra, const uint32_t nWork, PathState& s, uint32_t lane,
+												 uint32_t& wNext, uint32_t& wEnd, bool& drained )
+{
+	const uint32_t idleMask = __ballot_sync( 0xFFFFFFFFu, s.kind == LANE_IDLE );
+	if( !idleMask || drained ) return;
+	if( wNext == wEnd )
+	{
+		uint32_t base = 0;
+		if( lane == 0 ) base = (uint32_t)atomicAdd( p.counters, (unsigned long long)PT_CHUNK );
+		base = __shfl_sync( 0xFFFFFFFFu, base, 0 );
+		if( base >= nWork )
+		{
+			drained = true;
+			return;
+		}
+		wNext = base;
+		wEnd = min( base + PT_CHUNK, nWork );
+	}
+	const uint32_t rank = __popc( idleMask & ( ( 1u << lane ) - 1u ) );
+	const uint32_t avail = wEnd - wNext;
+	if( s.kind == LANE_IDLE && rank < avail )
+	{
+		if( FROM_QUEUE )
+		{
+			const uint32_t path = __ldg( p.hitQueue + wNext + rank );
+			const float4 rec = __ldcs( p.pathL + path ); // { t, vIndex, nMajor, - } of the primary hit
+			startPath( p, s, path );
+			shadeVertex( p, envOn, nExtra, s, true, rec.x, __float_as_int( rec.z ), __float_as_uint( rec.y ) );
+		}
+		else
+			startPath( p, s, wNext + rank );
+	}
+	wNext += min( (uint32_t)__popc( idleMask ), avail );
+}
+
+// renderPT, voxKernel.cu:610-777, as a persistent per-lane state machine (see the header of this file): every loop
+// iteration traces one whole ray per lane through ONE traversal call site, then shades and sets up the lane's next ray.
+// FROM_QUEUE = false: the whole path, primary ray included (single-kernel mode).
+// FROM_QUEUE = true : the continuation of the paths whose primary ray hit (second wave of the wavefront mode).
+template <bool FROM_QUEUE>
 __global__ void __launch_bounds__( PT_BLOCK ) pathTraceKernel( const PtParams p )
 {
 	const uint32_t lane = threadIdx.x & 31u;
 	const bool envOn = 0.0f < p.env.scale && p.env.pixels != nullptr; // HDRI::isEnabled
 	const uint32_t nExtra = p.tree.hasEmission ? 1u : 0u;			  // EXTRA_IMPLICIT_SAMPLING, :720
+	const uint32_t nWork = FROM_QUEUE ? (uint32_t)p.counters[2] : p.nPaths;
 
-	// warp-uniform chunk of path indices
-	uint32_t wNext = 0, wEnd = 0;
+	uint32_t wNext = 0, wEnd = 0; // warp-uniform chunk of work indices
 	bool drained = false;
-
-	// per-lane path state
-	uint32_t kind = LANE_IDLE;
-	uint32_t path = 0, spp = 0, stream = 0, dim = 0;
-	int depth = 0;
-	V3 o = {}, d = {};
-	V3 T = {}, L = {}, pending = {}, hitN = {};
+	PathState s = {};
+	s.kind = LANE_IDLE;
 	unsigned long long rays = 0;
 
 	for( ;; )
 	{
-		// ---- refill idle lanes: ballot -> rank -> index (persistent-thread work fetch) ----
-		const uint32_t idleMask = __ballot_sync( 0xFFFFFFFFu, kind == LANE_IDLE );
-		if( idleMask && !drained )
-		{
-			if( wNext == wEnd )
-			{
-				uint32_t base = 0;
-				if( lane == 0 ) base = (uint32_t)atomicAdd( p.counters, (unsigned long long)PT_CHUNK );
-				base = __shfl_sync( 0xFFFFFFFFu, base, 0 );
-				if( base >= p.nPaths )
-					drained = true;
-				else
-				{
-					wNext = base;
-					wEnd = min( base + PT_CHUNK, p.nPaths );
-				}
-			}
-			if( !drained )
-			{
-				const uint32_t rank = __popc( idleMask & ( ( 1u << lane ) - 1u ) );
-				const uint32_t avail = wEnd - wNext;
-				if( kind == LANE_IDLE && rank < avail )
-				{
-					path = wNext + rank;
-					const uint32_t localPixel = path / PT_SPP, localSpp = path % PT_SPP;
-					const uint32_t x = localPixel % (uint32_t)p.w, y = (uint32_t)p.y0 + localPixel / (uint32_t)p.w;
-					const uint32_t pixelIdx = y * (uint32_t)p.w + x;
-					spp = p.iteration * PT_SPP + localSpp;
-					Murmur32 hs( 0 );
-					hs.combine( pixelIdx );
-					stream = hs.getHash();
-					dim = 0;
-					const float2 cam_u01 = pmjSample2d( p.pmj, spp, dim++, stream );
-					const float2 lens_u01 = pmjSample2d( p.pmj, spp, dim++, stream );
-					cameraShootThinLens( p.cam, (int)x, (int)y, cam_u01.x, cam_u01.y, p.w, p.h, lens_u01.x, lens_u01.y, &o, &d );
-					T = { 1.0f, 1.0f, 1.0f };
-					L = { 0.0f, 0.0f, 0.0f };
-					depth = 0;
-					kind = RAY_PRIMARY;
-				}
-				wNext += min( (uint32_t)__popc( idleMask ), avail );
-			}
-		}
-		if( __all_sync( 0xFFFFFFFFu, kind == LANE_IDLE ) )
+		refillIdleLanes<FROM_QUEUE>( p, envOn, nExtra, nWork, s, lane, wNext, wEnd, drained );
+		if( __all_sync( 0xFFFFFFFFu, s.kind == LANE_IDLE ) )
 		{
 			if( drained ) break;
 			continue;
 		}
-
-		// ---- extend: ONE traversal call site for every ray kind ----
-		float t = HAKO_MAX_FLOAT;
-		int nMajor = 0;
-		uint32_t vIndex = 0;
-		bool hit = false;
-		if( kind != LANE_IDLE )
+		if( s.kind != LANE_IDLE )
 		{
-			hit = octreeTraverseImpl( p.tree, o, d, kind == RAY_SHADOW, &t, &nMajor, &vIndex );
+			// ---- extend: ONE traversal call site for every ray kind ----
+			float t = HAKO_MAX_FLOAT;
+			int nMajor = 0;
+			uint32_t vIndex = 0;
+			const bool hit = octreeTraverseImpl( p.tree, s.o, s.d, s.kind == RAY_SHADOW, &t, &nMajor, &vIndex );
 			rays++;
-		}
-
-		// ---- shade ----
-		if( kind == LANE_IDLE ) continue;
-		uint32_t next;
-		if( kind == RAY_PRIMARY )
-		{
-			if( !hit )
-			{
-				if( p.env.pixels ) L = L + T * hdriSampleNearest( p.env, d, true ); // :678-683
-				next = NEXT_FINISH;
-			}
-			else
-			{
-				L = L + T * rawReflectance( loadAttrib( p.tree, vIndex ).y ); // unscaled, :686-688
-				next = NEXT_SHADE;
-			}
-		}
-		else if( kind == RAY_SHADOW )
-		{
-			if( !hit ) L = L + pending; // :712-715
-			next = ( depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
-		}
-		else if( kind == RAY_EXTRA )
-		{
-			if( hit ) // :733-736
-				L = L + T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) / (float)( 1u + nExtra );
-			next = NEXT_GEN_BOUNCE;
-		}
-		else
-		{
-			if( hit ) // :750-758
-				L = L + T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) * ( depth == 0 ? 1.0f / (float)( 1u + nExtra ) : 1.0f );
-			depth++;
-			next = ( hit && depth < p.maxDepth ) ? NEXT_SHADE : NEXT_FINISH;
-		}
-
-		if( next == NEXT_SHADE )
-		{
-			// surface point of the path ray (o, d) that just hit: :693-695
-			const V3 R = rawReflectance( loadAttrib( p.tree, vIndex ).x );
-			hitN = getHitN( nMajor, d );
-			o = o + d * t; // hitP: every following ray of this vertex starts here, without an epsilon
-			if( envOn )
-			{
-				const float2 u01 = pmjSample2d( p.pmj, spp, dim++, stream );
-				const float2 u23 = pmjSample2d( p.pmj, spp, dim++, stream );
-				V3 dir, emissive;
-				float pdf;
-				hdriImportanceSample( p.env, &dir, &emissive, &pdf, hitN, u01.x, u01.y, u23.x, u23.y );
-				pending = T * ( R / HAKO_PI ) * smax( dot( hitN, dir ), 0.0f ) * emissive / pdf;
-				T = T * R;
-				d = dir;
-				kind = RAY_SHADOW;
-				next = NEXT_TRACE;
-			}
-			else
-			{
-				T = T * R;
-				next = ( depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
-			}
-		}
-		if( next == NEXT_GEN_EXTRA || next == NEXT_GEN_BOUNCE )
-		{
-			const float2 u01 = pmjSample2d( p.pmj, spp, dim++, stream );
-			d = sampleLambertian( u01.x, u01.y, hitN );
-			kind = ( next == NEXT_GEN_EXTRA ) ? RAY_EXTRA : RAY_BOUNCE;
-		}
-		else if( next == NEXT_FINISH )
-		{
-			p.pathL[path] = make_float4( L.x, L.y, L.z, 0.0f );
-			kind = LANE_IDLE;
+			shadeVertex( p, envOn, nExtra, s, hit, t, nMajor, vIndex );
 		}
 	}
 
 	// one atomic per warp for the ray counter
 	for( int off = 16; off; off >>= 1 ) rays += __shfl_down_sync( 0xFFFFFFFFu, rays, off );
 	if( lane == 0 && rays ) atomicAdd( p.counters + 1, rays );
+}
+
+// First wave of the wavefront mode: the primary rays of ALL paths of the step, one thread per path, plain launch.
+// Primary rays are coherent (the 16 samples of a pixel sit in adjacent lanes, a block is a 4x4 pixel tile) and short; in the
+// single persistent kernel they shared warps with the long incoherent shadow / bounce rays of the ~20 % of paths that hit
+// something, so most lanes of most warps waited (11 of 32 lanes active on average, profiles/r1b).  Here a miss finishes the
+// path at once (environment lookup, :678-683); a hit leaves { t, vIndex, nMajor } in pathL[path] and the path index in
+// hitQueue -- warp-ballot compaction, one atomicAdd per warp -- for continuePaths (pathTraceKernel<true>).
+__global__ void __launch_bounds__( PT_BLOCK ) primaryWaveKernel( const PtParams p, const int rows )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t tilesX = ( (uint32_t)p.w + 3u ) / 4u;
+	const uint32_t tx = blockIdx.x % tilesX, ty = blockIdx.x / tilesX;
+	const uint32_t pix = threadIdx.x / PT_SPP; // 0..15 inside the 4x4 tile
+	const uint32_t x = tx * 4u + ( pix & 3u ), yl = ty * 4u + ( pix >> 2 );
+	const bool inside = x < (uint32_t)p.w && yl < (uint32_t)rows;
+	const bool envOn = 0.0f < p.env.scale && p.env.pixels != nullptr;
+	const uint32_t nExtra = p.tree.hasEmission ? 1u : 0u;
+
+	bool hit = false;
+	uint32_t path = 0;
+	if( inside )
+	{
+		path = ( yl * (uint32_t)p.w + x ) * PT_SPP + ( threadIdx.x % PT_SPP );
+		PathState s;
+		startPath( p, s, path );
+		float t = HAKO_MAX_FLOAT;
+		int nMajor = 0;
+		uint32_t vIndex = 0;
+		hit = octreeTraverseImpl( p.tree, s.o, s.d, false, &t, &nMajor, &vIndex );
+		if( hit )
+			__stcs( p.pathL + path, make_float4( t, __uint_as_float( vIndex ), __int_as_float( nMajor ), 0.0f ) );
+		else
+			shadeVertex( p, envOn, nExtra, s, false, t, nMajor, vIndex ); // finishes the path: writes pathL[path]
+	}
+	// ray compaction: ballot -> rank -> one atomicAdd per warp
+	const uint32_t hitMask = __ballot_sync( 0xFFFFFFFFu, hit );
+	const uint32_t insideMask = __ballot_sync( 0xFFFFFFFFu, inside );
+	if( hitMask )
+	{
+		unsigned long long base = 0;
+		if( lane == 0 ) base = atomicAdd( p.counters + 2, (unsigned long long)__popc( hitMask ) );
+		base = __shfl_sync( 0xFFFFFFFFu, base, 0 );
+		if( hit ) p.hitQueue[base + __popc( hitMask & ( ( 1u << lane ) - 1u ) )] = path;
+	}
+	if( lane == 0 && insideMask ) atomicAdd( p.counters + 1, (unsigned long long)__popc( insideMask ) );
 }
 
 // per-pixel reduction in localSpp order, then `frameBuffer += `, voxKernel.cu:763-774
@@ -605,16 +686,17 @@ int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out )
 	HAKO_CUDA( cudaSetDevice( ctx->device ) );
 	hako_pt* pt = new hako_pt();
 	pt->ctx = ctx;
+	if( const char* e = getenv( "HAKO_PT_WAVEFRONT" ) ) pt->wavefront = atoi( e );
 	std::vector<float> table( (size_t)2 * PMJ_LENGTH * PMJ_NSEQ );
 	HostPCG32 rng;
 	rng.setup( 0, 2525 ); // pmjSampler.hpp:116-117
 	for( int i = 0; i < PMJ_NSEQ; i++ ) generatePMJ02( PMJ_LENGTH, table.data() + (size_t)2 * PMJ_LENGTH * i, rng );
 	int r = dalloc( ctx, &pt->pmj, table.size(), s );
-	if( r == 0 ) r = dalloc( ctx, &pt->counters, 2, s );
+	if( r == 0 ) r = dalloc( ctx, &pt->counters, 4, s );
 	if( r == 0 )
 	{
 		cudaError_t e = cudaMemcpyAsync( pt->pmj, table.data(), table.size() * sizeof( float ), cudaMemcpyHostToDevice, s );
-		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, 2 * sizeof( unsigned long long ), s );
+		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, 4 * sizeof( unsigned long long ), s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s ); // `table` dies with this scope
 		if( e != cudaSuccess ) r = cudaFail( e, "PMJ upload", __FILE__, __LINE__ );
 	}
@@ -637,6 +719,7 @@ void hako_pt_destroy( hako_pt* pt )
 	dfree( pt->rgba8, s );
 	dfree( pt->pmj, s );
 	dfree( pt->pathL, s );
+	dfree( pt->hitQueue, s );
 	dfree( pt->counters, s );
 	cudaStreamSynchronize( s );
 	delete pt;
@@ -791,12 +874,16 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 	if( pt->pathCap < nPaths )
 	{
 		dfree( pt->pathL, s );
+		dfree( pt->hitQueue, s );
 		pt->pathL = nullptr;
+		pt->hitQueue = nullptr;
 		pt->pathCap = 0;
 		HAKO_TRY( dalloc( ctx, &pt->pathL, nPaths, s ) );
+		HAKO_TRY( dalloc( ctx, &pt->hitQueue, nPaths, s ) );
 		pt->pathCap = nPaths;
 	}
-	HAKO_CUDA( cudaMemsetAsync( pt->counters, 0, sizeof( unsigned long long ), s ) ); // the work counter; [1] keeps counting rays
+	HAKO_CUDA( cudaMemsetAsync( pt->counters, 0, sizeof( unsigned long long ), s ) );	  // the work counter; [1] keeps counting rays
+	HAKO_CUDA( cudaMemsetAsync( pt->counters + 2, 0, sizeof( unsigned long long ), s ) ); // hit-queue length
 
 	PtParams p;
 	p.tree = o->view();
@@ -805,20 +892,35 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 	p.pmj = pt->pmj;
 	p.pathL = pt->pathL;
 	p.counters = pt->counters;
+	p.hitQueue = pt->hitQueue;
 	p.w = pt->w, p.h = pt->h, p.y0 = y0;
 	p.nPaths = (uint32_t)nPaths;
 	p.iteration = (uint32_t)iteration;
 	p.maxDepth = maxDepth;
 
 	// persistent grid: as many CTAs as are co-resident on the chip
-	static int ctasPerSm = 0;
-	if( ctasPerSm == 0 )
+	static int ctasPerSm[2] = { 0, 0 };
+	auto kWhole = pathTraceKernel<false>;
+	auto kContinue = pathTraceKernel<true>;
+	const int variant = pt->wavefront ? 1 : 0;
+	if( ctasPerSm[variant] == 0 )
 	{
-		HAKO_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &ctasPerSm, pathTraceKernel, PT_BLOCK, 0 ) );
-		if( ctasPerSm < 1 ) ctasPerSm = 1;
+		if( variant )
+			HAKO_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &ctasPerSm[1], kContinue, PT_BLOCK, 0 ) );
+		else
+			HAKO_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &ctasPerSm[0], kWhole, PT_BLOCK, 0 ) );
+		if( ctasPerSm[variant] < 1 ) ctasPerSm[variant] = 1;
 	}
-	const uint32_t grid = (uint32_t)std::min<uint64_t>( (uint64_t)ctasPerSm * ctx->smCount, ( nPaths + PT_BLOCK - 1 ) / PT_BLOCK );
-	HAKO_LAUNCH( ctx, pathTraceKernel, grid, PT_BLOCK, 0, s, p );
+	const uint32_t grid = (uint32_t)std::min<uint64_t>( (uint64_t)ctasPerSm[variant] * ctx->smCount, ( nPaths + PT_BLOCK - 1 ) / PT_BLOCK );
+	if( variant )
+	{
+		// wave 1: every primary ray (dense launch, 4x4-pixel tiles); wave 2: the paths that hit, from the compacted queue
+		const uint32_t tiles = ( ( (uint32_t)pt->w + 3u ) / 4u ) * ( ( (uint32_t)( y1 - y0 ) + 3u ) / 4u );
+		HAKO_LAUNCH( ctx, primaryWaveKernel, tiles, PT_BLOCK, 0, s, p, y1 - y0 );
+		HAKO_LAUNCH( ctx, kContinue, grid, PT_BLOCK, 0, s, p );
+	}
+	else
+		HAKO_LAUNCH( ctx, kWhole, grid, PT_BLOCK, 0, s, p );
 	HAKO_LAUNCH( ctx, accumulateKernel, divUp( nPixels, 256 ), 256, 0, s, pt->pathL, pt->accum + (size_t)y0 * pt->w, nPixels );
 	return HAKO_OK;
 }
