@@ -29,6 +29,8 @@ using namespace hako;
 #define PT_CHUNK 256	  // paths fetched from the global counter per warp-level atomic
 #define PMJ_LENGTH 4096	  // pmjSampler.hpp:107-111
 #define PMJ_NSEQ 128
+#define PT_COUNTERS 64	  // [0] work, [1] rays traced, [2 + v] live paths at vertex v, [32 + v] ray work counter of wave v
+#define PT_MAX_WAVES 28
 
 struct hako_pt
 {
@@ -48,10 +50,19 @@ struct hako_pt
 	float4* pathL = nullptr;
 	uint64_t pathCap = 0;
 	unsigned long long* counters = nullptr; // [0] work counter, [1] rays traced
-	uint32_t* hitQueue = nullptr;			// path indices whose primary ray hit (wavefront mode), capacity pathCap
-	// 1: wavefront -- primaryWaveKernel + pathTraceKernel<true>; 0 (default): single persistent kernel (pathTraceKernel<false>).
-	// HAKO_PT_WAVEFRONT overrides (A/B knob, read at create time).
-	int wavefront = 0;
+	uint32_t* hitQueue = nullptr;			// path indices whose primary ray hit (wavefront modes), capacity pathCap
+	// full wavefront mode: ping-pong vertex lists, ray directions, ray results; capacity waveCap live paths (3 rays each)
+	void* waveV[2] = { nullptr, nullptr };
+	float4* waveDir[2] = { nullptr, nullptr };
+	float4* waveRes = nullptr;
+	uint64_t waveCap = 0;
+	int waveRefillMin = 24, waveBurst = 16; // traceWaveKernel knobs (HAKO_PT_REFILL_MIN / HAKO_PT_BURST); B200 sweep in profiles/r1f_pt_sweep.txt
+	int waveTraceCtas = 5;
+	uint64_t waveBandPaths = 16u << 20;	  // paths per internal row band of a step (bounds the wavefront buffers)
+	// 0: single persistent kernel (pathTraceKernel<false>); 1: primaryWaveKernel + pathTraceKernel<true>;
+	// 2: full wavefront (primaryWaveKernel, then shadeWaveKernel / traceWaveKernel per vertex).  HAKO_PT_WAVEFRONT overrides
+	// (A/B knob, read at create time).
+	int wavefront = 2;
 };
 
 namespace
@@ -271,6 +282,51 @@ __device__ __forceinline__ void startPath( const PtParams& p, PathState& s, uint
 	s.kind = RAY_PRIMARY;
 }
 
+// ---- the pieces of one path vertex (voxKernel.cu:678-759), shared by the persistent kernel and the wavefront kernels ----
+__device__ __forceinline__ V3 emissionOf( const PtParams& p, uint32_t vIndex ) { return rawReflectance( loadAttrib( p.tree, vIndex ).y ); }
+// a camera ray that hits an emitter sees it unscaled, :686-688
+__device__ __forceinline__ void addPrimaryHit( const PtParams& p, PathState& s, uint32_t vIndex ) { s.L = s.L + s.T * emissionOf( p, vIndex ); }
+// :712-715
+__device__ __forceinline__ void addShadowResult( PathState& s, bool hit )
+{
+	if( !hit ) s.L = s.L + s.pending;
+}
+// :733-736
+__device__ __forceinline__ void addExtraResult( const PtParams& p, const uint32_t nExtra, PathState& s, bool hit, uint32_t vIndex )
+{
+	if( hit ) s.L = s.L + s.T * ( emissionOf( p, vIndex ) * p.tree.emissionScale ) / (float)( 1u + nExtra );
+}
+// :750-758; s.depth is the index of the vertex the bounce ray left from
+__device__ __forceinline__ void addBounceResult( const PtParams& p, const uint32_t nExtra, PathState& s, bool hit, uint32_t vIndex )
+{
+	if( hit ) s.L = s.L + s.T * ( emissionOf( p, vIndex ) * p.tree.emissionScale ) * ( s.depth == 0 ? 1.0f / (float)( 1u + nExtra ) : 1.0f );
+}
+// the surface point the path ray (s.o, s.d) just hit, :693-716: moves s.o to hitP, sets hitN, multiplies the throughput, and --
+// when the environment is on -- draws the light sample: s.pending is its contribution, `shadowDir` the shadow ray (from hitP)
+__device__ __forceinline__ void shadeSurface( const PtParams& p, const bool envOn, PathState& s, float t, int nMajor, uint32_t vIndex, V3* shadowDir )
+{
+	const V3 R = rawReflectance( loadAttrib( p.tree, vIndex ).x );
+	s.hitN = getHitN( nMajor, s.d );
+	s.o = s.o + s.d * t; // hitP: every following ray of this vertex starts here, without an epsilon
+	if( envOn )
+	{
+		const float2 u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+		const float2 u23 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+		V3 dir, emissive;
+		float pdf;
+		hdriImportanceSample( p.env, &dir, &emissive, &pdf, s.hitN, u01.x, u01.y, u23.x, u23.y );
+		s.pending = s.T * ( R / HAKO_PI ) * smax( dot( s.hitN, dir ), 0.0f ) * emissive / pdf;
+		*shadowDir = dir;
+	}
+	s.T = s.T * R;
+}
+// the cosine-weighted direction of the extra-implicit (:720-731) and bounce (:741-748) rays
+__device__ __forceinline__ V3 lambertDir( const PtParams& p, PathState& s )
+{
+	const float2 u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
+	return sampleLambertian( u01.x, u01.y, s.hitN );
+}
+
 // consume the result of the ray a lane just traced and set up its next ray (or finish the path: kind = LANE_IDLE)
 __device__ __forceinline__ void shadeVertex( const PtParams& p, const bool envOn, const uint32_t nExtra, PathState& s, const bool hit, const float t,
 											 const int nMajor, const uint32_t vIndex )
@@ -285,58 +341,43 @@ __device__ __forceinline__ void shadeVertex( const PtParams& p, const bool envOn
 		}
 		else
 		{
-			s.L = s.L + s.T * rawReflectance( loadAttrib( p.tree, vIndex ).y ); // unscaled, :686-688
+			addPrimaryHit( p, s, vIndex );
 			next = NEXT_SHADE;
 		}
 	}
 	else if( s.kind == RAY_SHADOW )
 	{
-		if( !hit ) s.L = s.L + s.pending; // :712-715
+		addShadowResult( s, hit );
 		next = ( s.depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
 	}
 	else if( s.kind == RAY_EXTRA )
 	{
-		if( hit ) // :733-736
-			s.L = s.L + s.T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) / (float)( 1u + nExtra );
+		addExtraResult( p, nExtra, s, hit, vIndex );
 		next = NEXT_GEN_BOUNCE;
 	}
 	else
 	{
-		if( hit ) // :750-758
-			s.L = s.L + s.T * ( rawReflectance( loadAttrib( p.tree, vIndex ).y ) * p.tree.emissionScale ) * ( s.depth == 0 ? 1.0f / (float)( 1u + nExtra ) : 1.0f );
+		addBounceResult( p, nExtra, s, hit, vIndex );
 		s.depth++;
 		next = ( hit && s.depth < p.maxDepth ) ? NEXT_SHADE : NEXT_FINISH;
 	}
 
 	if( next == NEXT_SHADE )
 	{
-		// surface point of the path ray (o, d) that just hit: :693-695
-		const V3 R = rawReflectance( loadAttrib( p.tree, vIndex ).x );
-		s.hitN = getHitN( nMajor, s.d );
-		s.o = s.o + s.d * t; // hitP: every following ray of this vertex starts here, without an epsilon
+		V3 dir;
+		shadeSurface( p, envOn, s, t, nMajor, vIndex, &dir );
 		if( envOn )
 		{
-			const float2 u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
-			const float2 u23 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
-			V3 dir, emissive;
-			float pdf;
-			hdriImportanceSample( p.env, &dir, &emissive, &pdf, s.hitN, u01.x, u01.y, u23.x, u23.y );
-			s.pending = s.T * ( R / HAKO_PI ) * smax( dot( s.hitN, dir ), 0.0f ) * emissive / pdf;
-			s.T = s.T * R;
 			s.d = dir;
 			s.kind = RAY_SHADOW;
 			next = NEXT_TRACE;
 		}
 		else
-		{
-			s.T = s.T * R;
 			next = ( s.depth == 0 && nExtra ) ? NEXT_GEN_EXTRA : NEXT_GEN_BOUNCE;
-		}
 	}
 	if( next == NEXT_GEN_EXTRA || next == NEXT_GEN_BOUNCE )
 	{
-		const float2 u01 = pmjSample2d( p.pmj, s.spp, s.dim++, s.stream );
-		s.d = sampleLambertian( u01.x, u01.y, s.hitN );
+		s.d = lambertDir( p, s );
 		s.kind = ( next == NEXT_GEN_EXTRA ) ? RAY_EXTRA : RAY_BOUNCE;
 	}
 	else if( next == NEXT_FINISH )
@@ -392,7 +433,7 @@ __device__ __forceinline__ void refillIdleLanes( const PtParams& p, const bool e
 // FROM_QUEUE = false: the whole path, primary ray included (single-kernel mode).
 // FROM_QUEUE = true : the continuation of the paths whose primary ray hit (second wave of the wavefront mode).
 template <bool FROM_QUEUE>
-__global__ void __launch_bounds__( PT_BLOCK ) pathTraceKernel( const PtParams p )
+__global__ void __launch_bounds__( PT_BLOCK, 4 ) pathTraceKernel( const PtParams p )
 {
 	const uint32_t lane = threadIdx.x & 31u;
 	const bool envOn = 0.0f < p.env.scale && p.env.pixels != nullptr; // HDRI::isEnabled
@@ -474,6 +515,238 @@ __global__ void __launch_bounds__( PT_BLOCK ) primaryWaveKernel( const PtParams 
 		if( hit ) p.hitQueue[base + __popc( hitMask & ( ( 1u << lane ) - 1u ) )] = path;
 	}
 	if( lane == 0 && insideMask ) atomicAdd( p.counters + 1, (unsigned long long)__popc( insideMask ) );
+}
+
+// ================= full wavefront mode (pt->wavefront == 2) =================
+// After primaryWaveKernel the live paths are a compact list.  Per path vertex v = 0, 1, ...:
+//   shadeWaveKernel( v )  one thread per live path: consumes the results of the rays of vertex v-1 (shadow / extra / bounce),
+//                         finishes the path or shades the new surface point and writes ALL rays of vertex v at once -- the
+//                         directions of the shadow, extra-implicit and bounce rays depend only on the sampler, not on each
+//                         other's results (:697-748) -- into a dense ray list (R(v) rays per live path); survivors are
+//                         compacted by warp ballot into the next vertex list;
+//   traceWaveKernel( v )  persistent, traversal only: a lane whose ray ended takes the next ray from the list as soon as enough
+//                         lanes of its warp are idle (ballot -> rank -> per-warp chunk from a global counter), so long rays no
+//                         longer hold 31 lanes hostage.  (profiles/r1e: in the single persistent kernel a warp round lasts 233
+//                         steps while the mean secondary ray takes 92; 12 of 32 lanes are active on average.)
+// The arithmetic per path is the same sequence of fp32 expressions as in shadeVertex, so the accumulators are bit-identical
+// across the three modes (tests/test_gpu_pt.py::test_pt_modes_identical).
+struct WaveVertex // 64 B
+{
+	float4 a; // hitP.xyz, path index
+	float4 b; // T.xyz
+	float4 c; // L.xyz
+	float4 d; // pending.xyz
+};
+struct WaveParams
+{
+	const WaveVertex* vin; // vertex list of v-1 (v > 0)
+	WaveVertex* vout;	   // vertex list of v
+	const float4* dirIn;   // ray directions of vertex v-1: [k * nIn + slot] (kind-major: a warp of the trace kernel gets rays of ONE kind)
+	const float4* resIn;   // their results: { t, vIndex, nMajor, hit }
+	float4* dirOut;		   // ray directions of vertex v: [k * stride + slot], stride = nIn (an upper bound of the survivors)
+	const unsigned long long* nIn; // live paths at vertex v; nIn[-1] = live paths at v-1 = the stride of dirIn / resIn
+	unsigned long long* nOut;
+	int v;	  // index of the vertex being created (0 = the primary hit)
+	int rIn;  // rays per live path at vertex v-1
+	int rOut; // rays per live path at vertex v
+};
+// rays per vertex: [shadow] [extra, first vertex only] bounce
+__host__ __device__ __forceinline__ int waveRaysPerVertex( bool envOn, uint32_t nExtra, int v ) { return ( envOn ? 1 : 0 ) + ( ( v == 0 && nExtra ) ? 1 : 0 ) + 1; }
+// sampler dimension at the start of vertex v: 2 camera dimensions, then per vertex 2 (light sample) + [1 extra] + 1 bounce
+__device__ __forceinline__ uint32_t waveDimAt( bool envOn, uint32_t nExtra, int v ) { return 2u + (uint32_t)v * ( envOn ? 3u : 1u ) + ( ( v > 0 && nExtra ) ? 1u : 0u ); }
+
+__global__ void __launch_bounds__( 256 ) shadeWaveKernel( const PtParams p, const WaveParams wp )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const bool envOn = 0.0f < p.env.scale && p.env.pixels != nullptr;
+	const uint32_t nExtra = p.tree.hasEmission ? 1u : 0u;
+	const uint32_t nIn = (uint32_t)*wp.nIn;
+	const size_t strideIn = wp.v > 0 ? (size_t)wp.nIn[-1] : 0, strideOut = nIn;
+	// whole warps iterate together (ballot compaction below)
+	for( uint32_t base = ( blockIdx.x * blockDim.x + threadIdx.x ) & ~31u; base < nIn; base += gridDim.x * blockDim.x )
+	{
+		const uint32_t i = base + lane;
+		bool alive = false;
+		PathState s;
+		float t = 0.0f;
+		int nMajor = 0;
+		uint32_t vIndex = 0;
+		if( i < nIn )
+		{
+			if( wp.v == 0 )
+			{
+				const uint32_t path = __ldg( p.hitQueue + i );
+				const float4 rec = __ldcs( p.pathL + path ); // { t, vIndex, nMajor, - } of the primary hit
+				startPath( p, s, path );
+				t = rec.x, vIndex = __float_as_uint( rec.y ), nMajor = __float_as_int( rec.z );
+				addPrimaryHit( p, s, vIndex );
+				alive = true;
+			}
+			else
+			{
+				const WaveVertex vx = wp.vin[i];
+				s.path = __float_as_uint( vx.a.w );
+				s.o = { vx.a.x, vx.a.y, vx.a.z };
+				s.T = { vx.b.x, vx.b.y, vx.b.z };
+				s.L = { vx.c.x, vx.c.y, vx.c.z };
+				s.pending = { vx.d.x, vx.d.y, vx.d.z };
+				s.depth = wp.v - 1;
+				int k = 0;
+				if( envOn )
+				{
+					const float4 r = __ldcs( wp.resIn + (size_t)( k++ ) * strideIn + i );
+					addShadowResult( s, r.w != 0.0f );
+				}
+				if( s.depth == 0 && nExtra )
+				{
+					const float4 r = __ldcs( wp.resIn + (size_t)( k++ ) * strideIn + i );
+					addExtraResult( p, nExtra, s, r.w != 0.0f, __float_as_uint( r.y ) );
+				}
+				const float4 r = __ldcs( wp.resIn + (size_t)k * strideIn + i );
+				const float4 bd = __ldcs( wp.dirIn + (size_t)k * strideIn + i );
+				const bool hit = r.w != 0.0f;
+				addBounceResult( p, nExtra, s, hit, __float_as_uint( r.y ) );
+				s.depth++;
+				if( hit && s.depth < p.maxDepth )
+				{
+					alive = true;
+					s.d = { bd.x, bd.y, bd.z };
+					t = r.x, vIndex = __float_as_uint( r.y ), nMajor = __float_as_int( r.z );
+					// re-derive the sampler state of the path
+					const uint32_t localPixel = s.path / PT_SPP, localSpp = s.path % PT_SPP;
+					const uint32_t x = localPixel % (uint32_t)p.w, y = (uint32_t)p.y0 + localPixel / (uint32_t)p.w;
+					s.spp = p.iteration * PT_SPP + localSpp;
+					Murmur32 hs( 0 );
+					hs.combine( y * (uint32_t)p.w + x );
+					s.stream = hs.getHash();
+				}
+				else
+					p.pathL[s.path] = make_float4( s.L.x, s.L.y, s.L.z, 0.0f );
+			}
+		}
+		// survivors: ballot -> rank -> one atomicAdd per warp
+		const uint32_t aliveMask = __ballot_sync( 0xFFFFFFFFu, alive );
+		if( !aliveMask ) continue;
+		unsigned long long slot0 = 0;
+		if( lane == 0 ) slot0 = atomicAdd( wp.nOut, (unsigned long long)__popc( aliveMask ) );
+		slot0 = __shfl_sync( 0xFFFFFFFFu, slot0, 0 );
+		if( alive )
+		{
+		const size_t slot = (size_t)slot0 + __popc( aliveMask & ( ( 1u << lane ) - 1u ) );
+		s.dim = waveDimAt( envOn, nExtra, wp.v );
+		s.depth = wp.v;
+		V3 dir = {};
+		shadeSurface( p, envOn, s, t, nMajor, vIndex, &dir );
+		float4* dout = wp.dirOut + slot;
+		if( envOn )
+		{
+			*dout = make_float4( dir.x, dir.y, dir.z, 0.0f );
+			dout += strideOut;
+		}
+		if( wp.v == 0 && nExtra )
+		{
+			const V3 e = lambertDir( p, s );
+			*dout = make_float4( e.x, e.y, e.z, 0.0f );
+			dout += strideOut;
+		}
+		const V3 bnc = lambertDir( p, s );
+		*dout = make_float4( bnc.x, bnc.y, bnc.z, 0.0f );
+		WaveVertex o;
+		o.a = make_float4( s.o.x, s.o.y, s.o.z, __uint_as_float( s.path ) );
+		o.b = make_float4( s.T.x, s.T.y, s.T.z, 0.0f );
+		o.c = make_float4( s.L.x, s.L.y, s.L.z, 0.0f );
+		o.d = make_float4( s.pending.x, s.pending.y, s.pending.z, 0.0f );
+		wp.vout[slot] = o;
+		}
+	}
+}
+
+struct TraceWaveParams
+{
+	const WaveVertex* vertices;
+	const float4* dirs;
+	float4* results;
+	const unsigned long long* nVertices; // nVertices[-1] = live paths one vertex earlier = pitch of dirs / results
+	unsigned long long* work; // ray index counter of this wave (zeroed)
+	unsigned long long* rays; // total rays traced
+	int raysPerVertex;
+	int shadowFirst; // ray 0 of every vertex is a shadow ray (any-hit semantics: no voxel-rank accumulation)
+	int refillMin;	 // refill when at least this many lanes of the warp are idle
+	int burst;		 // traversal steps between two refill checks
+};
+template <int MIN_CTAS>
+__global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const OctreeView tree, const TraceWaveParams tp )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t nVertices = (uint32_t)*tp.nVertices;
+	const uint32_t stride = (uint32_t)tp.nVertices[-1]; // live paths one vertex earlier: the pitch of the kind-major ray arrays
+	const uint32_t nRays = nVertices * (uint32_t)tp.raysPerVertex;
+	uint32_t wNext = 0, wEnd = 0;
+	bool drained = false;
+	Traversal tr;
+	TravStack stk;
+	bool flying = false, shadow = false;
+	uint32_t addr = 0; // k * stride + slot of the ray in flight
+	uint32_t traced = 0;
+	for( ;; )
+	{
+		const uint32_t idleMask = __ballot_sync( 0xFFFFFFFFu, !flying );
+		if( idleMask == 0xFFFFFFFFu || ( !drained && __popc( idleMask ) >= tp.refillMin ) )
+		{
+			if( !drained && wNext == wEnd )
+			{
+				uint32_t base = 0;
+				if( lane == 0 ) base = (uint32_t)atomicAdd( tp.work, (unsigned long long)PT_CHUNK );
+				base = __shfl_sync( 0xFFFFFFFFu, base, 0 );
+				if( base >= nRays )
+					drained = true;
+				else
+				{
+					wNext = base;
+					wEnd = min( base + PT_CHUNK, nRays );
+				}
+			}
+			if( drained )
+			{
+				if( idleMask == 0xFFFFFFFFu ) break;
+			}
+			else
+			{
+				const uint32_t rank = __popc( idleMask & ( ( 1u << lane ) - 1u ) );
+				const uint32_t avail = wEnd - wNext;
+				if( !flying && rank < avail )
+				{
+					const uint32_t ray = wNext + rank;
+					const uint32_t k = ray / nVertices, slot = ray - k * nVertices;
+					addr = k * stride + slot;
+					const float4 o = __ldg( &tp.vertices[slot].a );
+					const float4 d = __ldcs( tp.dirs + addr );
+					shadow = tp.shadowFirst && k == 0;
+					flying = tr.begin( tree, V3{ o.x, o.y, o.z }, V3{ d.x, d.y, d.z } );
+					if( !flying ) __stcs( tp.results + addr, make_float4( 0.0f, 0.0f, 0.0f, 0.0f ) ); // misses the root box
+					traced++;
+				}
+				wNext += min( (uint32_t)__popc( idleMask ), avail );
+			}
+		}
+		if( flying )
+		{
+#pragma unroll 1
+			for( int it = 0; it < tp.burst; it++ )
+			{
+				const int r = tr.step( tree, shadow, stk );
+				if( r == TRAV_CONTINUE ) continue;
+				flying = false;
+				if( r == TRAV_HIT )
+					__stcs( tp.results + addr, make_float4( tr.t, __uint_as_float( tr.skipped ), __int_as_float( tr.nMajor ), 1.0f ) );
+				else
+					__stcs( tp.results + addr, make_float4( 0.0f, 0.0f, 0.0f, 0.0f ) );
+				break;
+			}
+		}
+	}
+	for( int off = 16; off; off >>= 1 ) traced += __shfl_down_sync( 0xFFFFFFFFu, traced, off );
+	if( lane == 0 && traced ) atomicAdd( tp.rays, (unsigned long long)traced );
 }
 
 // per-pixel reduction in localSpp order, then `frameBuffer += `, voxKernel.cu:763-774
@@ -687,16 +960,20 @@ int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out )
 	hako_pt* pt = new hako_pt();
 	pt->ctx = ctx;
 	if( const char* e = getenv( "HAKO_PT_WAVEFRONT" ) ) pt->wavefront = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_REFILL_MIN" ) ) pt->waveRefillMin = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_BURST" ) ) pt->waveBurst = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_TRACE_CTAS" ) ) pt->waveTraceCtas = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_BAND_PATHS" ) ) pt->waveBandPaths = strtoull( e, nullptr, 10 );
 	std::vector<float> table( (size_t)2 * PMJ_LENGTH * PMJ_NSEQ );
 	HostPCG32 rng;
 	rng.setup( 0, 2525 ); // pmjSampler.hpp:116-117
 	for( int i = 0; i < PMJ_NSEQ; i++ ) generatePMJ02( PMJ_LENGTH, table.data() + (size_t)2 * PMJ_LENGTH * i, rng );
 	int r = dalloc( ctx, &pt->pmj, table.size(), s );
-	if( r == 0 ) r = dalloc( ctx, &pt->counters, 4, s );
+	if( r == 0 ) r = dalloc( ctx, &pt->counters, PT_COUNTERS, s );
 	if( r == 0 )
 	{
 		cudaError_t e = cudaMemcpyAsync( pt->pmj, table.data(), table.size() * sizeof( float ), cudaMemcpyHostToDevice, s );
-		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, 4 * sizeof( unsigned long long ), s );
+		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, PT_COUNTERS * sizeof( unsigned long long ), s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s ); // `table` dies with this scope
 		if( e != cudaSuccess ) r = cudaFail( e, "PMJ upload", __FILE__, __LINE__ );
 	}
@@ -720,6 +997,8 @@ void hako_pt_destroy( hako_pt* pt )
 	dfree( pt->pmj, s );
 	dfree( pt->pathL, s );
 	dfree( pt->hitQueue, s );
+	for( int i = 0; i < 2; i++ ) dfree( pt->waveV[i], s ), dfree( pt->waveDir[i], s );
+	dfree( pt->waveRes, s );
 	dfree( pt->counters, s );
 	cudaStreamSynchronize( s );
 	delete pt;
@@ -898,6 +1177,91 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 	p.iteration = (uint32_t)iteration;
 	p.maxDepth = maxDepth;
 
+	const bool envOn = p.env.pixels != nullptr && 0.0f < p.env.scale;
+	const uint32_t nExtra = o->hasEmission ? 1u : 0u;
+	const int waves = std::max( maxDepth, 1 ); // vertices per path: the primary hit is always shaded (voxKernel.cu:691-693)
+	if( pt->wavefront == 2 && waves <= PT_MAX_WAVES )
+	{
+		// full wavefront, in row bands of at most waveBandPaths paths so that the live-path buffers stay bounded even when
+		// every primary ray hits
+		const uint32_t rowsPerBand = (uint32_t)std::max<uint64_t>( 4, ( pt->waveBandPaths / ( (uint64_t)pt->w * PT_SPP ) ) & ~3ull );
+		const uint64_t bandCap = std::min<uint64_t>( nPaths, (uint64_t)rowsPerBand * pt->w * PT_SPP );
+		if( pt->waveCap < bandCap )
+		{
+			for( int i = 0; i < 2; i++ )
+			{
+				dfree( pt->waveV[i], s ), dfree( pt->waveDir[i], s );
+				pt->waveV[i] = nullptr, pt->waveDir[i] = nullptr;
+			}
+			dfree( pt->waveRes, s );
+			pt->waveRes = nullptr;
+			pt->waveCap = 0;
+			for( int i = 0; i < 2; i++ )
+			{
+				WaveVertex* v = nullptr;
+				HAKO_TRY( dalloc( ctx, &v, bandCap, s ) );
+				pt->waveV[i] = v;
+				HAKO_TRY( dalloc( ctx, &pt->waveDir[i], bandCap * 3, s ) );
+			}
+			HAKO_TRY( dalloc( ctx, &pt->waveRes, bandCap * 3, s ) );
+			pt->waveCap = bandCap;
+		}
+		// occupancy target of the trace kernel: 5 CTAs/SM = 48 registers, 6 = 40, 8 = 32 (HAKO_PT_TRACE_CTAS)
+		auto kTrace5 = traceWaveKernel<5>;
+		auto kTrace6 = traceWaveKernel<6>;
+		auto kTrace8 = traceWaveKernel<8>;
+		const int occ = pt->waveTraceCtas >= 8 ? 8 : ( pt->waveTraceCtas >= 6 ? 6 : 5 );
+		const uint32_t traceGrid = (uint32_t)occ * ctx->smCount;
+		const uint32_t shadeGrid = 8u * ctx->smCount;
+		for( int b0 = y0; b0 < y1; b0 += (int)rowsPerBand )
+		{
+			const int b1 = std::min( y1, b0 + (int)rowsPerBand );
+			PtParams q = p;
+			q.y0 = b0;
+			q.pathL = pt->pathL + (size_t)( b0 - y0 ) * pt->w * PT_SPP;
+			q.nPaths = (uint32_t)( (uint64_t)( b1 - b0 ) * pt->w * PT_SPP );
+			// live counts [2 .. 2 + waves] and the waves' ray counters [32 .. 32 + waves)
+			HAKO_CUDA( cudaMemsetAsync( pt->counters + 2, 0, ( PT_COUNTERS - 2 ) * sizeof( unsigned long long ), s ) );
+			const uint32_t tiles = ( ( (uint32_t)pt->w + 3u ) / 4u ) * ( ( (uint32_t)( b1 - b0 ) + 3u ) / 4u );
+			HAKO_LAUNCH( ctx, primaryWaveKernel, tiles, PT_BLOCK, 0, s, q, b1 - b0 );
+			for( int v = 0; v <= waves; v++ )
+			{
+				// shade( v ): consumes the rays of vertex v-1; for v == waves every path ends (depth == maxDepth)
+				WaveParams wp;
+				wp.vin = (const WaveVertex*)pt->waveV[( v + 1 ) & 1];
+				wp.vout = (WaveVertex*)pt->waveV[v & 1];
+				wp.dirIn = pt->waveDir[( v + 1 ) & 1];
+				wp.dirOut = pt->waveDir[v & 1];
+				wp.resIn = pt->waveRes;
+				wp.nIn = pt->counters + 2 + v;
+				wp.nOut = pt->counters + 2 + v + 1;
+				wp.v = v;
+				wp.rIn = v > 0 ? waveRaysPerVertex( envOn, nExtra, v - 1 ) : 0;
+				wp.rOut = waveRaysPerVertex( envOn, nExtra, v );
+				HAKO_LAUNCH( ctx, shadeWaveKernel, shadeGrid, 256, 0, s, q, wp );
+				if( v == waves ) break;
+				TraceWaveParams tp;
+				tp.vertices = wp.vout;
+				tp.dirs = wp.dirOut;
+				tp.results = pt->waveRes;
+				tp.nVertices = wp.nOut;
+				tp.work = pt->counters + 32 + v;
+				tp.rays = pt->counters + 1;
+				tp.raysPerVertex = wp.rOut;
+				tp.shadowFirst = envOn ? 1 : 0;
+				tp.refillMin = std::max( 1, std::min( 32, pt->waveRefillMin ) );
+				tp.burst = std::max( 1, pt->waveBurst );
+				if( occ == 8 )
+					HAKO_LAUNCH( ctx, kTrace8, traceGrid, 256, 0, s, q.tree, tp );
+				else if( occ == 6 )
+					HAKO_LAUNCH( ctx, kTrace6, traceGrid, 256, 0, s, q.tree, tp );
+				else
+					HAKO_LAUNCH( ctx, kTrace5, traceGrid, 256, 0, s, q.tree, tp );
+			}
+		}
+	}
+	else
+	{
 	// persistent grid: as many CTAs as are co-resident on the chip
 	static int ctasPerSm[2] = { 0, 0 };
 	auto kWhole = pathTraceKernel<false>;
@@ -921,6 +1285,7 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 	}
 	else
 		HAKO_LAUNCH( ctx, kWhole, grid, PT_BLOCK, 0, s, p );
+	}
 	HAKO_LAUNCH( ctx, accumulateKernel, divUp( nPixels, 256 ), 256, 0, s, pt->pathL, pt->accum + (size_t)y0 * pt->w, nPixels );
 	return HAKO_OK;
 }

@@ -150,6 +150,43 @@ def test_step_is_deterministic_and_shards_by_rows(hk, ctx, pt, scene):
     assert (full[..., 3] == 64).all()
 
 
+@pytest.mark.parametrize("with_env,with_emission,max_depth", [(True, True, 4), (True, False, 8), (False, True, 3), (True, True, 0)])
+def test_pt_modes_identical(hk, ctx, pt, scene, monkeypatch, with_env, with_emission, max_depth):
+    """the single persistent kernel, the primary-wave + continuation pair and the full wavefront (also split into row bands,
+    with different refill knobs) evaluate the same fp32 expressions per path: accumulators and ray counts are bit-identical"""
+    W, H = 100, 52          # not a multiple of the 4x4 primary tiles
+    s = scene
+    emi = s["emi"] if with_emission else np.zeros_like(s["emi"])
+    pt.updateScene(s["tris"], s["col"], emi, None, s["origin"], float(s["dps"]), s["grid"])
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR=0.02)
+    img = procedural_hdri(128, 64)
+    outs = []
+    for env in ({"HAKO_PT_WAVEFRONT": "0"}, {"HAKO_PT_WAVEFRONT": "1"}, {"HAKO_PT_WAVEFRONT": "2"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BAND_PATHS": str(W * 16 * 12), "HAKO_PT_REFILL_MIN": "1", "HAKO_PT_BURST": "3"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_REFILL_MIN": "32", "HAKO_PT_BURST": "1"}):
+        for k in ("HAKO_PT_WAVEFRONT", "HAKO_PT_BAND_PATHS", "HAKO_PT_REFILL_MIN", "HAKO_PT_BURST"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        p2 = hk.PathTracer(ctx).setup()      # the knobs are read at create time
+        p2.m_intersectorOctreeGPU = pt.m_intersectorOctreeGPU
+        if with_env:
+            p2.loadHDRI(None, img)
+        p2.maxDepth = max_depth
+        p2.resizeFrameBufferIfNeeded(None, W, H)
+        p2.ray_count(reset=True)
+        for it in range(2):
+            p2.step(None, cam, iteration=it)
+        p2.step(None, cam, rows=(5, 31), iteration=2)
+        outs.append((p2.accumulators().copy(), p2.ray_count()))
+        p2.m_intersectorOctreeGPU = hk.IntersectorOctreeGPU(ctx)
+        p2.cleanUp()
+    for acc, rays in outs[1:]:
+        assert np.array_equal(acc.view(np.uint32), outs[0][0].view(np.uint32))
+        assert rays == outs[0][1]
+    assert outs[0][1] > W * H * 16 * 2
+
+
 def test_resolve_matches_oracle(hk, ctx, pt, oracle, scene):
     W, H = 64, 40
     s = scene

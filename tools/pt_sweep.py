@@ -12,9 +12,10 @@ g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps),
 env = procedural_hdri(2048, 1024)
 cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR=0.0)
 ref = None
-variants = [0, 1]
-for wf in variants:
-    os.environ['HAKO_PT_WAVEFRONT'] = str(wf)
+variants = [(0, 8, 8, 5)] + [(2, r, b, c) for c in (5, 6, 8) for (r, b) in ((8, 16), (16, 16), (24, 16), (16, 32), (28, 32), (32, 16))]
+if len(sys.argv) > 2: variants = [(0, 8, 8, 5), (2, 16, 16, 5)]
+for wf, rmin, burst, ctas in variants:
+    os.environ['HAKO_PT_WAVEFRONT'] = str(wf); os.environ['HAKO_PT_REFILL_MIN'] = str(rmin); os.environ['HAKO_PT_BURST'] = str(burst); os.environ['HAKO_PT_TRACE_CTAS'] = str(ctas)
     pt = hk.PathTracer(ctx).setup()
     own = pt.m_intersectorOctreeGPU; pt.m_intersectorOctreeGPU = g
     pt.loadHDRI(None, env); pt.resizeFrameBufferIfNeeded(None, W, H)
@@ -31,5 +32,5 @@ for wf in variants:
         same = None
         if (depth) in ref: same = bool(np.array_equal(ref[depth].view(np.uint32), acc.view(np.uint32)))
         else: ref[depth] = acc
-        print('wavefront %d depth %d: %.2f ms/step = %.3f ms/spp, %.1f Mrays/s, identical_to_variant0 %s' % (wf, depth, ms, ms / 16, rays / ms / 1e3, same), flush=True)
+        print('wavefront %d refillMin %2d burst %2d ctas %d depth %d: %.2f ms/step = %.3f ms/spp, %.1f Mrays/s, identical_to_variant0 %s' % (wf, rmin, burst, ctas, depth, ms, ms / 16, rays / ms / 1e3, same), flush=True)
     pt.m_intersectorOctreeGPU = own; pt.cleanUp()
