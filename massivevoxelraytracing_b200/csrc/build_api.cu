@@ -33,12 +33,9 @@ static int log2i( int v )
 	while( ( 1 << l ) < v ) l++;
 	return l;
 }
-// IntersectorOctreeGPU.hpp:118: sort bits = next multiple of 8 of 3 * log2( gridRes )
-static int sortEndBit( int gridRes )
-{
-	int bits = 3 * log2i( gridRes );
-	return ( bits + 7 ) / 8 * 8;
-}
+// IntersectorOctreeGPU.hpp:118 sorts on the next multiple of 8 of 3 * log2( gridRes ) bits; the keys have no bits above
+// 3 * log2( gridRes ), so sorting on exactly that window gives the same order and lets the sort pick 9-bit digits
+static int sortEndBit( int gridRes ) { return 3 * log2i( gridRes ); }
 
 static void initOctree( hako_octree* o, hako_ctx* ctx, const float origin[3], float dps, int gridRes )
 {

@@ -3,11 +3,15 @@
 // Stands in for thrs::RadixSort::sortPairs / sortKeys (tinyhipradixsort.hpp:849-944), which runs three kernels per
 // 8-bit digit (blockCount :119-149, a chained prefix scan over 256 x nBlocks counters :182-250, reorderKeyPair :252-475)
 // and therefore reads the keys twice per pass.  Here:
+//   - digits are 8 or 9 bits wide, whichever needs fewer passes for the bit window (36 bits at 4096^3: 4 x 9 instead of 5 x 8;
+//     33 bits at 2048^3: 4 instead of 5; 42 / 45 bits at 2^14 / 2^15: 5 instead of 6);
 //   - ONE histogram kernel reads the keys once and produces the digit histograms of all passes;
 //   - each pass is ONE kernel: a tile ranks its keys (warp match + popc, stable), publishes its per-digit counts,
 //     resolves its global offsets by decoupled look-back over the preceding tiles, and scatters through shared
 //     memory so that global stores are runs of consecutive addresses.
 // Algorithmic traffic: n * (8 + P * 32) bytes for pairs, vs n * P * (8 + 32) for the reference.
+#include <cstdlib>
+
 #include "internal.cuh"
 
 namespace hako
@@ -18,7 +22,7 @@ constexpr int SORT_BLOCK = 256;
 constexpr int SORT_WARPS = SORT_BLOCK / 32;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_BLOCK * SORT_ITEMS; // 4096 pairs
-constexpr int RADIX = 256;
+constexpr int MAX_RADIX = 512;
 constexpr int MAX_PASSES = 8;
 
 #define LB_FLAG_AGG ( 1ull << 62 )
@@ -28,9 +32,11 @@ constexpr int MAX_PASSES = 8;
 __device__ __forceinline__ uint32_t digitOf( uint64_t key, int shift, uint32_t mask ) { return (uint32_t)( key >> shift ) & mask; }
 
 // ---- histograms of every pass in one read of the keys ----
+template <int RBITS>
 __global__ void __launch_bounds__( SORT_BLOCK ) sortHistogramKernel( const uint64_t* __restrict__ keys, uint64_t n, int beginBit, int endBit, int passes,
-																	 unsigned long long* __restrict__ hist /* [passes][256] */ )
+																	 unsigned long long* __restrict__ hist /* [passes][RADIX] */ )
 {
+	constexpr int RADIX = 1 << RBITS;
 	__shared__ uint32_t s_hist[MAX_PASSES * RADIX];
 	for( int i = threadIdx.x; i < passes * RADIX; i += SORT_BLOCK ) s_hist[i] = 0;
 	__syncthreads();
@@ -40,8 +46,8 @@ __global__ void __launch_bounds__( SORT_BLOCK ) sortHistogramKernel( const uint6
 		const uint64_t k = keys[i];
 		for( int p = 0; p < passes; p++ )
 		{
-			const int shift = beginBit + p * 8;
-			const int bits = min( 8, endBit - shift );
+			const int shift = beginBit + p * RBITS;
+			const int bits = min( RBITS, endBit - shift );
 			atomicAdd( &s_hist[p * RADIX + digitOf( k, shift, ( 1u << bits ) - 1u )], 1u );
 		}
 	}
@@ -52,9 +58,11 @@ __global__ void __launch_bounds__( SORT_BLOCK ) sortHistogramKernel( const uint6
 		if( c ) atomicAdd( &hist[i], (unsigned long long)c );
 	}
 }
-// exclusive scan of each pass's 256 bins (one block per pass)
-__global__ void __launch_bounds__( RADIX ) sortScanHistogramKernel( unsigned long long* __restrict__ hist )
+// exclusive scan of each pass's bins (one block of RADIX threads per pass)
+template <int RBITS>
+__global__ void __launch_bounds__( 1 << RBITS ) sortScanHistogramKernel( unsigned long long* __restrict__ hist )
 {
+	constexpr int RADIX = 1 << RBITS;
 	__shared__ unsigned long long s[RADIX];
 	unsigned long long* h = hist + (size_t)blockIdx.x * RADIX;
 	const unsigned long long v = h[threadIdx.x];
@@ -71,14 +79,16 @@ __global__ void __launch_bounds__( RADIX ) sortScanHistogramKernel( unsigned lon
 }
 
 // ---- one pass ----
-template <bool PAIRS>
-__global__ void __launch_bounds__( SORT_BLOCK ) onesweepKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
+template <int RBITS, bool PAIRS, int MIN_CTAS>
+__global__ void __launch_bounds__( SORT_BLOCK, MIN_CTAS ) onesweepKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
 															   uint64_t* __restrict__ keysOut, uint64_t* __restrict__ valuesOut, uint64_t n,
-															   int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [256] exclusive */,
-															   unsigned long long* __restrict__ lookback /* [tiles][256], zeroed */, uint32_t* __restrict__ ticket )
+															   int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [RADIX] exclusive */,
+															   unsigned long long* __restrict__ lookback /* [tiles][RADIX], zeroed */, uint32_t* __restrict__ ticket )
 {
+	constexpr int RADIX = 1 << RBITS;
+	constexpr int DPT = RADIX / SORT_BLOCK; // digits per thread in the per-digit phase: thread t owns digits [t * DPT, (t + 1) * DPT)
 	__shared__ uint64_t s_data[SORT_TILE];				   // 32 KB: keys, then values, in sorted-by-digit order
-	__shared__ uint32_t s_warpHist[SORT_WARPS][RADIX];	   // 8 KB: per-warp digit counts -> per-warp exclusive offsets
+	__shared__ uint16_t s_warpHist[SORT_WARPS][RADIX];	   // 4 / 8 KB: per-warp digit counts (<= 512) -> per-warp exclusive offsets (<= 4096)
 	__shared__ uint32_t s_tileBase[RADIX];				   // exclusive offset of each digit inside the sorted tile
 	__shared__ unsigned long long s_globalBase[RADIX];	   // global output index of the tile's first key of each digit
 	__shared__ uint32_t s_tile;
@@ -108,56 +118,66 @@ __global__ void __launch_bounds__( SORT_BLOCK ) onesweepKernel( const uint64_t* 
 	{
 		const uint32_t idx = warpBase + i * 32 + lane;
 		const bool valid = idx < tileCount;
-		// invalid (padding) items take digit 255 + are ranked last in the last warps; they are never written
+		// invalid (padding) items sit behind the tile's last key; they get their own match class and are never written
 		const uint32_t d = valid ? digitOf( key[i], shift, mask ) : ( RADIX - 1 );
-		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, d | ( valid ? 0u : 0x100u ) );
+		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, d | ( valid ? 0u : 0x10000u ) );
 		const uint32_t before = __popc( peers & ( ( 1u << lane ) - 1u ) );
 		uint32_t base = 0;
 		if( valid ) base = s_warpHist[warp][d];
 		__syncwarp();
-		if( valid && before == 0 ) s_warpHist[warp][d] = base + __popc( peers );
+		if( valid && before == 0 ) s_warpHist[warp][d] = (uint16_t)( base + __popc( peers ) );
 		__syncwarp();
 		rank[i] = (uint16_t)( base + before );
 	}
 	__syncthreads();
 
-	// per digit (thread d): exclusive scan over the warps, tile total, look-back
+	// per digit (thread t owns DPT consecutive digits): exclusive scan over the warps, tile total, look-back
 	{
-		const uint32_t d = threadIdx.x;
-		uint32_t total = 0;
+		uint32_t total[DPT];
+		unsigned long long excl[DPT];
+		uint32_t mine = 0;
 #pragma unroll
-		for( int w = 0; w < SORT_WARPS; w++ )
+		for( int j = 0; j < DPT; j++ )
 		{
-			const uint32_t c = s_warpHist[w][d];
-			s_warpHist[w][d] = total;
-			total += c;
-		}
-		// publish this tile's count for digit d, then sum the predecessors
-		unsigned long long* my = lookback + (size_t)tile * RADIX + d;
-		unsigned long long excl = 0;
-		if( tile == 0 )
-		{
-			*(volatile unsigned long long*)my = LB_FLAG_INC | (unsigned long long)total;
-		}
-		else
-		{
-			*(volatile unsigned long long*)my = LB_FLAG_AGG | (unsigned long long)total;
-			int64_t t = (int64_t)tile - 1;
-			for( ;; )
+			const uint32_t d = threadIdx.x * DPT + j;
+			uint32_t tot = 0;
+#pragma unroll
+			for( int w = 0; w < SORT_WARPS; w++ )
 			{
-				unsigned long long v;
-				do
-				{
-					v = *(const volatile unsigned long long*)( lookback + (size_t)t * RADIX + d );
-				} while( ( v >> 62 ) == 0 );
-				excl += v & LB_VALUE_MASK;
-				if( ( v >> 62 ) == 2 ) break;
-				t--;
+				const uint32_t c = s_warpHist[w][d];
+				s_warpHist[w][d] = (uint16_t)tot;
+				tot += c;
 			}
-			*(volatile unsigned long long*)my = LB_FLAG_INC | ( excl + total );
+			total[j] = tot;
+			mine += tot;
+			// publish this tile's count for digit d (the predecessors are summed below, after every digit is published)
+			unsigned long long* my = lookback + (size_t)tile * RADIX + d;
+			*(volatile unsigned long long*)my = ( tile == 0 ? LB_FLAG_INC : LB_FLAG_AGG ) | (unsigned long long)tot;
 		}
-		// block-wide exclusive scan of the tile totals over the 256 digits
-		uint32_t inc = total;
+#pragma unroll
+		for( int j = 0; j < DPT; j++ )
+		{
+			const uint32_t d = threadIdx.x * DPT + j;
+			excl[j] = 0;
+			if( tile != 0 )
+			{
+				int64_t t = (int64_t)tile - 1;
+				for( ;; )
+				{
+					unsigned long long v;
+					do
+					{
+						v = *(const volatile unsigned long long*)( lookback + (size_t)t * RADIX + d );
+					} while( ( v >> 62 ) == 0 );
+					excl[j] += v & LB_VALUE_MASK;
+					if( ( v >> 62 ) == 2 ) break;
+					t--;
+				}
+				*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + d ) = LB_FLAG_INC | ( excl[j] + total[j] );
+			}
+		}
+		// block-wide exclusive scan of the tile totals over the digits (thread-local run of DPT digits, then over threads)
+		uint32_t inc = mine;
 #pragma unroll
 		for( int o = 1; o < 32; o <<= 1 )
 		{
@@ -171,9 +191,15 @@ __global__ void __launch_bounds__( SORT_BLOCK ) onesweepKernel( const uint64_t* 
 #pragma unroll
 		for( int w = 0; w < SORT_WARPS; w++ )
 			if( w < (int)warp ) wbase += s_warpTotals[w];
-		const uint32_t tb = wbase + inc - total;
-		s_tileBase[d] = tb;
-		s_globalBase[d] = digitBase[d] + excl - tb; // so that output index = s_globalBase[digit] + position in sorted tile
+		uint32_t tb = wbase + inc - mine;
+#pragma unroll
+		for( int j = 0; j < DPT; j++ )
+		{
+			const uint32_t d = threadIdx.x * DPT + j;
+			s_tileBase[d] = tb;
+			s_globalBase[d] = digitBase[d] + excl[j] - tb; // so that output index = s_globalBase[digit] + position in sorted tile
+			tb += total[j];
+		}
 	}
 	__syncthreads();
 
@@ -235,7 +261,12 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 		setError( "sort: bad bit window [%d, %d)", beginBit, endBit );
 		return HAKO_E_INVALID;
 	}
-	const int passes = ( endBit - beginBit + 7 ) / 8;
+	// digit width: 9 bits when that saves a pass, else 8
+	const int window = endBit - beginBit;
+	const char* rbEnv = getenv( "HAKO_SORT_RBITS" ); // tuning knob: force the digit width
+	const int rbits = rbEnv ? ( atoi( rbEnv ) == 9 ? 9 : 8 ) : ( ( window + 8 ) / 9 < ( window + 7 ) / 8 ? 9 : 8 );
+	const int RADIX = 1 << rbits;
+	const int passes = ( window + rbits - 1 ) / rbits;
 	ctx->stats.sortPasses = (uint32_t)passes;
 	if( n == 0 || passes == 0 ) return 0;
 	const uint64_t tiles = ( n + SORT_TILE - 1 ) / SORT_TILE;
@@ -262,22 +293,33 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 			break;
 		}
 		const uint32_t histBlocks = (uint32_t)min( (uint64_t)ctx->smCount * 8, ( n + SORT_BLOCK * 8 - 1 ) / ( SORT_BLOCK * 8 ) );
-		HAKO_LAUNCH( ctx, sortHistogramKernel, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
-		HAKO_LAUNCH( ctx, sortScanHistogramKernel, passes, RADIX, 0, s, hist );
+		if( rbits == 9 )
+		{
+			HAKO_LAUNCH( ctx, sortHistogramKernel<9>, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
+			HAKO_LAUNCH( ctx, sortScanHistogramKernel<9>, passes, RADIX, 0, s, hist );
+		}
+		else
+		{
+			HAKO_LAUNCH( ctx, sortHistogramKernel<8>, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
+			HAKO_LAUNCH( ctx, sortScanHistogramKernel<8>, passes, RADIX, 0, s, hist );
+		}
 		uint64_t *kin = keys, *vin = values, *kout = keysTmp, *vout = valuesTmp;
 		for( int p = 0; p < passes; p++ )
 		{
-			const int shift = beginBit + p * 8;
-			const int bits = ( endBit - shift < 8 ) ? ( endBit - shift ) : 8;
+			const int shift = beginBit + p * rbits;
+			const int bits = ( endBit - shift < rbits ) ? ( endBit - shift ) : rbits;
 			const uint32_t mask = ( 1u << bits ) - 1u;
-			auto kPairs = onesweepKernel<true>;
-			auto kKeys = onesweepKernel<false>;
-			if( values )
-				HAKO_LAUNCH( ctx, kPairs, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
-							 lookback + (size_t)p * tiles * RADIX, tickets + p );
-			else
-				HAKO_LAUNCH( ctx, kKeys, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
-							 lookback + (size_t)p * tiles * RADIX, tickets + p );
+			auto k8p = onesweepKernel<8, true, 2>;
+			auto k8k = onesweepKernel<8, false, 2>;
+			auto k9p = onesweepKernel<9, true, 2>;
+			auto k9k = onesweepKernel<9, false, 2>;
+			auto k = rbits == 9 ? ( values ? k9p : k9k ) : ( values ? k8p : k8k );
+			const char* occEnv = getenv( "HAKO_SORT_MIN_CTAS" ); // tuning knob
+			const int occ = occEnv ? atoi( occEnv ) : 4; // B200: 2 CTAs/SM 5.43 ms, 3: 5.08, 4: 4.50 (72.7 M pairs, 36 bits; profiles/r1g)
+			if( occ == 3 ) k = rbits == 9 ? ( values ? onesweepKernel<9, true, 3> : onesweepKernel<9, false, 3> ) : ( values ? onesweepKernel<8, true, 3> : onesweepKernel<8, false, 3> );
+			if( occ == 4 ) k = rbits == 9 ? ( values ? onesweepKernel<9, true, 4> : onesweepKernel<9, false, 4> ) : ( values ? onesweepKernel<8, true, 4> : onesweepKernel<8, false, 4> );
+			HAKO_LAUNCH( ctx, k, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
+						 lookback + (size_t)p * tiles * RADIX, tickets + p );
 			uint64_t* t = kin;
 			kin = kout, kout = t;
 			t = vin;

@@ -213,7 +213,7 @@ template <bool EMIT>
 __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
 															uint32_t nTriangles, const uint32_t* __restrict__ colOffset, uint32_t nColumns,
 															V3 origin, float dps, int gridRes, int sixSeparating,
-															uint32_t* __restrict__ colCount, const uint32_t* __restrict__ voxOffset,
+															uint32_t* __restrict__ colCount, const uint32_t* __restrict__ voxOffset, uint32_t totalVoxels,
 															uint64_t* __restrict__ keys, uint64_t* __restrict__ values )
 {
 	// column -> triangle: colOffset is the exclusive scan of columns per triangle; the owner of column c is the last
@@ -243,8 +243,27 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 		s_off[j] = ( tIdx < nTriangles ) ? colOffset[tIdx] : 0xFFFFFFFFu;
 	}
 	__syncthreads();
-	const uint32_t c = c0 + threadIdx.x;
-	if( c >= nColumns ) return;
+	// EMIT: a warp whose 32 columns hold at most EMIT_QUEUE voxels enumerates them into a shared-memory queue (cheap, divergent:
+	// lanes own 0..dozens of voxels) and then shades them with all 32 lanes (closest-point barycentrics, colour mix, Morton
+	// key: ~250 instructions per voxel) and stores keys / values as consecutive words.  Inactive lanes of the last block
+	// run on the last column with empty loops so that the whole warp reaches the queue drain.
+	constexpr uint32_t EMIT_QUEUE = 384;
+	__shared__ uint64_t s_qVoxel[EMIT ? 4 : 1][EMIT ? EMIT_QUEUE : 1];
+	__shared__ uint8_t s_qOwner[EMIT ? 4 : 1][EMIT ? EMIT_QUEUE : 1];	 // the lane whose triangle the voxel belongs to
+	__shared__ float s_triData[EMIT ? 4 : 1][EMIT ? 32 : 1][27];		 // per lane: positions, colours, emissions of its triangle (odd pitch: no bank conflicts)
+	const bool active = c0 + threadIdx.x < nColumns;
+	if( !EMIT && !active ) return;
+	const uint32_t c = active ? c0 + threadIdx.x : nColumns - 1;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	uint32_t warpOut0 = 0, warpTotal = 0;
+	bool useQueue = false;
+	if( EMIT )
+	{
+		const uint32_t cw0 = c0 + warp * 32u, cw1 = cw0 + 32u;
+		warpOut0 = cw0 < nColumns ? voxOffset[cw0] : totalVoxels;
+		warpTotal = ( cw1 < nColumns ? voxOffset[cw1] : totalVoxels ) - warpOut0;
+		useQueue = warpTotal <= EMIT_QUEUE;
+	}
 
 	uint32_t tri;
 	if( c < s_off[128] )
@@ -333,13 +352,29 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 		}
 	}
 
-	V3 c0v, c1v, c2v, e0v, e1v, e2v;
+	V3 c0v = {}, c1v = {}, c2v = {}, e0v = {}, e1v = {}, e2v = {};
 	uint32_t out = 0;
 	if( EMIT )
 	{
-		c0v = loadV3( col, (uint64_t)tri * 3 ), c1v = loadV3( col, (uint64_t)tri * 3 + 1 ), c2v = loadV3( col, (uint64_t)tri * 3 + 2 );
-		e0v = loadV3( emi, (uint64_t)tri * 3 ), e1v = loadV3( emi, (uint64_t)tri * 3 + 1 ), e2v = loadV3( emi, (uint64_t)tri * 3 + 2 );
+		if( !useQueue )
+		{
+			c0v = loadV3( col, (uint64_t)tri * 3 ), c1v = loadV3( col, (uint64_t)tri * 3 + 1 ), c2v = loadV3( col, (uint64_t)tri * 3 + 2 );
+			e0v = loadV3( emi, (uint64_t)tri * 3 ), e1v = loadV3( emi, (uint64_t)tri * 3 + 1 ), e2v = loadV3( emi, (uint64_t)tri * 3 + 2 );
+		}
+		else
+		{
+			// the drain reads the triangle through shared memory: 27 words per voxel from L1 would make it LSU-bound
+			float* d = s_triData[warp][lane];
+			d[0] = v0.x, d[1] = v0.y, d[2] = v0.z, d[3] = v1.x, d[4] = v1.y, d[5] = v1.z, d[6] = v2.x, d[7] = v2.y, d[8] = v2.z;
+#pragma unroll
+			for( int k = 0; k < 9; k++ )
+			{
+				d[9 + k] = col[(uint64_t)tri * 9 + k];
+				d[18 + k] = emi[(uint64_t)tri * 9 + k];
+			}
+		}
 		out = voxOffset[c];
+		if( !active ) uy = ly - 1; // padding lane: nothing to enumerate
 	}
 	uint32_t count = 0;
 	const bool flat = b.lo_z == b.hi_z; // voxelization.hpp:313-316: a one-slab box overlaps by construction
@@ -380,7 +415,14 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 				}
 				if( !ok ) continue;
 			}
-			if( EMIT )
+			if( EMIT && useQueue )
+			{
+				const I3 ci = unproji( x, y, z, major );
+				s_qVoxel[warp][out - warpOut0] = (uint64_t)(uint32_t)ci.x | ( (uint64_t)(uint32_t)ci.y << 21 ) | ( (uint64_t)(uint32_t)ci.z << 42 );
+				s_qOwner[warp][out - warpOut0] = (uint8_t)lane;
+				out++;
+			}
+			else if( EMIT )
 			{
 				const I3 ci = unproji( x, y, z, major );
 				const V3 bc = closestBary( v0, v1, v2, p );
@@ -395,6 +437,26 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 		}
 	}
 	if( !EMIT ) colCount[c] = count;
+	if( EMIT && useQueue )
+	{
+		__syncwarp();
+		for( uint32_t i = lane; i < warpTotal; i += 32u )
+		{
+			const uint64_t q = s_qVoxel[warp][i];
+			const float* d = s_triData[warp][s_qOwner[warp][i]];
+			const uint32_t cx = (uint32_t)q & 0x1FFFFFu, cy = (uint32_t)( q >> 21 ) & 0x1FFFFFu, cz = (uint32_t)( q >> 42 ) & 0x1FFFFFu;
+			// the voxel's lower corner: origin + dps * index per axis, the same products and sums as in the enumeration
+			// ( o = org_xy + dps * {x, y}, r = org_z + (float)z * dps, voxelization.hpp:300-305 )
+			const V3 p = { origin.x + dps * (int)cx, origin.y + dps * (int)cy, origin.z + dps * (int)cz };
+			const V3 bc = closestBary( V3{ d[0], d[1], d[2] }, V3{ d[3], d[4], d[5] }, V3{ d[6], d[7], d[8] }, p );
+			const V3 k0 = { d[9], d[10], d[11] }, k1 = { d[12], d[13], d[14] }, k2 = { d[15], d[16], d[17] };
+			const V3 m0 = { d[18], d[19], d[20] }, m1 = { d[21], d[22], d[23] }, m2 = { d[24], d[25], d[26] };
+			const V3 bcol = bc.x * k1 + bc.y * k2 + bc.z * k0; // voxKernel.cu:148, voxRT.cpp:229
+			const V3 bemi = bc.x * m1 + bc.y * m2 + bc.z * m0;
+			keys[warpOut0 + i] = mortonEncode( cx, cy, cz );
+			values[warpOut0 + i] = (uint64_t)packRGB255( bcol ) | ( (uint64_t)packRGB255( bemi ) << 32 );
+		}
+	}
 }
 
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
@@ -434,7 +496,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		auto kCount = columnVoxelsKernel<false>;
 		auto kEmit = columnVoxelsKernel<true>;
 		HAKO_LAUNCH( ctx, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
-					 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr );
+					 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, 0u, (uint64_t*)nullptr, (uint64_t*)nullptr );
 		if( ( r = scanU32( ctx, s, colCount, colCount, nColumns, totals + 1 ) ) ) break;
 		e = cudaMemcpyAsync( ctx->pinned, totals + 1, 8, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
@@ -457,7 +519,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		if( ( r = dalloc( ctx, keysOut, total, s ) ) ) break;
 		if( ( r = dalloc( ctx, valuesOut, total, s ) ) ) break;
 		HAKO_LAUNCH( ctx, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
-					 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, *keysOut, *valuesOut );
+					 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, (uint32_t)total, *keysOut, *valuesOut );
 	} while( 0 );
 	dfree( colOffset, s ), dfree( colCount, s ), dfree( totals, s );
 	if( r && keysOut )

@@ -128,6 +128,30 @@ def main():
             small["nmajor_%d" % grid] = nm.astype(np.int8)
             small["vindex_%d" % grid] = vi
 
+    # large-grid arithmetic (BASELINE config 4: the 2^10..2^14 sweep) on a bounded input: the first 64 bunny triangles in the
+    # full-mesh frame (same origin / dps as the whole bunny at that grid), so Morton keys use 39 / 42 / 45 bits
+    golden["subset_cases"] = {}
+    NSUB = 64
+    for grid in (8192, 16384, 32768):
+        origin, dps = scene_params(tris, grid)
+        st, sc, se = tris[:NSUB], col[:NSUB], emi[:NSUB]
+        keys, c, e = ref.voxelize(st, sc, se, origin, float(dps), grid)
+        mk, mc, me = ref.merge_voxels(keys, c, e)
+        tree = ref.build_octree(mk, origin, float(dps), grid, dag=True)
+        nodes = tree.nodes()
+        W, H = 512, 512
+        cam = ref.camera_lookat((-2.2, 1.2, 1.0), tuple(float(x) for x in st.reshape(-1, 3).mean(0)), (0, 1, 0), None, W, H)
+        t, nm, vi = tree.render_primary(cam, W, H)
+        golden["subset_cases"][str(grid)] = {
+            "grid": grid, "triangles": NSUB, "D": int(keys.size), "U": int(mk.size), "dag_nodes": tree.num_nodes,
+            "fnv_sorted_dumped_keys": fnv(ref, np.sort(keys)), "fnv_merged_keys": fnv(ref, mk),
+            "fnv_merged_rgb": fnv(ref, np.ascontiguousarray(mc[:, :3])), "fnv_merged_emission_rgb": fnv(ref, np.ascontiguousarray(me[:, :3])),
+            "fnv_node_mask": fnv(ref, np.ascontiguousarray(nodes["mask"])), "fnv_node_children": fnv(ref, np.ascontiguousarray(nodes["children"])),
+            "fnv_node_psum": fnv(ref, np.ascontiguousarray(nodes["psum"])),
+            "image": [W, H], "camera_bytes_hex": bytes(cam).hex(), "hits": int((t != orc.FLT_MAX).sum()),
+            "fnv_vindex": fnv(ref, vi), "fnv_nmajor": fnv(ref, nm), "fnv_t": fnv(ref, t)}
+        print("subset", grid, golden["subset_cases"][str(grid)]["D"], golden["subset_cases"][str(grid)]["U"], tree.num_nodes, golden["subset_cases"][str(grid)]["hits"])
+
     # degenerate / edge-case triangles (SURVEY.md section 7 hard part 3): collinear, point, off-grid, huge
     deg = np.array([
         [[0, 0, 0], [1, 1, 1], [2, 2, 2]],            # collinear

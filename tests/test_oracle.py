@@ -49,6 +49,30 @@ def test_oracle_matches_golden(oracle, bunny, golden, grid):
     assert naive.num_nodes == g["naive_nodes"]
 
 
+@pytest.mark.parametrize("grid", [8192, 16384])
+def test_oracle_matches_golden_large_grid_subset(oracle, bunny, golden, grid):
+    """BASELINE config 4 grids (39 / 42-bit Morton keys) on the first 64 bunny triangles, in the full mesh's frame"""
+    g = golden["subset_cases"][str(grid)]
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    n = g["triangles"]
+    keys, c, e = oracle.voxelize(tris[:n], col[:n], emi[:n], origin, float(dps), grid)
+    mk, mc, me = oracle.merge_voxels(keys, c, e)
+    tree = oracle.build_octree(mk, origin, float(dps), grid)
+    f = lambda a: "%016x" % oracle.fnv1a64(a)
+    assert (keys.size, mk.size, tree.num_nodes) == (g["D"], g["U"], g["dag_nodes"])
+    assert f(np.sort(keys)) == g["fnv_sorted_dumped_keys"] and f(mk) == g["fnv_merged_keys"]
+    assert f(np.ascontiguousarray(mc[:, :3])) == g["fnv_merged_rgb"] and f(np.ascontiguousarray(me[:, :3])) == g["fnv_merged_emission_rgb"]
+    nodes = tree.nodes()
+    assert f(np.ascontiguousarray(nodes["mask"])) == g["fnv_node_mask"] and f(np.ascontiguousarray(nodes["children"])) == g["fnv_node_children"]
+    assert f(np.ascontiguousarray(nodes["psum"])) == g["fnv_node_psum"]
+    W, H = g["image"]
+    cam = oracle.camera_lookat((-2.2, 1.2, 1.0), tuple(float(x) for x in tris[:n].reshape(-1, 3).mean(0)), (0, 1, 0), None, W, H)
+    assert bytes(cam).hex() == g["camera_bytes_hex"]
+    t, nm, vi = tree.render_primary(cam, W, H)
+    assert int((t != FLT_MAX).sum()) == g["hits"] and f(vi) == g["fnv_vindex"] and f(nm) == g["fnv_nmajor"] and f(t) == g["fnv_t"]
+
+
 def test_survey_probe_values(golden):
     """values the surveyor measured by driving the reference headers."""
     c = golden["cases"]["256"]
@@ -56,6 +80,8 @@ def test_survey_probe_values(golden):
     assert abs(c["sum_t_hits"] - 2042694.863875) < 1e-5
     c = golden["cases"]["1024"]
     assert (c["D"], c["U"], c["naive_nodes"], c["dag_nodes"], c["hits"]) == (2320463, 2115628, 978199, 86489, 458220)
+    c = golden["cases"]["4096"]     # the C2* row of SURVEY 8(a): bunny at the bench grid
+    assert (c["D"], c["U"], c["naive_nodes"], c["dag_nodes"], c["hits"]) == (34653745, 33810276, 15658017, 734869, 456677)
 
 
 @pytest.mark.parametrize("grid", [16, 64])
