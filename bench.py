@@ -309,7 +309,23 @@ def run_ours(args):
 
     # ---- path tracing leg (BASELINE config[2] shape): same octree, 1920x1080, 4 bounces, procedural 2k environment;
     # samples-per-pixel sharded over ranks (rank r renders iterations r, r+G, ...), ONE ncclReduce of the accumulators ----
-    pt_res = run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args)
+    pt_octree = None
+    pt_build_ms = None
+    if rank == 0:
+        tris, col, emi, _, _, _ = scene
+        from scenes import scene_params
+        pt_origin, pt_dps = scene_params(tris, PT_GRID)
+        t0 = time.perf_counter()
+        pt_octree = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, pt_origin, float(pt_dps), PT_GRID)
+        pt_build_ms = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        pt_octree = hdist.broadcast_octree(ctx, hk.IntersectorOctreeGPU, pt_octree, 0)
+    pt_res = run_pt_leg(hk, hdist, ctx, pt_octree, dev, rank, world, args)
+    if rank == 0 and pt_res is not None:
+        pt_info = pt_octree.info()
+        pt_res["octree"] = {"grid": PT_GRID, "voxels": int(pt_info.numberOfVoxels), "nodes": int(pt_info.numberOfNodes), "build_e2e_ms": pt_build_ms}
+    pt_octree.cleanUp()
+    sweep = run_build_sweep(hk, ctx, scene) if (rank == 0 and not args.no_sweep) else None
 
     if rank != 0:
         if world > 1:
@@ -379,7 +395,8 @@ def run_ours(args):
                     "call": "hako_render_primary (host buffers, pinned), one call per view, RGBA8 frame out = the voxRTGPU frame (render kernel + D2H of the image, voxRTGPU.cpp:191-208)",
                     "hit_records": {"value": rays_step_all * args.steps / (e2e_rec_total * 1e-3) / 1e6, "unit": "Mrays/s", "d2h_bytes_per_step": 12 * nrays_view * VIEWS,
                                     "ms_per_step": e2e_rec_total / args.steps, "call": "same call returning t / nMajor / vIndex (12 B per ray) instead of the image"}},
-            "gpu_launches": int(launches), "roofline": roofline, "path_tracing": pt_res, "cpu_baseline": cpu, "build": build, "hits_view0": hits_view0,
+            "gpu_launches": int(launches), "roofline": roofline, "path_tracing": pt_res, "cpu_baseline": cpu, "build": build, "build_sweep": sweep,
+            "hits_view0": hits_view0,
             "parity_vs_cpu_reference_view0": parity, "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware"}
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
@@ -388,6 +405,8 @@ def run_ours(args):
 
 PT_STEPS = 4            # PathTracer::step calls per rank inside the timed region (16 spp each)
 PT_DEPTH = 4            # BASELINE config[2]: 4 bounces (the reference's literal is 8, voxKernel.cu:691)
+PT_GRID = 8192          # BASELINE config[2]: the dragon at 8192^3
+SWEEP_GRIDS = (1024, 2048, 4096, 8192, 16384)   # BASELINE config[3]: voxelize + sort + octree build, 2^10 .. 2^14
 
 
 def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
@@ -452,8 +471,8 @@ def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
         a = pt.accumulators()
         ok = bool((a[..., 3] == spp).all())
         paths = W * H * spp
-        res = {"workload": "stand-in dragon %d^3, %dx%d, maxDepth %d, procedural 2048x1024 environment (monks_forest_2k.hdr is missing), %d spp per frame = %d steps x 16 spp per GPU"
-                           % (GRID, W, H, PT_DEPTH, spp, PT_STEPS),
+        res = {"workload": "config[2]: stand-in dragon %d^3, %dx%d, maxDepth %d, procedural 2048x1024 environment (monks_forest_2k.hdr is missing), %d spp per frame = %d steps x 16 spp per GPU"
+                           % (PT_GRID, W, H, PT_DEPTH, spp, PT_STEPS),
                "ms_per_frame": float(ms.item()), "ms_per_spp_per_gpu": float(ms.item()) / (16 * PT_STEPS), "mpaths_per_s": paths / (float(ms.item()) * 1e-3) / 1e6,
                "mrays_per_s": float(rays.item()) / (float(ms.item()) * 1e-3) / 1e6, "rays_per_path": float(rays.item()) / paths,
                "e2e_ms_per_frame": float(e2e_ms.item()), "e2e_mpaths_per_s": paths / (float(e2e_ms.item()) * 1e-3) / 1e6, "d2h_bytes_per_frame": W * H * 4,
@@ -463,6 +482,36 @@ def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
     pt.m_intersectorOctreeGPU = own
     pt.cleanUp()
     return res
+
+
+def run_build_sweep(hk, ctx, scene):
+    """BASELINE config[3]: voxelization + Morton radix sort + octree build at 2^10 .. 2^14 on the bench mesh (host-buffer call,
+    best of 2 after a warm-up; per-stage device times from hako_ctx_build_stats).  A grid whose octree exceeds the reference
+    format's 24-bit node index is reported as such (HAKO_E_LIMIT), not skipped silently."""
+    from scenes import scene_params
+    tris, col, emi, _, _, _ = scene
+    rows = []
+    for grid in SWEEP_GRIDS:
+        origin, dps = scene_params(tris, grid)
+        row = {"grid": grid}
+        try:
+            best = None
+            for i in range(3):
+                t0 = time.perf_counter()
+                g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+                wall = (time.perf_counter() - t0) * 1e3
+                st = ctx.build_stats()
+                g.cleanUp()
+                if i > 0 and (best is None or wall < best[0]):
+                    best = (wall, dict(st))
+            wall, st = best
+            row.update({"e2e_host_call_ms": round(wall, 3), "dumped_voxels": int(st["dumpedVoxels"]), "unique_voxels": int(st["uniqueVoxels"]),
+                        "octree_nodes": int(st["numberOfNodes"]), "sort_passes": int(st["sortPasses"]),
+                        "device_ms": {k: round(st[k], 3) for k in ("ms_h2d", "ms_voxelize", "ms_sort", "ms_unique", "ms_octree", "ms_total")}})
+        except hk.HakoError as e:
+            row["error"] = str(e)[:200]
+        rows.append(row)
+    return rows
 
 
 _REAL_STDOUT = sys.stdout
@@ -482,6 +531,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the build sweep (profiling runs)")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner there) go to stderr
     global _REAL_STDOUT

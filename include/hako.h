@@ -38,6 +38,8 @@ extern "C" {
 typedef struct hako_ctx hako_ctx;
 typedef struct hako_octree hako_octree;
 typedef struct hako_pt hako_pt;
+typedef struct hako_mesh hako_mesh;
+typedef struct hako_seq hako_seq;
 typedef void* hako_stream; /* cudaStream_t */
 
 /* == OctreeNode, voxCommon.hpp:133-138 (68 bytes, align 4).  children[i] = index | mask<<24 after embedMasks
@@ -194,6 +196,43 @@ int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, in
 /* pieces of the sampler / environment exposed for parity tests */
 int hako_pt_pmj_table( hako_pt* pt, hako_stream stream, float* samples /* [128][4096][2], HOST */ );
 int hako_pt_hdri_sats( hako_pt* pt, hako_stream stream, uint32_t* sats /* [7][w*h], HOST */ );
+
+int hako_pt_rgba8_device( hako_pt* pt, void** rgba8_d, int* w, int* h );				/* m_frameBufferU8 (PathTracer.hpp:93), for the frame loop */
+hako_ctx* hako_pt_context( hako_pt* pt );
+
+/* ---- input stage: voxUtil.hpp:8-77, voxRT.cpp:188-190 ---- */
+/* triangle meshes from Wavefront OBJ (what prlib loads through tiny_obj_loader, libs/prlib/src/prg.cpp:1231-1241; "v x y z r g b"
+ * vertex colours are read as Cd) or Stanford PLY (ascii / binary, the xyzrgb dragon's native format).  Polygons are fanned. */
+int hako_mesh_load( const char* path, hako_mesh** out );
+void hako_mesh_destroy( hako_mesh* m );
+int hako_mesh_info( const hako_mesh* m, uint64_t* nVertices, uint64_t* nTriangles, int* hasColors );
+/* trianglesFlattened (voxUtil.hpp:8-65): 9 floats per triangle into pos / col / emi (col, emi may be NULL); colour = Cd or 1, emission = 0 */
+int hako_mesh_flatten( const hako_mesh* m, float* pos, float* col, float* emi );
+/* getBoundingBox (voxUtil.hpp:66-77) as a device reduction over DEVICE-resident vertices (3 floats each); HOST results */
+int hako_bounds_device( hako_ctx* ctx, hako_stream stream, const float* pos_d, uint64_t nVertices, float lower[3], float upper[3] );
+/* voxRT.cpp:188-190: origin = bbox lower, dps = max( bbox size ) / (float)gridRes */
+int hako_scene_params( const float lower[3], const float upper[3], int gridRes, float origin[3], float* dps );
+
+/* ---- images ---- */
+/* Radiance .hdr -> RGBA32F exactly as stbi_loadf( file, &w, &h, 0, 4 ) (libs/prlib/src/prp.cpp:353-366): the decode step of
+ * PathTracer::loadHDRI (PathTracer.hpp:104-116).  *rgba is malloc'ed; release with hako_image_free. */
+int hako_image_load_hdr( const char* path, float** rgba, int* w, int* h );
+void hako_image_free( float* rgba );
+/* Image2DRGBA8::saveAsPngUncompressed (libs/prlib/src/prp.cpp:215-223): RGBA8 PNG with stored deflate blocks */
+int hako_image_save_png( const char* path, const uint8_t* rgba, int w, int h );
+
+/* ---- frame loop: RTCamp.cpp:122-196, headless ----
+ * Per frame: updateScene -> clearFrameBuffer -> `iterations` steps -> resolve -> D2D into one of nBuffers pooled frame buffers ->
+ * a pool thread downloads it and writes the PNG while the next frame builds and renders.  HOST vertex pointers. */
+int hako_seq_create( hako_pt* pt, int nBuffers, int nWriters, hako_seq** out );
+int hako_seq_render_frame( hako_seq* q, const float* pos, const float* col, const float* emi, uint32_t nTriangles, const float origin[3], float dps,
+						   int gridRes, const hako_camera* cam, int iterations, int maxDepth, const char* pngPath, float* updateMs, float* renderMs );
+int hako_seq_wait( hako_seq* q ); /* taskGroup.waitForAllElementsToFinish, RTCamp.cpp:196 */
+void hako_seq_destroy( hako_seq* q );
+
+/* ---- debug export: saveVoxelsAsMesh, voxMesh.cpp:111-219 ----
+ * binary little-endian PLY: 8 corners per voxel, one quad per face without a neighbouring voxel.  HOST pointers. */
+int hako_voxel_mesh_save_ply( const char* path, const uint64_t* sortedMortons, uint64_t n, const float origin[3], float dps );
 
 #ifdef __cplusplus
 }

@@ -14,6 +14,7 @@ _abi.load()
 from .intersector import (FLT_MAX, NODE68, VOXEL_ATTRIB, Context, IntersectorOctree, IntersectorOctreeGPU)  # noqa: E402
 from .camera import camera_from_matrices, camera_lookat  # noqa: E402
 from .pathtracer import PathTracer  # noqa: E402
+from . import io  # noqa: E402
 
 __all__ = ["Camera", "HakoError", "Context", "IntersectorOctree", "IntersectorOctreeGPU", "PathTracer", "FLT_MAX", "NODE68", "VOXEL_ATTRIB",
            "camera_lookat", "camera_from_matrices"]

@@ -92,6 +92,22 @@ SIGNATURES = {
     "hako_pt_ray_count": (i32, [vp, vp, pu64, i32]),
     "hako_pt_pmj_table": (i32, [vp, vp, vp]),
     "hako_pt_hdri_sats": (i32, [vp, vp, vp]),
+    "hako_pt_rgba8_device": (i32, [vp, pp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "hako_pt_context": (vp, [vp]),
+    "hako_mesh_load": (i32, [C.c_char_p, pp]),
+    "hako_mesh_destroy": (None, [vp]),
+    "hako_mesh_info": (i32, [vp, pu64, pu64, C.POINTER(C.c_int)]),
+    "hako_mesh_flatten": (i32, [vp, vp, vp, vp]),
+    "hako_bounds_device": (i32, [vp, vp, vp, u64, vp, vp]),
+    "hako_scene_params": (i32, [vp, vp, i32, vp, C.POINTER(C.c_float)]),
+    "hako_image_load_hdr": (i32, [C.c_char_p, pp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "hako_image_free": (None, [vp]),
+    "hako_image_save_png": (i32, [C.c_char_p, vp, i32, i32]),
+    "hako_seq_create": (i32, [vp, i32, i32, pp]),
+    "hako_seq_render_frame": (i32, [vp, vp, vp, vp, u32, vp, f32, i32, C.POINTER(Camera), i32, i32, C.c_char_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "hako_seq_wait": (i32, [vp]),
+    "hako_seq_destroy": (None, [vp]),
+    "hako_voxel_mesh_save_ply": (i32, [C.c_char_p, vp, u64, vp, f32]),
 }
 
 _lib = None

@@ -1335,6 +1335,15 @@ int hako_pt_accum_device( hako_pt* pt, void** accum_d, uint64_t* bytes )
 	return HAKO_OK;
 }
 
+int hako_pt_rgba8_device( hako_pt* pt, void** rgba8_d, int* w, int* h )
+{
+	PT_ARG( pt && rgba8_d && w && h, "hako_pt_rgba8_device: null argument" );
+	*rgba8_d = pt->rgba8;
+	*w = pt->w, *h = pt->h;
+	return HAKO_OK;
+}
+hako_ctx* hako_pt_context( hako_pt* pt ) { return pt ? pt->ctx : nullptr; }
+
 int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, int reset )
 {
 	PT_ARG( pt && raysTraced, "hako_pt_ray_count: null argument" );

@@ -69,7 +69,14 @@ class PathTracer:
         check(self.lib.hako_pt_clear(self.h, _stream(stream)))
 
     def loadHDRI(self, stream, pixels, pixelsPrimary=None):
-        """pixels: float32 [h, w, 4] (RGBA32F, as pr::Image2DRGBA32::loadFromHDR yields); builds the 7 SATs."""
+        """pixels: a Radiance .hdr file name (PathTracer.hpp:104-116 takes file names) or float32 [h, w, 4] (RGBA32F, as
+        pr::Image2DRGBA32::loadFromHDR yields); builds the 7 SATs."""
+        if isinstance(pixels, (str, bytes)) or hasattr(pixels, "__fspath__"):
+            from .io import load_hdr
+            pixels = load_hdr(pixels)
+        if isinstance(pixelsPrimary, (str, bytes)) or hasattr(pixelsPrimary, "__fspath__"):
+            from .io import load_hdr
+            pixelsPrimary = load_hdr(pixelsPrimary)
         p = _f32(pixels)
         assert p.ndim == 3 and p.shape[2] == 4
         q = None if pixelsPrimary is None else _f32(pixelsPrimary)
