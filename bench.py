@@ -229,6 +229,9 @@ def run_ours(args):
                  "octree_nodes": int(st["numberOfNodes"]), "sort_passes": int(st["sortPasses"]), "host_syncs": int(st["hostSyncs"]),
                  "kernel_launches": int(st["kernelLaunches"]), "mesh_generation_s": round(gen_s, 2)}
     if world > 1:
+        warm = torch.zeros(1, device=dev)
+        dist.broadcast(warm, 0)                 # communicator set-up is not part of the replication time
+        torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
         octree = hdist.broadcast_octree(ctx, hk.IntersectorOctreeGPU, octree, 0)
         dist.barrier()
@@ -318,12 +321,18 @@ def run_ours(args):
         t0 = time.perf_counter()
         pt_octree = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, pt_origin, float(pt_dps), PT_GRID)
         pt_build_ms = (time.perf_counter() - t0) * 1e3
+    pt_bcast_ms = None
     if world > 1:
+        dist.barrier()
+        t0 = time.perf_counter()
         pt_octree = hdist.broadcast_octree(ctx, hk.IntersectorOctreeGPU, pt_octree, 0)
+        dist.barrier()
+        pt_bcast_ms = (time.perf_counter() - t0) * 1e3
     pt_res = run_pt_leg(hk, hdist, ctx, pt_octree, dev, rank, world, args)
     if rank == 0 and pt_res is not None:
         pt_info = pt_octree.info()
-        pt_res["octree"] = {"grid": PT_GRID, "voxels": int(pt_info.numberOfVoxels), "nodes": int(pt_info.numberOfNodes), "build_e2e_ms": pt_build_ms}
+        pt_res["octree"] = {"grid": PT_GRID, "voxels": int(pt_info.numberOfVoxels), "nodes": int(pt_info.numberOfNodes), "build_e2e_ms": pt_build_ms,
+                            "device_bytes": int(pt_info.deviceBytes), "nccl_broadcast_ms": pt_bcast_ms}
     pt_octree.cleanUp()
     sweep = run_build_sweep(hk, ctx, scene) if (rank == 0 and not args.no_sweep) else None
 
