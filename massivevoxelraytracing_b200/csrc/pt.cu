@@ -734,7 +734,7 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 #pragma unroll 1
 			for( int it = 0; it < tp.burst; it++ )
 			{
-				const int r = tr.step( tree, shadow, stk );
+				const int r = tr.ordinary ? tr.template step<true>( tree, shadow, stk ) : tr.template step<false>( tree, shadow, stk );
 				if( r == TRAV_CONTINUE ) continue;
 				flying = false;
 				if( r == TRAV_HIT )

@@ -47,6 +47,7 @@ struct Traversal
 	float dtx, dty, dtz;
 	float tx1, ty1, tz1;
 	uint32_t node, level, childMask, skipped, vMask;
+	bool ordinary; // every root slab distance is below 1e37 in magnitude: step<true> is bit-identical to step<false>
 	// results of a TRAV_HIT step
 	float t;
 	int nMajor;
@@ -86,6 +87,8 @@ struct Traversal
 		tx1 = up.x * inv.x, ty1 = up.y * inv.y, tz1 = up.z * inv.z;
 		if( min3( tx1, ty1, tz1 ) < max3( t0x, t0y, t0z ) ) return false;
 		dtx = tx1 - t0x, dty = ty1 - t0y, dtz = tz1 - t0z;
+		const float big = 1.0e37f;
+		ordinary = sabs( t0x ) < big && sabs( t0y ) < big && sabs( t0z ) < big && sabs( tx1 ) < big && sabs( ty1 ) < big && sabs( tz1 ) < big;
 		sp = 0;
 		const uint32_t root = v.numberOfNodes - 1; // the root is the last node (IntersectorOctree.hpp:252)
 		node = root | ( (uint32_t)__ldg( v.masks + root ) << 24 );
@@ -95,7 +98,14 @@ struct Traversal
 		return true;
 	}
 
-	// hit: t / nMajor are set, `skipped` is vIndex
+	// hit: t / nMajor are set, `skipped` is vIndex.
+	// FINITE = true may be used when begin() found every root slab distance below 1e37 in magnitude (`ordinary`): all later t
+	// values lie inside the root interval, so none is inf / NaN and fmaxf / fminf select the same operand as the reference's
+	// compare-select max / min except for the sign of a zero, which no consumer below can see (==, <, and t only when
+	// 0 < lmax): one FMNMX3 instead of two FSETP + FSEL pairs, ~6 of ~95 instructions per step.  Rays with huge slab distances
+	// (a zero or denormal direction component against the clamped 1/rd) can produce inf - inf = NaN, where the two forms
+	// differ; they take the exact path (tests/test_gpu_traverse.py::test_random_rays_and_shadow has such rays).
+	template <bool FINITE = false>
 	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, TravStack& stk )
 	{
 		const float scale = levelScale( level );
@@ -103,7 +113,7 @@ struct Traversal
 		const float tx0 = tx1 - dtx * scale;
 		const float ty0 = ty1 - dty * scale;
 		const float tz0 = tz1 - dtz * scale;
-		const float lmax = max3( tx0, ty0, tz0 );
+		const float lmax = FINITE ? fmaxf( fmaxf( tx0, ty0 ), tz0 ) : max3( tx0, ty0, tz0 );
 
 		bool pop = false;
 		if( node == 0xFFFFFFFFu )
@@ -128,7 +138,7 @@ struct Traversal
 			const float y1 = ( childMask & 2u ) ? ty1 : tyM;
 			const float z1 = ( childMask & 4u ) ? tz1 : tzM;
 			// :365-411 the child the ray is in now; the exit plane decides the next sibling
-			const float umin = min3( x1, y1, z1 );
+			const float umin = FINITE ? fminf( fminf( x1, y1 ), z1 ) : min3( x1, y1, z1 );
 			const uint32_t mv = ( umin == x1 ) ? 1u : ( ( umin == y1 ) ? 2u : 4u );
 			const bool hasNext = ( childMask & mv ) == 0;
 			const uint32_t ci = childMask ^ vMask;
@@ -179,16 +189,26 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 	Traversal tr;
 	TravStack stk;
 	if( !tr.begin( v, ro, rd ) ) return false;
-	for( ;; )
+	int r;
+	if( tr.ordinary )
 	{
-		const int r = tr.step( v, shadow, stk );
-		if( r == TRAV_CONTINUE ) continue;
-		if( r == TRAV_MISS ) return false;
-		*tOut = tr.t;
-		*nMajorOut = tr.nMajor;
-		*vIndexOut = tr.skipped;
-		return true;
+		do
+		{
+			r = tr.template step<true>( v, shadow, stk );
+		} while( r == TRAV_CONTINUE );
 	}
+	else
+	{
+		do
+		{
+			r = tr.template step<false>( v, shadow, stk );
+		} while( r == TRAV_CONTINUE );
+	}
+	if( r == TRAV_MISS ) return false;
+	*tOut = tr.t;
+	*nMajorOut = tr.nMajor;
+	*vIndexOut = tr.skipped;
+	return true;
 }
 
 template <bool SHADOW>
