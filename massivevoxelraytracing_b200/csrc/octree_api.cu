@@ -303,14 +303,19 @@ int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_ca
 			if( nMajor && ( e = cudaMemcpyAsync( nMajor + off, nm_d + off, cnt * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
 			if( vIndex && ( e = cudaMemcpyAsync( vIndex + off, vi_d + off, cnt * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
 		}
-		// every band kernel is ordered before its copy, so the last copy closes the call; the frees below are ordered on `s`
+		// every band kernel is ordered before its copy, so the last copy closes the call: ONE host wait on that event; the
+		// frees below are stream-ordered on `s`, which is made to wait for the same event
 		if( e == cudaSuccess ) e = cudaEventRecord( ctx->bandEv[16], ctx->copyStream );
 		if( e == cudaSuccess ) e = cudaStreamWaitEvent( s, ctx->bandEv[16], 0 );
+		if( e == cudaSuccess ) e = cudaEventSynchronize( ctx->bandEv[16] );
 		if( e != cudaSuccess && r == 0 ) r = cudaFail( e, "band pipeline", __FILE__, __LINE__ );
-		for( int i = 0; i < 2; i++ )
-			if( ( e = cudaStreamSynchronize( ctx->bandStream[i] ) ) != cudaSuccess && r == 0 ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
-		if( ( e = cudaStreamSynchronize( ctx->copyStream ) ) != cudaSuccess && r == 0 ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
-		if( ( e = cudaStreamSynchronize( s ) ) != cudaSuccess && r == 0 ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+		if( r )
+		{
+			// error path: drain everything before the buffers go back to the pool
+			for( int i = 0; i < 2; i++ ) cudaStreamSynchronize( ctx->bandStream[i] );
+			cudaStreamSynchronize( ctx->copyStream );
+			cudaStreamSynchronize( s );
+		}
 	} while( 0 );
 #undef CP
 	dfree( rgba_d, s ), dfree( t_d, s ), dfree( nm_d, s ), dfree( vi_d, s );
