@@ -32,7 +32,7 @@ extern "C" {
 #define HAKO_OK 0
 #define HAKO_E_INVALID -1 /* bad argument (e.g. gridRes not a power of two: IntersectorOctreeGPU.hpp:48-51 abort()) */
 #define HAKO_E_CUDA -2	  /* CUDA runtime error / no device */
-#define HAKO_E_LIMIT -3	  /* 32-bit / 24-bit format ceiling exceeded (SURVEY.md section 7 hard part 5) */
+#define HAKO_E_LIMIT -3	  /* 32-bit format ceiling exceeded (voxel / node counters), or a reference-layout export of a wide-index tree */
 #define HAKO_E_STATE -4	  /* call order (e.g. step before resize) */
 
 typedef struct hako_ctx hako_ctx;
@@ -83,6 +83,11 @@ typedef struct hako_octree_info
 	uint32_t hasEmission;
 	int32_t gridRes;
 	uint64_t deviceBytes; /* nodes + attributes (+ kept Morton keys) resident in HBM */
+	/* 1: the tree has >= 2^24 - 1 nodes, more than the reference's child pointers (index | mask << 24, voxCommon.hpp:183-195) can
+	 * address; it is kept with plain 32-bit child indices (the traversal reads child masks from a side array) and cannot be exported
+	 * in the 68-byte reference layout.  0: reference layout. */
+	uint32_t wideIndex;
+	uint32_t reserved;
 } hako_octree_info;
 
 /* per-stage record of the last hako_octree_build* call on a context (voxRTGPU.cpp:169-173 prints one total) */

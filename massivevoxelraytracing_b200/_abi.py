@@ -28,7 +28,7 @@ class Camera(C.Structure):
 class OctreeInfo(C.Structure):
     _fields_ = [("numberOfNodes", C.c_uint32), ("numberOfVoxels", C.c_uint32), ("lower", C.c_float * 3), ("upper", C.c_float * 3),
                 ("dps", C.c_float), ("emissionScale", C.c_float), ("hasEmission", C.c_uint32), ("gridRes", C.c_int32),
-                ("deviceBytes", C.c_uint64)]
+                ("deviceBytes", C.c_uint64), ("wideIndex", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class BuildStats(C.Structure):

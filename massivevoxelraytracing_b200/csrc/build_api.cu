@@ -105,7 +105,7 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 		}
 		o->numberOfVoxels = (uint32_t)U;
 		CK( cudaEventRecord( ctx->ev[4], s ) );
-		if( ( r = buildOctreeDevice( ctx, s, o->mortons, U, gridRes, 1, &o->nodes, &o->masks, &o->numberOfNodes, nullptr ) ) ) break;
+		if( ( r = buildOctreeDevice( ctx, s, o->mortons, U, gridRes, 1, &o->nodes, &o->masks, &o->numberOfNodes, nullptr, &o->wide ) ) ) break;
 		st.numberOfNodes = o->numberOfNodes;
 		CK( cudaEventRecord( ctx->ev[5], s ) );
 		CK( cudaStreamSynchronize( s ) );
@@ -209,7 +209,7 @@ int hako_octree_build_from_morton( hako_ctx* ctx, hako_stream stream, const uint
 			for( uint64_t i = 0; i < n && !o->hasEmission; i++ ) o->hasEmission = ( attrs[i].emission[0] | attrs[i].emission[1] | attrs[i].emission[2] ) != 0;
 		}
 		uint32_t launches = 0;
-		if( ( r = buildOctreeDevice( ctx, s, o->mortons, n, gridRes, dag, &o->nodes, &o->masks, &o->numberOfNodes, &launches ) ) ) break;
+		if( ( r = buildOctreeDevice( ctx, s, o->mortons, n, gridRes, dag, &o->nodes, &o->masks, &o->numberOfNodes, &launches, &o->wide ) ) ) break;
 		ctx->stats.uniqueVoxels = n;
 		ctx->stats.numberOfNodes = o->numberOfNodes;
 		ctx->stats.kernelLaunches = launches;

@@ -151,6 +151,7 @@ struct OctreeView
 	V3 lower, upper;
 	float emissionScale;
 	uint32_t hasEmission;
+	uint32_t wide; // child slots hold plain 32-bit indices; masks[child] is the child's mask
 };
 
 // read-only 8-byte load through the non-coherent path (the tree is immutable while tracing)

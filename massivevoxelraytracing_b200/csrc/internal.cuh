@@ -44,6 +44,9 @@ struct hako_octree
 	float emissionScale = 7.5f; // IntersectorOctreeGPU.hpp:273
 	uint32_t hasEmission = 0;
 	int gridRes = 0;
+	// 1: plain 32-bit child indices, the child's mask comes from `masks` (trees of >= 2^24 - 1 nodes, which the reference's
+	// index | mask << 24 child pointers cannot express); 0: the reference layout
+	int wide = 0;
 
 	hako::OctreeView view() const
 	{
@@ -57,6 +60,7 @@ struct hako_octree
 		v.upper = upper;
 		v.emissionScale = emissionScale;
 		v.hasEmission = hasEmission;
+		v.wide = (uint32_t)wide;
 		return v;
 	}
 };
@@ -120,5 +124,5 @@ int uniqueMergeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, cons
 					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, uint64_t* U, uint32_t* hasEmission );
 // octree.cu
 int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, uint64_t n, int gridRes, int dag,
-					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodes, uint32_t* launchesOut );
+					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodes, uint32_t* launchesOut, int* wideOut );
 } // namespace hako

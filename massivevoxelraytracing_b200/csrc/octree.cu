@@ -19,6 +19,8 @@
 // Level 0 is special-cased: its key is the 8-bit mask alone, so first occurrences are found with a 256-entry atomicMin
 // table and the <= 255 leaf nodes are rebuilt from their masks (nVoxelsPSum = popcount prefix) -- no per-group node is stored.
 // Child pointers carry the child's mask from the start (index | mask << 24), so there is no separate embedMasks pass.
+#include <cstdlib>
+
 #include "internal.cuh"
 #include "scan.cuh"
 
@@ -70,7 +72,7 @@ __global__ void __launch_bounds__( OB_BLOCK ) groupBuildKernel( const uint64_t* 
 															   uint64_t* __restrict__ nextMorton, uint32_t* __restrict__ nextChild, uint32_t* __restrict__ nextVox,
 															   TraceNode* __restrict__ groupNode, uint8_t* __restrict__ groupMask,
 															   uint32_t* __restrict__ leafFirst /* [256] DAG leaf level */,
-															   TraceNode* __restrict__ nodes, uint8_t* __restrict__ masks, uint32_t naiveBase )
+															   TraceNode* __restrict__ nodes, uint8_t* __restrict__ masks, uint32_t naiveBase, int wide )
 {
 	__shared__ uint32_t s_first[256];
 	if( LEAF && DAG )
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__( OB_BLOCK ) groupBuildKernel( const uint64_t* 
 			const uint32_t idx = naiveBase + g;
 			storeNode( &nodes[idx], children, psum );
 			masks[idx] = (uint8_t)mask;
-			nextChild[g] = idx | ( mask << 24 );
+			nextChild[g] = wide ? idx : ( idx | ( mask << 24 ) );
 		}
 		g++;
 	}
@@ -209,7 +211,7 @@ __global__ void __launch_bounds__( 256 ) leafRankKernel( const uint32_t* __restr
 		ls->levelBase[1] = present;
 	}
 }
-__global__ void __launch_bounds__( 256 ) leafAssignKernel( const uint8_t* __restrict__ groupMask, uint32_t G, const uint32_t* __restrict__ leafIndexOfMask, uint32_t* __restrict__ nextChild )
+__global__ void __launch_bounds__( 256 ) leafAssignKernel( const uint8_t* __restrict__ groupMask, uint32_t G, const uint32_t* __restrict__ leafIndexOfMask, uint32_t* __restrict__ nextChild, int wide )
 {
 	__shared__ uint32_t s_idx[256];
 	s_idx[threadIdx.x] = leafIndexOfMask[threadIdx.x];
@@ -217,7 +219,7 @@ __global__ void __launch_bounds__( 256 ) leafAssignKernel( const uint8_t* __rest
 	const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
 	if( g >= G ) return;
 	const uint32_t mask = groupMask[g];
-	nextChild[g] = s_idx[mask] | ( mask << 24 );
+	nextChild[g] = wide ? s_idx[mask] : ( s_idx[mask] | ( mask << 24 ) );
 }
 
 // ---- DAG, upper levels ----
@@ -315,11 +317,22 @@ __global__ void __launch_bounds__( OB_BLOCK ) dagLookupKernel( const TraceNode* 
 	if( tile == gridDim.x - 1 && threadIdx.x == 0 ) ls->levelBase[level + 1] = base + (uint32_t)( prefix + total );
 }
 __global__ void __launch_bounds__( 256 ) dagAssignKernel( const uint32_t* __restrict__ rep, const uint32_t* __restrict__ rankOf, const uint8_t* __restrict__ groupMask, uint32_t G,
-														  const LevelState* __restrict__ ls, int level, uint32_t* __restrict__ nextChild )
+														  const LevelState* __restrict__ ls, int level, uint32_t* __restrict__ nextChild, int wide )
 {
 	const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
 	if( g >= G ) return;
-	nextChild[g] = ( ls->levelBase[level] + rankOf[rep[g]] ) | ( (uint32_t)groupMask[g] << 24 );
+	const uint32_t idx = ls->levelBase[level] + rankOf[rep[g]];
+	nextChild[g] = wide ? idx : ( idx | ( (uint32_t)groupMask[g] << 24 ) );
+}
+// embedMasks (voxCommon.hpp:183-195, voxKernel.cu:426-435) for a tree that was built with plain 32-bit child indices because its
+// node count before deduplication did not fit 24 bits, but whose final count does
+__global__ void __launch_bounds__( 256 ) embedMasksKernel( TraceNode* __restrict__ nodes, const uint8_t* __restrict__ masks, uint32_t nNodes )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if( ( i >> 3 ) >= nNodes ) return;
+	uint2* slot = &nodes[i >> 3].slot[i & 7u];
+	const uint32_t c = slot->x;
+	if( c != SENTINEL ) slot->x = c | ( (uint32_t)masks[c] << 24 );
 }
 
 int zeroedScanState( hako_ctx* ctx, cudaStream_t s, uint64_t tiles, void** mem, ScanState* st )
@@ -332,8 +345,9 @@ int zeroedScanState( hako_ctx* ctx, cudaStream_t s, uint64_t tiles, void** mem, 
 } // namespace
 
 int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, uint64_t n, int gridRes, int dag,
-					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodesOut, uint32_t* launchesOut )
+					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodesOut, uint32_t* launchesOut, int* wideOut )
 {
+	if( wideOut ) *wideOut = 0;
 	*nodesOut = nullptr;
 	*masksOut = nullptr;
 	*nNodesOut = 0;
@@ -375,11 +389,18 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 	for( int l = 0; l < levels; l++ ) pool += ( dag && l == 0 ) ? ( G[0] < 255 ? G[0] : 255 ) : G[l];
 	uint64_t maxUpper = 0; // largest group count of a level >= 1 (temp node storage / hash table sizing)
 	for( int l = 1; l < levels; l++ ) maxUpper = G[l] > maxUpper ? G[l] : maxUpper;
-	if( !dag && pool >= 0xFFFFFFull )
+	if( pool >= 0xFFFFFFFFull )
 	{
-		setError( "octree: %llu nodes exceed the 24-bit node index (voxCommon.hpp:183-195); use the DAG build", (unsigned long long)pool );
+		setError( "octree: %llu nodes before deduplication exceed the 32-bit node index", (unsigned long long)pool );
 		return HAKO_E_LIMIT;
 	}
+	// The reference keeps a child's mask in the top byte of its 32-bit pointer (voxCommon.hpp:183-195), so 2^24 - 1 nodes is the
+	// ceiling of its format.  When the node count BEFORE deduplication does not fit, the tree is built with plain 32-bit child
+	// indices; if the final count fits 24 bits after all the masks are embedded at the end (one more pass), otherwise the tree
+	// stays in the wide layout (the traversal then reads the child's mask from the side array).  HAKO_FORCE_WIDE=1: tests.
+	const char* forceEnv = getenv( "HAKO_FORCE_WIDE" );
+	const bool forceWide = forceEnv && atoi( forceEnv ) != 0;
+	const int wide = ( pool >= 0xFFFFFFull || forceWide ) ? 1 : 0;
 
 	TraceNode* nodes = nullptr;
 	uint8_t* masks = nullptr;
@@ -443,14 +464,14 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 				{
 					CK( cudaMemsetAsync( leafTables, 0xFF, 512 * 4, s ) );
 					HAKO_LAUNCH( ctx, kLeafDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
-								 leafTables, nodes, masks, 0u );
+								 leafTables, nodes, masks, 0u, wide );
 					HAKO_LAUNCH( ctx, leafRankKernel, 1, 256, 0, s, leafTables, leafTables + 256, nodes, masks, ls );
-					HAKO_LAUNCH( ctx, leafAssignKernel, divUp( Gl, 256 ), 256, 0, s, groupMask, Gl, leafTables + 256, nC );
+					HAKO_LAUNCH( ctx, leafAssignKernel, divUp( Gl, 256 ), 256, 0, s, groupMask, Gl, leafTables + 256, nC, wide );
 				}
 				else
 				{
 					HAKO_LAUNCH( ctx, kUpperDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
-								 (uint32_t*)nullptr, nodes, masks, 0u );
+								 (uint32_t*)nullptr, nodes, masks, 0u, wide );
 					uint32_t tsz = 1;
 					while( tsz < 2 * (uint64_t)Gl ) tsz <<= 1;
 					CK( cudaMemsetAsync( table, 0xFF, (size_t)tsz * 4, s ) );
@@ -461,17 +482,17 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 					ScanState st2;
 					if( ( r = zeroedScanState( ctx, s, tiles2, &scanMem, &st2 ) ) ) break;
 					HAKO_LAUNCH( ctx, dagLookupKernel, (uint32_t)tiles2, OB_BLOCK, 0, s, groupNode, groupMask, Gl, table, tsz - 1, st2, rep, rankOf, nodes, masks, ls, l );
-					HAKO_LAUNCH( ctx, dagAssignKernel, divUp( Gl, 256 ), 256, 0, s, rep, rankOf, groupMask, Gl, ls, l, nC );
+					HAKO_LAUNCH( ctx, dagAssignKernel, divUp( Gl, 256 ), 256, 0, s, rep, rankOf, groupMask, Gl, ls, l, nC, wide );
 				}
 			}
 			else
 			{
 				if( l == 0 )
 					HAKO_LAUNCH( ctx, kLeafNaive, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
-								 (uint32_t*)nullptr, nodes, masks, naiveBase );
+								 (uint32_t*)nullptr, nodes, masks, naiveBase, wide );
 				else
 					HAKO_LAUNCH( ctx, kUpperNaive, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
-								 (uint32_t*)nullptr, nodes, masks, naiveBase );
+								 (uint32_t*)nullptr, nodes, masks, naiveBase, wide );
 				naiveBase += Gl;
 			}
 			cudaFreeAsync( scanMem, s );
@@ -494,7 +515,16 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 			ctx->stats.hostSyncs++;
 			nNodes = *(uint32_t*)ctx->pinned;
 		}
-		if( nNodes >= 0xFFFFFFu )
+		int stayWide = 0;
+		if( wide )
+		{
+			if( nNodes < 0xFFFFFFu && !forceWide )
+				HAKO_LAUNCH( ctx, embedMasksKernel, divUp( (uint64_t)nNodes * 8, 256 ), 256, 0, s, nodes, masks, nNodes );
+			else
+				stayWide = 1;
+		}
+		if( wideOut ) *wideOut = stayWide;
+		if( stayWide && !wideOut )
 		{
 			setError( "octree: %u nodes exceed the 24-bit node index (voxCommon.hpp:183-195)", nNodes );
 			r = HAKO_E_LIMIT;

@@ -97,6 +97,8 @@ int hako_octree_info_get( const hako_octree* o, hako_octree_info* out )
 	out->gridRes = o->gridRes;
 	out->deviceBytes = (uint64_t)o->numberOfNodes * ( sizeof( TraceNode ) + 1 ) + ( o->attrs ? (uint64_t)o->numberOfVoxels * 8 : 0 ) +
 					   ( o->mortons ? (uint64_t)o->numberOfVoxels * 8 : 0 );
+	out->wideIndex = (uint32_t)o->wide;
+	out->reserved = 0;
 	return HAKO_OK;
 }
 
@@ -105,6 +107,11 @@ int hako_octree_export( const hako_octree* o, hako_stream stream, hako_node68* n
 	CHECK_ARG( o, "hako_octree_export: null octree" );
 	cudaStream_t s = (cudaStream_t)stream;
 	HAKO_CUDA( cudaSetDevice( o->ctx->device ) );
+	if( nodes && o->numberOfNodes && o->wide )
+	{
+		hako::setError( "hako_octree_export: a wide-index tree (%u nodes) has no representation in the reference's 68-byte layout (24-bit child index)", o->numberOfNodes );
+		return HAKO_E_LIMIT;
+	}
 	if( nodes && o->numberOfNodes )
 	{
 		hako_node68* staged = nullptr;
@@ -179,6 +186,7 @@ int hako_octree_create_replica( hako_ctx* ctx, const hako_octree_info* info, hak
 	o->emissionScale = info->emissionScale;
 	o->hasEmission = info->hasEmission;
 	o->gridRes = info->gridRes;
+	o->wide = (int)info->wideIndex;
 	int r = dalloc( ctx, &o->nodes, o->numberOfNodes, 0 );
 	if( !r ) r = dalloc( ctx, &o->masks, o->numberOfNodes, 0 );
 	if( !r ) r = dalloc( ctx, &o->attrs, o->numberOfVoxels, 0 );

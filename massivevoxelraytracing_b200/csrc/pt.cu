@@ -722,7 +722,8 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 					const float4 o = __ldg( &tp.vertices[slot].a );
 					const float4 d = __ldcs( tp.dirs + addr );
 					shadow = tp.shadowFirst && k == 0;
-					flying = tr.begin( tree, V3{ o.x, o.y, o.z }, V3{ d.x, d.y, d.z } );
+					flying = tree.wide ? tr.template begin<true>( tree, V3{ o.x, o.y, o.z }, V3{ d.x, d.y, d.z } )
+									   : tr.template begin<false>( tree, V3{ o.x, o.y, o.z }, V3{ d.x, d.y, d.z } );
 					if( !flying ) __stcs( tp.results + addr, make_float4( 0.0f, 0.0f, 0.0f, 0.0f ) ); // misses the root box
 					traced++;
 				}
@@ -734,7 +735,8 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 #pragma unroll 1
 			for( int it = 0; it < tp.burst; it++ )
 			{
-				const int r = tr.ordinary ? tr.template step<true>( tree, shadow, stk ) : tr.template step<false>( tree, shadow, stk );
+				const int r = tree.wide ? ( tr.ordinary ? tr.template step<true, true>( tree, shadow, stk ) : tr.template step<false, true>( tree, shadow, stk ) )
+										: ( tr.ordinary ? tr.template step<true, false>( tree, shadow, stk ) : tr.template step<false, false>( tree, shadow, stk ) );
 				if( r == TRAV_CONTINUE ) continue;
 				flying = false;
 				if( r == TRAV_HIT )

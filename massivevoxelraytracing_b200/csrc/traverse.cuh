@@ -48,11 +48,14 @@ struct Traversal
 	float tx1, ty1, tz1;
 	uint32_t node, level, childMask, skipped, vMask;
 	bool ordinary; // every root slab distance is below 1e37 in magnitude: step<true> is bit-identical to step<false>
+	uint32_t nmask; // WIDE trees only: the mask of `node` (narrow trees carry it in the top byte of `node`)
 	// results of a TRAV_HIT step
 	float t;
 	int nMajor;
 
-	// false: the ray misses the root box (or the tree is empty)
+	// false: the ray misses the root box (or the tree is empty).
+	// WIDE: the tree has plain 32-bit child indices (>= 2^24 - 1 nodes); a node's mask comes from v.masks.
+	template <bool WIDE = false>
 	__device__ __forceinline__ bool begin( const OctreeView& v, V3 ro, V3 rd )
 	{
 		if( v.numberOfNodes == 0 ) return false;
@@ -91,7 +94,8 @@ struct Traversal
 		ordinary = sabs( t0x ) < big && sabs( t0y ) < big && sabs( t0z ) < big && sabs( tx1 ) < big && sabs( ty1 ) < big && sabs( tz1 ) < big;
 		sp = 0;
 		const uint32_t root = v.numberOfNodes - 1; // the root is the last node (IntersectorOctree.hpp:252)
-		node = root | ( (uint32_t)__ldg( v.masks + root ) << 24 );
+		nmask = (uint32_t)__ldg( v.masks + root );
+		node = WIDE ? root : ( root | ( nmask << 24 ) );
 		level = 0;
 		childMask = 0xFFu; // "not chosen yet" (reference: 0xFFFFFFFF)
 		skipped = 0;
@@ -105,7 +109,7 @@ struct Traversal
 	// 0 < lmax): one FMNMX3 instead of two FSETP + FSEL pairs, ~6 of ~95 instructions per step.  Rays with huge slab distances
 	// (a zero or denormal direction component against the clamped 1/rd) can produce inf - inf = NaN, where the two forms
 	// differ; they take the exact path (tests/test_gpu_traverse.py::test_random_rays_and_shadow has such rays).
-	template <bool FINITE = false>
+	template <bool FINITE = false, bool WIDE = false>
 	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, TravStack& stk )
 	{
 		const float scale = levelScale( level );
@@ -143,16 +147,18 @@ struct Traversal
 			const bool hasNext = ( childMask & mv ) == 0;
 			const uint32_t ci = childMask ^ vMask;
 			childMask |= mv;
-			if( ( ( node >> ( 24 + ci ) ) & 1u ) && !( umin < 0.0f ) )
+			const uint32_t present = WIDE ? ( ( nmask >> ci ) & 1u ) : ( ( node >> ( 24 + ci ) ) & 1u );
+			if( present && !( umin < 0.0f ) )
 			{
 				if( hasNext )
 				{
 					stk.a[sp] = make_uint4( node, __float_as_uint( tx1 ), __float_as_uint( ty1 ), __float_as_uint( tz1 ) );
-					stk.b[sp] = make_uint2( childMask | ( level << 8 ), skipped );
+					stk.b[sp] = make_uint2( childMask | ( level << 8 ) | ( WIDE ? nmask << 16 : 0u ), skipped );
 					sp++;
 				}
-				const uint2 slot = ldg_u2( &v.nodes[node & 0xFFFFFFu].slot[ci] );
+				const uint2 slot = ldg_u2( &v.nodes[WIDE ? node : ( node & 0xFFFFFFu )].slot[ci] );
 				node = slot.x;
+				if( WIDE ) nmask = ( node != 0xFFFFFFFFu ) ? (uint32_t)__ldg( v.masks + node ) : 0u; // the second dependent load of the wide layout
 				tx1 = x1;
 				ty1 = y1;
 				tz1 = z1;
@@ -175,7 +181,8 @@ struct Traversal
 			ty1 = __uint_as_float( a.z );
 			tz1 = __uint_as_float( a.w );
 			childMask = b.x & 0xFFu;
-			level = b.x >> 8;
+			level = WIDE ? ( ( b.x >> 8 ) & 0xFFu ) : ( b.x >> 8 );
+			if( WIDE ) nmask = b.x >> 16;
 			skipped = b.y;
 		}
 		return TRAV_CONTINUE;
@@ -188,21 +195,43 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 {
 	Traversal tr;
 	TravStack stk;
-	if( !tr.begin( v, ro, rd ) ) return false;
 	int r;
-	if( tr.ordinary )
+	if( v.wide )
 	{
-		do
+		// trees beyond the reference format's 2^24 - 1 nodes
+		if( !tr.template begin<true>( v, ro, rd ) ) return false;
+		if( tr.ordinary )
 		{
-			r = tr.template step<true>( v, shadow, stk );
-		} while( r == TRAV_CONTINUE );
+			do
+			{
+				r = tr.template step<true, true>( v, shadow, stk );
+			} while( r == TRAV_CONTINUE );
+		}
+		else
+		{
+			do
+			{
+				r = tr.template step<false, true>( v, shadow, stk );
+			} while( r == TRAV_CONTINUE );
+		}
 	}
 	else
 	{
-		do
+		if( !tr.template begin<false>( v, ro, rd ) ) return false;
+		if( tr.ordinary )
 		{
-			r = tr.template step<false>( v, shadow, stk );
-		} while( r == TRAV_CONTINUE );
+			do
+			{
+				r = tr.template step<true, false>( v, shadow, stk );
+			} while( r == TRAV_CONTINUE );
+		}
+		else
+		{
+			do
+			{
+				r = tr.template step<false, false>( v, shadow, stk );
+			} while( r == TRAV_CONTINUE );
+		}
 	}
 	if( r == TRAV_MISS ) return false;
 	*tOut = tr.t;

@@ -289,6 +289,36 @@ def test_build_sweep_full_mesh_invariants(hk, ctx, bunny, golden, grid):
     g2.cleanUp()
 
 
+def test_build_beyond_the_24_bit_node_index(hk, ctx, bunny):
+    """BASELINE config 3 at 2^14 on a dragon-like mesh: 18.9 M DAG nodes, more than the reference's child pointers can address.
+    The tree is kept in the wide-index layout; invariants as in the sweep test, plus agreement of the silhouette with the same
+    mesh at 4096^3 (reference layout)."""
+    from scenes import dragon_standin
+    tris, col, emi = dragon_standin(5, 0.15)
+    W, H = 1920, 1080
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H)
+    hits = {}
+    for grid in (4096, 16384):
+        origin, dps = scene_params(tris, grid)
+        g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+        info = g.info()
+        st = ctx.build_stats()
+        _, t, nm, vi = g.render(cam, W, H, rgba=False)
+        hit = t != FLT_MAX
+        hits[grid] = hit
+        assert int(vi[hit].max()) < st["uniqueVoxels"] and (nm[hit] >= 0).all() and (nm[hit] <= 2).all()
+        if grid == 16384:
+            assert info.wideIndex == 1 and info.numberOfNodes >= (1 << 24) - 1
+            assert st["uniqueVoxels"] > 500_000_000
+            with pytest.raises(hk.HakoError):
+                g.export(True, False, False)
+        else:
+            assert info.wideIndex == 0
+        g.cleanUp()
+    assert (hits[4096] != hits[16384]).mean() < 0.01
+    assert abs(int(hits[4096].sum()) - int(hits[16384].sum())) < 0.01 * hits[4096].sum()
+
+
 def test_build_subdivided_mesh_matches_oracle(hk, ctx, oracle, bunny):
     """many small triangles (the dragon-like regime): 82k triangles at 512^3"""
     tris = subdivide(bunny[0], 2, 0.15)

@@ -140,3 +140,51 @@ def test_edge_rays(hk, ctx, oracle, bunny):
     assert (t != FLT_MAX).sum() > 100
     e = np.zeros((0, 3), np.float32)
     assert g.intersect(e, e)[0].size == 0
+
+
+def test_wide_index_layout_matches_reference_layout(hk, ctx, bunny, small_cases, monkeypatch):
+    """Trees with >= 2^24 - 1 nodes cannot use the reference's child pointers (index | mask << 24, voxCommon.hpp:183-195); they are
+    kept with plain 32-bit indices and the traversal reads child masks from the side array.  Forced on a small tree, that layout must
+    give bit-identical hits (primary frame, random + exotic rays, shadow rays, a path-traced step) and refuse the 68-byte export."""
+    from scenes import procedural_hdri
+    tris, col, emi = bunny
+    grid = 64
+    origin, dps = scene_params(tris, grid)
+    W, H = 320, 200
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H)
+    env = procedural_hdri(128, 64)
+    res = []
+    for force in ("0", "1"):
+        monkeypatch.setenv("HAKO_FORCE_WIDE", force)
+        g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+        assert g.info().wideIndex == int(force)
+        rgba, t, nm, vi = g.render(cam, W, H)
+        rt = g.intersect(small_cases["rays_ro"], small_cases["rays_rd"])
+        rs = g.intersect(small_cases["rays_ro"], small_cases["rays_rd"], isShadowRay=True)
+        pt = hk.PathTracer(ctx).setup()
+        pt.m_intersectorOctreeGPU = g
+        pt.maxDepth = 4
+        pt.resizeFrameBufferIfNeeded(None, 96, 64)
+        pt.loadHDRI(None, env)
+        pcam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=96, height=64, focus=6.0, lensR=0.01)
+        pt.step(None, pcam)
+        acc = pt.accumulators().copy()
+        if force == "1":
+            with pytest.raises(hk.HakoError):
+                g.export(True, False, False)
+            assert g.export(False, True, False)[1].size == g.info().numberOfVoxels      # keys / attributes still export
+        pt.m_intersectorOctreeGPU = hk.IntersectorOctreeGPU(ctx)
+        pt.cleanUp()
+        res.append((rgba, t, nm, vi, rt, rs, acc, g.info().numberOfNodes))
+        g.cleanUp()
+    a, b = res
+    assert a[7] == b[7]
+    for k in range(4):
+        assert np.array_equal(a[k].view(np.uint8), b[k].view(np.uint8))
+    for k in (4, 5):
+        for x, y in zip(a[k], b[k]):
+            assert np.array_equal(np.asarray(x).view(np.uint8), np.asarray(y).view(np.uint8))
+    assert np.array_equal(a[6].view(np.uint32), b[6].view(np.uint32))
+    # the same rays against the golden values of the reference
+    assert np.array_equal(b[4][0].view(np.uint32), small_cases["rays_t"].view(np.uint32))
+    assert np.array_equal(b[4][2], small_cases["rays_vindex"])
