@@ -391,6 +391,8 @@ def run_ours(args):
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
                 "traffic": load_profile_value("render_dram_bytes_per_launch", None),
                 "algorithmic_bytes_per_ray": bytes_per_ray, "descents_per_ray": dbar, "rays_per_launch": nrays_view, "avg_launch_ms": launch_ms,
+                "ncu": {k: load_profile_value(k, None) for k in ("render_issue_active_pct", "render_lanes_active_per_instruction", "render_l2_throughput_pct_of_peak",
+                                                                  "render_l1_hit_pct", "render_l2_hit_pct", "render_warp_instructions_per_launch", "source")},
                 "note": "pointer-chasing traversal: latency/issue-bound with the %.0f MB octree L2-resident; see profiles/ for L2 throughput, issue utilisation and warp efficiency"
                         % (info.numberOfNodes * 64 / 1e6)}
     cfg = base_config(world)
