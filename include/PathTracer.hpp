@@ -5,8 +5,8 @@
 //
 // Differences a caller sees
 //   - setup() takes no kernel path / include dir / isNvidia flag (no nvrtc), and allocates no 1 GiB stack pool;
-//   - loadHDRI() takes decoded RGBA32F pixels (what pr::Image2DRGBA32::loadFromHDR yields, libs/prlib/src/prp.cpp:353-366);
-//     decoding a .hdr file stays with the caller's image library;
+//   - loadHDRI( stream, file, filePrimary ) as in the reference (Radiance .hdr, decoded by hako_image_load_hdr exactly as
+//     stbi_loadf( .., 4 ) does, libs/prlib/src/prp.cpp:353-366), plus an overload taking decoded RGBA32F pixels;
 //   - step() takes the pinhole camera directly (hako_camera == CameraPinhole).  A pr::Camera3D caller builds it with
 //     hako_camera_lookat( origin, lookat, up, fovy, width, height, zNear, zFar, focus, lensR ), which is
 //     pr::GetCameraMatrix + CameraPinhole::initFromPerspective (PathTracer.hpp:152-156);
@@ -56,6 +56,25 @@ public:
 	void loadHDRI( hako_stream stream, const float* rgba, int width, int height, const float* rgbaPrimary = nullptr, int widthPrimary = 0, int heightPrimary = 0 ) // :104-116
 	{
 		hako::check( hako_pt_load_hdri( m_pt, stream, rgba, width, height, rgbaPrimary, widthPrimary, heightPrimary ) );
+	}
+	void loadHDRI( hako_stream stream, const char* file, const char* filePrimary = nullptr ) // :104-116, the reference's signature
+	{
+		float *a = nullptr, *b = nullptr;
+		int w = 0, h = 0, wp = 0, hp = 0;
+		hako::check( hako_image_load_hdr( file, &a, &w, &h ) );
+		if( filePrimary )
+		{
+			const int r = hako_image_load_hdr( filePrimary, &b, &wp, &hp );
+			if( r )
+			{
+				hako_image_free( a );
+				hako::check( r );
+			}
+		}
+		const int r = hako_pt_load_hdri( m_pt, stream, a, w, h, b, wp, hp );
+		hako_image_free( a );
+		hako_image_free( b );
+		hako::check( r );
 	}
 	template <class Vec3>
 	void updateScene( const std::vector<Vec3>& vertices, const std::vector<Vec3>& vcolors, const std::vector<Vec3>& vemissions, hako_stream stream, const Vec3& origin, float dps,
