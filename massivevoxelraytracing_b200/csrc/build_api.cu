@@ -86,11 +86,20 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 			uint32_t he = 0;
 			if( ( r = uniqueMergeDevice( ctx, s, sk, sv, D, uk, (hako_voxel_attrib*)ua, &U, &he ) ) ) break;
 			o->hasEmission = he;
-			// keep exact-size copies resident; the D-sized work buffers go back to the pool
+			// the sorted input pair is dead: give it back BEFORE the exact-size resident copies are allocated (at billions of
+			// voxels the four D-sized work buffers plus the resident arrays do not fit 180 GB together)
+			dfree( sk, s ), dfree( sv, s );
+			if( inTmp )
+				keysTmp = valuesTmp = nullptr;
+			else
+				keys = values = nullptr;
 			if( ( r = dalloc( ctx, &o->mortons, U, s ) ) ) break;
 			if( ( r = dalloc( ctx, &o->attrs, U, s ) ) ) break;
 			CK( cudaMemcpyAsync( o->mortons, uk, U * 8, cudaMemcpyDeviceToDevice, s ) );
 			CK( cudaMemcpyAsync( o->attrs, ua, U * 8, cudaMemcpyDeviceToDevice, s ) );
+			// ... and the unique output pair before the octree build sizes its node pool
+			dfree( uk, s ), dfree( ua, s );
+			keys = values = keysTmp = valuesTmp = nullptr;
 		}
 		else
 		{
