@@ -6,6 +6,8 @@
 // -> embedMasks, with ~12 oroMalloc/oroFree.  Here: columns -> [read] -> count -> [read D] -> emit -> histogram + P onesweep
 // passes -> unique -> [read U] -> level histogram -> [read] -> 4 kernels per level -> [read node count] -> D2D copy.
 // Allocations come from the context's stream-ordered pool.
+#include <thread>
+
 #include "internal.cuh"
 
 using namespace hako;
@@ -49,7 +51,8 @@ static void initOctree( hako_octree* o, hako_ctx* ctx, const float origin[3], fl
 }
 
 static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float* pos_d, const float* col_d, const float* emi_d, uint32_t nTriangles,
-									 const float origin[3], float dps, int gridRes, hako_octree** out )
+									 const float origin[3], float dps, int gridRes, hako_octree** out,
+									 const std::function<int()>& beforeAttributesAreRead = std::function<int()>() )
 {
 	hako_build_stats& st = ctx->stats;
 	const uint64_t launches0 = ctx->launches.load();
@@ -68,7 +71,9 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 	}
 		CK( cudaEventRecord( ctx->ev[1], s ) );
 		uint64_t D = 0;
-		if( ( r = voxelizeDevice( ctx, s, pos_d, col_d, emi_d, nTriangles, o->lower, dps, gridRes, 1 /* sixSeparating: voxKernel.cu:68,109 */, &keys, &values, &D ) ) ) break;
+		if( ( r = voxelizeDevice( ctx, s, pos_d, col_d, emi_d, nTriangles, o->lower, dps, gridRes, 1 /* sixSeparating: voxKernel.cu:68,109 */, &keys, &values, &D,
+								   beforeAttributesAreRead ) ) )
+			break;
 		st.dumpedVoxels = D;
 		CK( cudaEventRecord( ctx->ev[2], s ) );
 		uint64_t U = 0;
@@ -174,12 +179,39 @@ int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, cons
 	const uint64_t nf = (uint64_t)nTriangles * 9;
 	HAKO_TRY( dalloc( ctx, &d, nf * 3, s ) );
 	int r = 0;
-	if( nf )
+	// The positions go up first; the colour / emission arrays follow on a helper thread while the counting pass of the voxelizer
+	// (which reads positions only) already runs: their copies are joined right before the first kernel that reads them.
+	std::thread helper;
+	int helperResult = 0;
+	if( nf && nf * 4 < ( 4u << 20 ) )
 	{
-		const H2DSegment segs[3] = { { d, pos, nf * 4 }, { d + nf, col, nf * 4 }, { d + 2 * nf, emi, nf * 4 } };
-		r = uploadSegments( ctx, s, segs, 3 );
+		// small meshes: three plain copies, no staging threads
+		cudaError_t e = cudaMemcpyAsync( d, pos, nf * 4, cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( d + nf, col, nf * 4, cudaMemcpyHostToDevice, s );
+		if( e == cudaSuccess ) e = cudaMemcpyAsync( d + 2 * nf, emi, nf * 4, cudaMemcpyHostToDevice, s );
+		if( e != cudaSuccess ) r = cudaFail( e, "H2D vertices", __FILE__, __LINE__ );
 	}
-	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out );
+	else if( nf )
+	{
+		const H2DSegment segPos = { d, pos, nf * 4 };
+		r = uploadSegments( ctx, s, &segPos, 1 );
+		if( r == 0 )
+			helper = std::thread( [&]() {
+				const H2DSegment segs[2] = { { d + nf, col, nf * 4 }, { d + 2 * nf, emi, nf * 4 } };
+				helperResult = cudaSetDevice( ctx->device ) == cudaSuccess ? uploadBegin( ctx, s, segs, 2, false ) : HAKO_E_CUDA;
+			} );
+	}
+	auto join = [&]() -> int {
+		if( helper.joinable() ) helper.join();
+		if( helperResult )
+		{
+			setError( "hako_octree_build: staged upload of the colour / emission arrays failed" );
+			return helperResult;
+		}
+		return uploadFinish( ctx, s );
+	};
+	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out, join );
+	if( helper.joinable() ) helper.join();
 	dfree( d, s );
 	return r;
 }

@@ -80,7 +80,10 @@ static bool isPinned( const void* p )
 	return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
 }
 
-int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n )
+// Puts the copies in flight on the stager's own streams (ordered behind everything enqueued on `s` so far) and returns when the
+// last chunk has been handed to the DMA engine.  `s` does NOT wait for them until uploadFinish( ctx, s ) is called, so a caller
+// may run this on a helper thread and keep launching kernels that do not need the data on `s`.
+int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, bool orderBehindStream )
 {
 	struct Job
 	{
@@ -88,25 +91,29 @@ int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n
 		const char* src;
 		size_t bytes;
 	};
+	HAKO_TRY( makeStager( ctx ) );
+	Stager* st = ctx->stager;
+	if( orderBehindStream )
+	{
+		// the destination was allocated stream-ordered on s: the worker streams start behind that point.  (A helper thread that
+		// continues an upload whose first part already did this passes false: it must not touch `s` while the caller enqueues on it.)
+		HAKO_CUDA( cudaEventRecord( st->start, s ) );
+		for( int t = 0; t < st->workers; t++ ) HAKO_CUDA( cudaStreamWaitEvent( st->stream[t], st->start, 0 ) );
+	}
 	std::vector<Job> jobs;
 	for( int i = 0; i < n; i++ )
 	{
 		if( segs[i].bytes == 0 ) continue;
 		if( segs[i].bytes < ( 1u << 20 ) || isPinned( segs[i].src ) )
 		{
-			HAKO_CUDA( cudaMemcpyAsync( segs[i].dst, segs[i].src, segs[i].bytes, cudaMemcpyHostToDevice, s ) );
+			// small or already pinned: straight onto the wire (worker stream 0; its buffer-0 event is re-recorded below)
+			HAKO_CUDA( cudaMemcpyAsync( segs[i].dst, segs[i].src, segs[i].bytes, cudaMemcpyHostToDevice, st->stream[0] ) );
 			continue;
 		}
 		for( size_t off = 0; off < segs[i].bytes; off += Stager::CHUNK )
 			jobs.push_back( { (char*)segs[i].dst + off, (const char*)segs[i].src + off, std::min( Stager::CHUNK, segs[i].bytes - off ) } );
 	}
-	if( jobs.empty() ) return 0;
-	HAKO_TRY( makeStager( ctx ) );
-	Stager* st = ctx->stager;
-	const int W = std::min<int>( st->workers, (int)jobs.size() );
-	// the destination was allocated stream-ordered on s: the worker streams start behind that point
-	HAKO_CUDA( cudaEventRecord( st->start, s ) );
-	for( int t = 0; t < W; t++ ) HAKO_CUDA( cudaStreamWaitEvent( st->stream[t], st->start, 0 ) );
+	const int W = std::max( 1, std::min<int>( st->workers, (int)jobs.size() ) );
 	std::atomic<int> err{ 0 };
 	const int device = ctx->device;
 	auto work = [&]( int t ) {
@@ -138,9 +145,23 @@ int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n
 	work( 0 );
 	for( auto& th : threads ) th.join();
 	if( err.load() ) return cudaFail( (cudaError_t)err.load(), "staged H2D", __FILE__, __LINE__ );
-	// s continues behind the last chunk of every worker (both buffers' events cover the tail)
-	for( int t = 0; t < W; t++ )
+	// direct copies (and an empty job list) are covered by re-recording stream 0's events
+	if( jobs.empty() || W == 1 )
+		for( int b = 0; b < Stager::NBUF; b++ ) HAKO_CUDA( cudaEventRecord( st->ev[0][b], st->stream[0] ) );
+	return 0;
+}
+// `s` continues behind the last chunk of every worker (both buffers' events cover the tail)
+int uploadFinish( hako_ctx* ctx, cudaStream_t s )
+{
+	Stager* st = ctx->stager;
+	if( !st ) return 0;
+	for( int t = 0; t < st->workers; t++ )
 		for( int b = 0; b < Stager::NBUF; b++ ) HAKO_CUDA( cudaStreamWaitEvent( s, st->ev[t][b], 0 ) );
 	return 0;
+}
+int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n )
+{
+	HAKO_TRY( uploadBegin( ctx, s, segs, n, true ) );
+	return uploadFinish( ctx, s );
 }
 } // namespace hako

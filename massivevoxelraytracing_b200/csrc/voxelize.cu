@@ -460,12 +460,14 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 }
 
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
-					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D )
+					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D,
+					const std::function<int()>& beforeEmit )
 {
+	bool emitHookRun = false;
 	*D = 0;
 	if( keysOut ) *keysOut = nullptr;
 	if( valuesOut ) *valuesOut = nullptr;
-	if( nTriangles == 0 ) return 0;
+	if( nTriangles == 0 ) return beforeEmit ? beforeEmit() : 0;
 	uint32_t* colOffset = nullptr;
 	uint32_t* colCount = nullptr;
 	uint64_t* totals = nullptr; // [0] columns, [1] voxels
@@ -518,9 +520,16 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		if( total == 0 || !keysOut ) break;
 		if( ( r = dalloc( ctx, keysOut, total, s ) ) ) break;
 		if( ( r = dalloc( ctx, valuesOut, total, s ) ) ) break;
+		emitHookRun = true;
+		if( beforeEmit && ( r = beforeEmit() ) ) break;
 		HAKO_LAUNCH( ctx, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
 					 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, (uint32_t)total, *keysOut, *valuesOut );
 	} while( 0 );
+	if( beforeEmit && !emitHookRun )
+	{
+		const int rh = beforeEmit(); // the caller's upload must be joined on every path
+		if( r == 0 ) r = rh;
+	}
 	dfree( colOffset, s ), dfree( colCount, s ), dfree( totals, s );
 	if( r && keysOut )
 	{
