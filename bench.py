@@ -7,9 +7,10 @@ reported beside it.  Workload at N=1 = BASELINE config[1]: the (synthetic stand-
 voxRT's default camera, voxRT.cpp:69-72), so one step is ~33 M rays and is not launch-bound.
 
   value      rays / s with the octree resident in HBM (device outputs), CUDA events on the launching stream
-  e2e        same rays through the host-buffer C-ABI call (hako_render_primary): per view the camera goes in by value and the
-             RGBA8 frame (4 B per ray, what voxRTGPU downloads per frame) comes back to pinned host memory inside the timed
-             region; e2e.hit_records is the same call returning t / nMajor / vIndex (12 B per ray)
+  e2e        same rays through the host-buffer C-ABI call (hako_render_primary_views, the frames of a step in one call): the
+             cameras go in by value and the RGBA8 frames (4 B per ray, what voxRTGPU downloads per frame) come back to pinned
+             host memory inside the timed region; e2e.hit_records is the same call returning t / nMajor / vIndex (12 B per
+             ray), e2e.per_frame_call the one-synchronous-call-per-frame form (hako_render_primary)
   roofline   dominant kernel = renderPrimaryKernel; algorithmic bytes = rays * (12 + 8 * descents/ray)
   cpu_baseline / --impl reference   the reference's own CPU traversal (oracle/_ref when present, else the oracle port)
              on the box's host cores, on a bounded sample of the same views
@@ -157,7 +158,9 @@ def base_config(n_gpus):
                         "missing from the reference checkout) voxelized at %d^3, %dx%d pixel-centre primary rays, %d orbit views per step per GPU"
                         % (MESH_LEVELS, 5110 * 4 ** MESH_LEVELS, GRID, W, H, VIEWS),
             "grid": GRID, "image": [W, H], "views_per_step_per_gpu": VIEWS,
-            "parallelism": "octree built on rank 0 + NCCL broadcast; views sharded over %d GPU(s), no data-path collective" % n_gpus}
+            "parallelism": "octree built on rank 0 + NCCL broadcast; views sharded over %d GPU(s), no data-path collective" % n_gpus,
+            "streams": "the frames of a step alternate between CUDA streams (4 per GPU unless HAKO_BENCH_STREAMS says otherwise; tail of frame i overlaps the head of frame i+1); "
+                       "timed with events on the stream that forks and joins them"}
 
 
 def run_reference(args):
@@ -246,10 +249,22 @@ def run_ours(args):
     nm_d = torch.empty((VIEWS, nrays_view), dtype=torch.int32, device=dev)
     vi_d = torch.empty((VIEWS, nrays_view), dtype=torch.int32, device=dev)
     stream = torch.cuda.current_stream()
+    # frames alternate between two streams (what hako_render_primary_views does inside): a frame is one wave of CTAs whose
+    # tail -- the few long rays -- would otherwise idle most SMs before the next frame starts
+    n_streams = max(1, int(os.environ.get("HAKO_BENCH_STREAMS", "4")))
+    sides = [torch.cuda.Stream(device=dev) for _ in range(n_streams - 1)]
+    fork, joins = torch.cuda.Event(), [torch.cuda.Event() for _ in sides]
 
     def step_device():
+        fork.record(stream)
+        for sd in sides:
+            sd.wait_event(fork)
         for i, cam in enumerate(cams):
-            octree.render_device(cam, W, H, t=t_d[i], nMajor=nm_d[i], vIndex=vi_d[i], stream=stream)
+            k = i % n_streams
+            octree.render_device(cam, W, H, t=t_d[i], nMajor=nm_d[i], vIndex=vi_d[i], stream=sides[k - 1] if k else stream)
+        for sd, j in zip(sides, joins):
+            j.record(sd)
+            stream.wait_event(j)
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -284,13 +299,24 @@ def run_ours(args):
     rgba_h = torch.empty(nrays_view * 4, dtype=torch.uint8).pin_memory().numpy()
     import ctypes as C
 
+    # the frames of a step land in VIEWS distinct pinned host frames (hako_render_primary_views: frame i+1 is traced while
+    # frame i is copied out); the one-call-per-frame form (hako_render_primary, trace and copy of a frame in sequence) is
+    # timed beside it
+    cam_arr = (hk.Camera * VIEWS)(*cams)
+    rgba_all = torch.empty(VIEWS * nrays_view * 4, dtype=torch.uint8).pin_memory().numpy()
+    t_all = torch.empty(VIEWS * nrays_view, dtype=torch.float32).pin_memory().numpy()
+    nm_all = torch.empty(VIEWS * nrays_view, dtype=torch.int32).pin_memory().numpy()
+    vi_all = torch.empty(VIEWS * nrays_view, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+
     def step_host_rgba():
-        for cam in cams:
-            hk._abi.check(ctx.lib.hako_render_primary(octree.h, None, C.byref(cam), W, H, 0, H, 0, rgba_h.ctypes.data, None, None, None))
+        hk._abi.check(ctx.lib.hako_render_primary_views(octree.h, None, cam_arr, VIEWS, W, H, 0, rgba_all.ctypes.data, None, None, None))
 
     def step_host_records():
+        hk._abi.check(ctx.lib.hako_render_primary_views(octree.h, None, cam_arr, VIEWS, W, H, 0, None, t_all.ctypes.data, nm_all.ctypes.data, vi_all.ctypes.data))
+
+    def step_host_rgba_per_frame():
         for cam in cams:
-            hk._abi.check(ctx.lib.hako_render_primary(octree.h, None, C.byref(cam), W, H, 0, H, 0, None, t_h.ctypes.data, nm_h.ctypes.data, vi_h.ctypes.data))
+            hk._abi.check(ctx.lib.hako_render_primary(octree.h, None, C.byref(cam), W, H, 0, H, 0, rgba_h.ctypes.data, None, None, None))
 
     def time_host(fn):
         fn()
@@ -306,6 +332,10 @@ def run_ours(args):
 
     e2e_total = time_host(step_host_rgba)
     e2e_rec_total = time_host(step_host_records)
+    e2e_frame_total = time_host(step_host_rgba_per_frame)
+    # the frames that came back are the frames the device-resident leg produced
+    e2e_parity = bool(np.array_equal(t_all.view(np.uint32), t_d.cpu().numpy().reshape(-1).view(np.uint32))
+                      and np.array_equal(vi_all, vi_d.cpu().numpy().reshape(-1).view(np.uint32)))
     sampler.stop_flag = True
     sampler.join(timeout=2)
     hits_view0 = int((t_d[0] != 3.402823466e38).sum().item())
@@ -403,9 +433,12 @@ def run_ours(args):
             "config": cfg, "clocks": sampler.summary(),
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 60 * VIEWS, "d2h_bytes_per_step": 4 * nrays_view * VIEWS,
                     "ms_per_step": e2e_total / args.steps,
-                    "call": "hako_render_primary (host buffers, pinned), one call per view, RGBA8 frame out = the voxRTGPU frame (render kernel + D2H of the image, voxRTGPU.cpp:191-208)",
+                    "call": "hako_render_primary_views (pinned host frames): the 16 views of a step in one call, RGBA8 frames out = the voxRTGPU frame loop (render kernel + D2H of the image, voxRTGPU.cpp:150-208), frame i+1 traced while frame i is copied",
+                    "per_frame_call": {"value": rays_step_all * args.steps / (e2e_frame_total * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_frame_total / args.steps,
+                                       "call": "hako_render_primary, one synchronous call per frame"},
+                    "frames_equal_device_leg": e2e_parity,
                     "hit_records": {"value": rays_step_all * args.steps / (e2e_rec_total * 1e-3) / 1e6, "unit": "Mrays/s", "d2h_bytes_per_step": 12 * nrays_view * VIEWS,
-                                    "ms_per_step": e2e_rec_total / args.steps, "call": "same call returning t / nMajor / vIndex (12 B per ray) instead of the image"}},
+                                    "ms_per_step": e2e_rec_total / args.steps, "call": "same call returning t / nMajor / vIndex (12 B per ray) instead of the images"}},
             "gpu_launches": int(launches), "roofline": roofline, "path_tracing": pt_res, "cpu_baseline": cpu, "build": build, "build_sweep": sweep,
             "hits_view0": hits_view0,
             "parity_vs_cpu_reference_view0": parity, "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware"}

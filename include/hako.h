@@ -174,6 +174,11 @@ int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_ca
 						 int showVertexColor, uint8_t* rgba, float* t, int32_t* nMajor, uint32_t* vIndex );
 int hako_render_primary_device( const hako_octree* o, hako_stream stream, const hako_camera* cam, int w, int h, int y0, int y1,
 								int showVertexColor, uint8_t* rgba_d, float* t_d, int32_t* nMajor_d, uint32_t* vIndex_d );
+/* A run of nViews whole frames in one call -- the orbit loop of voxRTGPU.cpp:150-208 without the window: cams[i] -> frame i of
+ * every non-NULL output (HOST pointers, nViews x h x w, frame-major).  Frame i+1 is traced while frame i is copied out, so the
+ * call costs about max( trace, D2H ) per frame instead of their sum; results equal nViews hako_render_primary calls. */
+int hako_render_primary_views( const hako_octree* o, hako_stream stream, const hako_camera* cams, int nViews, int w, int h,
+							   int showVertexColor, uint8_t* rgba, float* t, int32_t* nMajor, uint32_t* vIndex );
 
 /* ---- camera (host-side math; no device work) ----
  * CameraPinhole::initFromPerspective( viewMatrix, projMatrix, focus, lensR ), renderCommon.hpp:21-35.

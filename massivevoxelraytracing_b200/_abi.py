@@ -77,6 +77,7 @@ SIGNATURES = {
     "hako_intersect_batch_device": (i32, [vp, vp, vp, vp, u64, i32, vp, vp, vp]),
     "hako_render_primary": (i32, [vp, vp, C.POINTER(Camera), i32, i32, i32, i32, i32, vp, vp, vp, vp]),
     "hako_render_primary_device": (i32, [vp, vp, C.POINTER(Camera), i32, i32, i32, i32, i32, vp, vp, vp, vp]),
+    "hako_render_primary_views": (i32, [vp, vp, C.POINTER(Camera), i32, i32, i32, i32, vp, vp, vp, vp]),
     "hako_camera_from_matrices": (i32, [vp, vp, f32, f32, C.POINTER(Camera)]),
     "hako_camera_lookat": (i32, [vp, vp, vp, f32, i32, i32, f32, f32, f32, f32, C.POINTER(Camera)]),
     "hako_pt_create": (i32, [vp, vp, pp]),

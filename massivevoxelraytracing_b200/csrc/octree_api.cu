@@ -329,4 +329,77 @@ int hako_render_primary( const hako_octree* o, hako_stream stream, const hako_ca
 	dfree( rgba_d, s ), dfree( t_d, s ), dfree( nm_d, s ), dfree( vi_d, s );
 	return r;
 }
+
+// A run of frames (the orbit loop of voxRTGPU.cpp:150-208, headless): frame i is traced while frame i-1 is on its way to the
+// host.  A ring of RING device frames; frame kernels alternate between the two band streams, copies are queued on the copy
+// stream, and the host waits once, for the last copy.
+int hako_render_primary_views( const hako_octree* o, hako_stream stream, const hako_camera* cams, int nViews, int w, int h,
+							   int showVertexColor, uint8_t* rgba, float* t, int32_t* nMajor, uint32_t* vIndex )
+{
+	CHECK_ARG( o && ( cams || nViews == 0 ), "hako_render_primary_views: null argument" );
+	CHECK_ARG( w > 0 && h > 0 && nViews >= 0, "hako_render_primary_views: bad image / view count" );
+	CHECK_ARG( !( showVertexColor && rgba && !o->attrs ), "hako_render_primary_views: showVertexColor needs voxel attributes" );
+	if( nViews == 0 ) return HAKO_OK;
+	hako_ctx* ctx = o->ctx;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	const uint64_t n = (uint64_t)w * h;
+	enum { RING = 4 };
+	const int ring = nViews < RING ? nViews : RING;
+	uint8_t* rgba_d = nullptr;
+	float* t_d = nullptr;
+	int32_t* nm_d = nullptr;
+	uint32_t* vi_d = nullptr;
+	cudaEvent_t traced[RING] = {}, copied[RING] = {};
+	int r = 0;
+	cudaError_t e = cudaSuccess;
+	do
+	{
+		if( rgba && ( r = dalloc( ctx, &rgba_d, n * 4 * ring, s ) ) ) break;
+		if( t && ( r = dalloc( ctx, &t_d, n * ring, s ) ) ) break;
+		if( nMajor && ( r = dalloc( ctx, &nm_d, n * ring, s ) ) ) break;
+		if( vIndex && ( r = dalloc( ctx, &vi_d, n * ring, s ) ) ) break;
+		for( int i = 0; i < ring && e == cudaSuccess; i++ )
+		{
+			e = cudaEventCreateWithFlags( &traced[i], cudaEventDisableTiming );
+			if( e == cudaSuccess ) e = cudaEventCreateWithFlags( &copied[i], cudaEventDisableTiming );
+		}
+		if( e == cudaSuccess ) e = cudaEventRecord( ctx->bandEv[16], s ); // the device frames were allocated on `s`
+		for( int i = 0; i < 2 && e == cudaSuccess; i++ ) e = cudaStreamWaitEvent( ctx->bandStream[i], ctx->bandEv[16], 0 );
+		for( int v = 0; v < nViews && r == 0 && e == cudaSuccess; v++ )
+		{
+			const int slot = v % ring;
+			const uint64_t dOff = (uint64_t)slot * n, hOff = (uint64_t)v * n;
+			cudaStream_t bs = ctx->bandStream[v & 1];
+			if( v >= ring && ( e = cudaStreamWaitEvent( bs, copied[slot], 0 ) ) != cudaSuccess ) break; // the slot's previous frame has left
+			if( ( r = launchRenderPrimary( ctx, bs, o->view(), cams[v], w, h, 0, h, showVertexColor, rgba_d ? rgba_d + dOff * 4 : nullptr, t_d ? t_d + dOff : nullptr,
+										   nm_d ? nm_d + dOff : nullptr, vi_d ? vi_d + dOff : nullptr ) ) )
+				break;
+			if( ( e = cudaEventRecord( traced[slot], bs ) ) != cudaSuccess ) break;
+			if( ( e = cudaStreamWaitEvent( ctx->copyStream, traced[slot], 0 ) ) != cudaSuccess ) break;
+			if( rgba && ( e = cudaMemcpyAsync( rgba + hOff * 4, rgba_d + dOff * 4, n * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( t && ( e = cudaMemcpyAsync( t + hOff, t_d + dOff, n * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( nMajor && ( e = cudaMemcpyAsync( nMajor + hOff, nm_d + dOff, n * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( vIndex && ( e = cudaMemcpyAsync( vIndex + hOff, vi_d + dOff, n * 4, cudaMemcpyDeviceToHost, ctx->copyStream ) ) != cudaSuccess ) break;
+			if( ( e = cudaEventRecord( copied[slot], ctx->copyStream ) ) != cudaSuccess ) break;
+		}
+		if( e == cudaSuccess ) e = cudaEventRecord( ctx->bandEv[16], ctx->copyStream );
+		if( e == cudaSuccess ) e = cudaStreamWaitEvent( s, ctx->bandEv[16], 0 );
+		if( e == cudaSuccess ) e = cudaEventSynchronize( ctx->bandEv[16] );
+		if( e != cudaSuccess && r == 0 ) r = cudaFail( e, "frame pipeline", __FILE__, __LINE__ );
+		if( r )
+		{
+			for( int i = 0; i < 2; i++ ) cudaStreamSynchronize( ctx->bandStream[i] );
+			cudaStreamSynchronize( ctx->copyStream );
+			cudaStreamSynchronize( s );
+		}
+	} while( 0 );
+	for( int i = 0; i < RING; i++ )
+	{
+		if( traced[i] ) cudaEventDestroy( traced[i] );
+		if( copied[i] ) cudaEventDestroy( copied[i] );
+	}
+	dfree( rgba_d, s ), dfree( t_d, s ), dfree( nm_d, s ), dfree( vi_d, s );
+	return r;
+}
 }

@@ -30,6 +30,7 @@ using namespace hako;
 #define PMJ_LENGTH 4096	  // pmjSampler.hpp:107-111
 #define PMJ_NSEQ 128
 #define PT_COUNTERS 64	  // [0] work, [1] rays traced, [2 + v] live paths at vertex v, [32 + v] ray work counter of wave v
+#define PT_LANES 4 // concurrent row bands of a wavefront step; each has its own PT_COUNTERS block and wave buffers
 #define PT_MAX_WAVES 28
 
 struct hako_pt
@@ -51,10 +52,16 @@ struct hako_pt
 	uint64_t pathCap = 0;
 	unsigned long long* counters = nullptr; // [0] work counter, [1] rays traced
 	uint32_t* hitQueue = nullptr;			// path indices whose primary ray hit (wavefront modes), capacity pathCap
-	// full wavefront mode: ping-pong vertex lists, ray directions, ray results; capacity waveCap live paths (3 rays each)
-	void* waveV[2] = { nullptr, nullptr };
-	float4* waveDir[2] = { nullptr, nullptr };
-	float4* waveRes = nullptr;
+	// full wavefront mode: ping-pong vertex lists, ray directions, ray results; capacity waveCap live paths (3 rays each).
+	// One set per LANE: the row bands of a step run on up to PT_LANES internal streams at once, because every trace wave ends
+	// with a tail in which a few long rays hold the kernel open (a ray is a serial chain of dependent node fetches) while most
+	// SMs idle; the waves of another band fill those tails (tools/pt_overlap_probe.py: 17.6 -> 15.8 ms per 1080p step).
+	void* waveV[PT_LANES][2] = {};
+	float4* waveDir[PT_LANES][2] = {};
+	float4* waveRes[PT_LANES] = {};
+	cudaStream_t laneStream[PT_LANES] = {};
+	cudaEvent_t laneEv[PT_LANES + 1] = {};
+	int lanes = 3; // HAKO_PT_LANES
 	uint64_t waveCap = 0;
 	int waveRefillMin = 24, waveBurst = 16; // traceWaveKernel knobs (HAKO_PT_REFILL_MIN / HAKO_PT_BURST); B200 sweep in profiles/r1f_pt_sweep.txt
 	int waveTraceCtas = 5;
@@ -966,16 +973,20 @@ int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out )
 	if( const char* e = getenv( "HAKO_PT_BURST" ) ) pt->waveBurst = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_TRACE_CTAS" ) ) pt->waveTraceCtas = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_BAND_PATHS" ) ) pt->waveBandPaths = strtoull( e, nullptr, 10 );
+	if( const char* e = getenv( "HAKO_PT_LANES" ) ) pt->lanes = atoi( e );
+	pt->lanes = std::max( 1, std::min( PT_LANES, pt->lanes ) );
 	std::vector<float> table( (size_t)2 * PMJ_LENGTH * PMJ_NSEQ );
 	HostPCG32 rng;
 	rng.setup( 0, 2525 ); // pmjSampler.hpp:116-117
 	for( int i = 0; i < PMJ_NSEQ; i++ ) generatePMJ02( PMJ_LENGTH, table.data() + (size_t)2 * PMJ_LENGTH * i, rng );
 	int r = dalloc( ctx, &pt->pmj, table.size(), s );
-	if( r == 0 ) r = dalloc( ctx, &pt->counters, PT_COUNTERS, s );
+	if( r == 0 ) r = dalloc( ctx, &pt->counters, PT_COUNTERS * PT_LANES, s );
 	if( r == 0 )
 	{
 		cudaError_t e = cudaMemcpyAsync( pt->pmj, table.data(), table.size() * sizeof( float ), cudaMemcpyHostToDevice, s );
-		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, PT_COUNTERS * sizeof( unsigned long long ), s );
+		if( e == cudaSuccess ) e = cudaMemsetAsync( pt->counters, 0, PT_COUNTERS * PT_LANES * sizeof( unsigned long long ), s );
+		for( int i = 0; i < PT_LANES && e == cudaSuccess; i++ ) e = cudaStreamCreateWithFlags( &pt->laneStream[i], cudaStreamNonBlocking );
+		for( int i = 0; i <= PT_LANES && e == cudaSuccess; i++ ) e = cudaEventCreateWithFlags( &pt->laneEv[i], cudaEventDisableTiming );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s ); // `table` dies with this scope
 		if( e != cudaSuccess ) r = cudaFail( e, "PMJ upload", __FILE__, __LINE__ );
 	}
@@ -999,8 +1010,15 @@ void hako_pt_destroy( hako_pt* pt )
 	dfree( pt->pmj, s );
 	dfree( pt->pathL, s );
 	dfree( pt->hitQueue, s );
-	for( int i = 0; i < 2; i++ ) dfree( pt->waveV[i], s ), dfree( pt->waveDir[i], s );
-	dfree( pt->waveRes, s );
+	for( int k = 0; k < PT_LANES; k++ )
+	{
+		if( pt->laneStream[k] ) cudaStreamSynchronize( pt->laneStream[k] );
+		for( int i = 0; i < 2; i++ ) dfree( pt->waveV[k][i], s ), dfree( pt->waveDir[k][i], s );
+		dfree( pt->waveRes[k], s );
+		if( pt->laneStream[k] ) cudaStreamDestroy( pt->laneStream[k] );
+	}
+	for( int k = 0; k <= PT_LANES; k++ )
+		if( pt->laneEv[k] ) cudaEventDestroy( pt->laneEv[k] );
 	dfree( pt->counters, s );
 	cudaStreamSynchronize( s );
 	delete pt;
@@ -1185,27 +1203,36 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 	if( pt->wavefront == 2 && waves <= PT_MAX_WAVES )
 	{
 		// full wavefront, in row bands of at most waveBandPaths paths so that the live-path buffers stay bounded even when
-		// every primary ray hits
-		const uint32_t rowsPerBand = (uint32_t)std::max<uint64_t>( 4, ( pt->waveBandPaths / ( (uint64_t)pt->w * PT_SPP ) ) & ~3ull );
+		// every primary ray hits; band b runs on lane b % lanes (own stream, counters and wave buffers), the lanes side by side
+		const int lanes = pt->lanes;
+		const uint32_t rowsTotal = (uint32_t)( y1 - y0 );
+		const uint32_t rowsCap = (uint32_t)std::max<uint64_t>( 4, ( pt->waveBandPaths / ( (uint64_t)pt->w * PT_SPP ) ) & ~3ull );
+		const uint32_t rowsPerBand = std::min( rowsCap, std::max( 4u, ( ( rowsTotal + lanes - 1 ) / lanes + 3u ) & ~3u ) );
 		const uint64_t bandCap = std::min<uint64_t>( nPaths, (uint64_t)rowsPerBand * pt->w * PT_SPP );
 		if( pt->waveCap < bandCap )
 		{
-			for( int i = 0; i < 2; i++ )
+			for( int k = 0; k < PT_LANES; k++ )
 			{
-				dfree( pt->waveV[i], s ), dfree( pt->waveDir[i], s );
-				pt->waveV[i] = nullptr, pt->waveDir[i] = nullptr;
+				for( int i = 0; i < 2; i++ )
+				{
+					dfree( pt->waveV[k][i], s ), dfree( pt->waveDir[k][i], s );
+					pt->waveV[k][i] = nullptr, pt->waveDir[k][i] = nullptr;
+				}
+				dfree( pt->waveRes[k], s );
+				pt->waveRes[k] = nullptr;
 			}
-			dfree( pt->waveRes, s );
-			pt->waveRes = nullptr;
 			pt->waveCap = 0;
-			for( int i = 0; i < 2; i++ )
+			for( int k = 0; k < lanes; k++ )
 			{
-				WaveVertex* v = nullptr;
-				HAKO_TRY( dalloc( ctx, &v, bandCap, s ) );
-				pt->waveV[i] = v;
-				HAKO_TRY( dalloc( ctx, &pt->waveDir[i], bandCap * 3, s ) );
+				for( int i = 0; i < 2; i++ )
+				{
+					WaveVertex* v = nullptr;
+					HAKO_TRY( dalloc( ctx, &v, bandCap, s ) );
+					pt->waveV[k][i] = v;
+					HAKO_TRY( dalloc( ctx, &pt->waveDir[k][i], bandCap * 3, s ) );
+				}
+				HAKO_TRY( dalloc( ctx, &pt->waveRes[k], bandCap * 3, s ) );
 			}
-			HAKO_TRY( dalloc( ctx, &pt->waveRes, bandCap * 3, s ) );
 			pt->waveCap = bandCap;
 		}
 		// occupancy target of the trace kernel: 5 CTAs/SM = 48 registers, 6 = 40, 8 = 32 (HAKO_PT_TRACE_CTAS)
@@ -1215,51 +1242,66 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 		const int occ = pt->waveTraceCtas >= 8 ? 8 : ( pt->waveTraceCtas >= 6 ? 6 : 5 );
 		const uint32_t traceGrid = (uint32_t)occ * ctx->smCount;
 		const uint32_t shadeGrid = 8u * ctx->smCount;
-		for( int b0 = y0; b0 < y1; b0 += (int)rowsPerBand )
+		// fork: the lanes start after everything queued on `s` (allocations, the previous step's accumulate)
+		HAKO_CUDA( cudaEventRecord( pt->laneEv[PT_LANES], s ) );
+		for( int k = 0; k < lanes; k++ ) HAKO_CUDA( cudaStreamWaitEvent( pt->laneStream[k], pt->laneEv[PT_LANES], 0 ) );
+		int band = 0;
+		for( int b0 = y0; b0 < y1; b0 += (int)rowsPerBand, band++ )
 		{
+			const int lane = band % lanes;
+			cudaStream_t ls = pt->laneStream[lane];
+			unsigned long long* counters = pt->counters + (size_t)lane * PT_COUNTERS;
 			const int b1 = std::min( y1, b0 + (int)rowsPerBand );
 			PtParams q = p;
 			q.y0 = b0;
 			q.pathL = pt->pathL + (size_t)( b0 - y0 ) * pt->w * PT_SPP;
+			q.hitQueue = pt->hitQueue + (size_t)( b0 - y0 ) * pt->w * PT_SPP;
+			q.counters = counters;
 			q.nPaths = (uint32_t)( (uint64_t)( b1 - b0 ) * pt->w * PT_SPP );
 			// live counts [2 .. 2 + waves] and the waves' ray counters [32 .. 32 + waves)
-			HAKO_CUDA( cudaMemsetAsync( pt->counters + 2, 0, ( PT_COUNTERS - 2 ) * sizeof( unsigned long long ), s ) );
+			HAKO_CUDA( cudaMemsetAsync( counters + 2, 0, ( PT_COUNTERS - 2 ) * sizeof( unsigned long long ), ls ) );
 			const uint32_t tiles = ( ( (uint32_t)pt->w + 3u ) / 4u ) * ( ( (uint32_t)( b1 - b0 ) + 3u ) / 4u );
-			HAKO_LAUNCH( ctx, primaryWaveKernel, tiles, PT_BLOCK, 0, s, q, b1 - b0 );
+			HAKO_LAUNCH( ctx, primaryWaveKernel, tiles, PT_BLOCK, 0, ls, q, b1 - b0 );
 			for( int v = 0; v <= waves; v++ )
 			{
 				// shade( v ): consumes the rays of vertex v-1; for v == waves every path ends (depth == maxDepth)
 				WaveParams wp;
-				wp.vin = (const WaveVertex*)pt->waveV[( v + 1 ) & 1];
-				wp.vout = (WaveVertex*)pt->waveV[v & 1];
-				wp.dirIn = pt->waveDir[( v + 1 ) & 1];
-				wp.dirOut = pt->waveDir[v & 1];
-				wp.resIn = pt->waveRes;
-				wp.nIn = pt->counters + 2 + v;
-				wp.nOut = pt->counters + 2 + v + 1;
+				wp.vin = (const WaveVertex*)pt->waveV[lane][( v + 1 ) & 1];
+				wp.vout = (WaveVertex*)pt->waveV[lane][v & 1];
+				wp.dirIn = pt->waveDir[lane][( v + 1 ) & 1];
+				wp.dirOut = pt->waveDir[lane][v & 1];
+				wp.resIn = pt->waveRes[lane];
+				wp.nIn = counters + 2 + v;
+				wp.nOut = counters + 2 + v + 1;
 				wp.v = v;
 				wp.rIn = v > 0 ? waveRaysPerVertex( envOn, nExtra, v - 1 ) : 0;
 				wp.rOut = waveRaysPerVertex( envOn, nExtra, v );
-				HAKO_LAUNCH( ctx, shadeWaveKernel, shadeGrid, 256, 0, s, q, wp );
+				HAKO_LAUNCH( ctx, shadeWaveKernel, shadeGrid, 256, 0, ls, q, wp );
 				if( v == waves ) break;
 				TraceWaveParams tp;
 				tp.vertices = wp.vout;
 				tp.dirs = wp.dirOut;
-				tp.results = pt->waveRes;
+				tp.results = pt->waveRes[lane];
 				tp.nVertices = wp.nOut;
-				tp.work = pt->counters + 32 + v;
-				tp.rays = pt->counters + 1;
+				tp.work = counters + 32 + v;
+				tp.rays = counters + 1;
 				tp.raysPerVertex = wp.rOut;
 				tp.shadowFirst = envOn ? 1 : 0;
 				tp.refillMin = std::max( 1, std::min( 32, pt->waveRefillMin ) );
 				tp.burst = std::max( 1, pt->waveBurst );
 				if( occ == 8 )
-					HAKO_LAUNCH( ctx, kTrace8, traceGrid, 256, 0, s, q.tree, tp );
+					HAKO_LAUNCH( ctx, kTrace8, traceGrid, 256, 0, ls, q.tree, tp );
 				else if( occ == 6 )
-					HAKO_LAUNCH( ctx, kTrace6, traceGrid, 256, 0, s, q.tree, tp );
+					HAKO_LAUNCH( ctx, kTrace6, traceGrid, 256, 0, ls, q.tree, tp );
 				else
-					HAKO_LAUNCH( ctx, kTrace5, traceGrid, 256, 0, s, q.tree, tp );
+					HAKO_LAUNCH( ctx, kTrace5, traceGrid, 256, 0, ls, q.tree, tp );
 			}
+		}
+		// join: the accumulate below (and whatever the caller queues next) waits for every lane
+		for( int k = 0; k < lanes; k++ )
+		{
+			HAKO_CUDA( cudaEventRecord( pt->laneEv[k], pt->laneStream[k] ) );
+			HAKO_CUDA( cudaStreamWaitEvent( s, pt->laneEv[k], 0 ) );
 		}
 	}
 	else
@@ -1350,11 +1392,16 @@ int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, in
 {
 	PT_ARG( pt && raysTraced, "hako_pt_ray_count: null argument" );
 	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
-	unsigned long long v = 0;
-	HAKO_CUDA( cudaMemcpyAsync( &v, pt->counters + 1, sizeof( v ), cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
-	if( reset ) HAKO_CUDA( cudaMemsetAsync( pt->counters + 1, 0, sizeof( v ), (cudaStream_t)stream ) );
+	// every lane counts in its own block (steps join their lanes into the caller's stream before they return)
+	unsigned long long v[PT_LANES] = {};
+	for( int k = 0; k < PT_LANES; k++ )
+	{
+		HAKO_CUDA( cudaMemcpyAsync( &v[k], pt->counters + k * PT_COUNTERS + 1, sizeof( v[k] ), cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+		if( reset ) HAKO_CUDA( cudaMemsetAsync( pt->counters + k * PT_COUNTERS + 1, 0, sizeof( v[k] ), (cudaStream_t)stream ) );
+	}
 	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
-	*raysTraced = v;
+	*raysTraced = 0;
+	for( int k = 0; k < PT_LANES; k++ ) *raysTraced += v[k];
 	return HAKO_OK;
 }
 

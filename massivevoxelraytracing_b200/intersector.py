@@ -205,6 +205,20 @@ class _OctreeBase:
                                            _ptr(out_rgba), _ptr(t), _ptr(nm), _ptr(vi)))
         return out_rgba, t, nm, vi
 
+    def render_views(self, cameras, width, height, showVertexColor=False, rgba=True, ids=True, stream=None, out=None):
+        """a run of whole frames in one call (the orbit loop of voxRTGPU.cpp:150-208, headless); frame i+1 is traced while
+        frame i is copied out.  `out` = (rgba, t, nMajor, vIndex) host arrays to fill (e.g. pinned), else fresh arrays."""
+        n = len(cameras)
+        cams = (Camera * max(n, 1))(*cameras)
+        if out is None:
+            out = (np.empty((n, height, width, 4), np.uint8) if rgba else None,
+                   np.empty((n, height, width), np.float32) if ids else None,
+                   np.empty((n, height, width), np.int32) if ids else None,
+                   np.empty((n, height, width), np.uint32) if ids else None)
+        check(self.lib.hako_render_primary_views(self.h, _stream(stream), cams, n, width, height, int(bool(showVertexColor)),
+                                                 _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _ptr(out[3])))
+        return out
+
     def render_device(self, camera, width, height, y0=0, y1=None, showVertexColor=False, rgba=None, t=None, nMajor=None, vIndex=None, stream=None):
         y1 = height if y1 is None else y1
         check(self.lib.hako_render_primary_device(self.h, _stream(stream), C.byref(camera), width, height, y0, y1, int(bool(showVertexColor)),

@@ -846,6 +846,31 @@ void orc_render_primary( const OrcOctree* o, const OrcCamera* cam, int w, int h,
 	}
 }
 
+// diagnostic: loop visits of every primary ray (how long the longest rays of a frame are; tools/ray_length_probe.py)
+void orc_render_primary_visits( const OrcOctree* o, const OrcCamera* cam, int w, int h, int nThreads, uint32_t* visits )
+{
+	if( nThreads < 1 ) nThreads = 1;
+	uint32_t root = o->nodes.empty() ? 0 : (uint32_t)o->nodes.size() - 1;
+	auto work = [&]( int tid ) {
+		for( int j = tid; j < h; j += nThreads )
+			for( int i = 0; i < w; i++ )
+			{
+				float ro[3], rd[3];
+				orc_camera_shoot( cam, i, j, 0.5f, 0.5f, w, h, ro, rd );
+				float tt = FLT_MAX;
+				int nm = -1;
+				uint32_t vi = 0xFFFFFFFFu;
+				TravStats st;
+				if( !o->nodes.empty() )
+					traverse<true>( o->nodes.data(), root, { ro[0], ro[1], ro[2] }, { rd[0], rd[1], rd[2] }, o->lower, o->upper, &tt, &nm, &vi, false, &st );
+				visits[(size_t)j * w + i] = (uint32_t)st.visits;
+			}
+	};
+	std::vector<std::thread> th;
+	for( int k = 0; k < nThreads; k++ ) th.emplace_back( work, k );
+	for( auto& x : th ) x.join();
+}
+
 uint64_t orc_fnv1a64( const void* p, uint64_t bytes )
 {
 	const uint8_t* b = (const uint8_t*)p;

@@ -89,6 +89,9 @@ void orc_camera_shoot_thin_lens( const OrcCamera* cam, int x, int y, float ox, f
 void orc_render_primary( const OrcOctree* o, const OrcCamera* cam, int w, int h, int y0, int y1, int nThreads,
 						 float* t, int* nMajor, uint32_t* vIndex, uint64_t* stats );
 
+/* diagnostic (tools/ray_length_probe.py): traversal loop visits of every pixel-centre primary ray of a w x h frame */
+void orc_render_primary_visits( const OrcOctree* o, const OrcCamera* cam, int w, int h, int nThreads, uint32_t* visits );
+
 /* FNV-1a-64 over a byte buffer (used for the golden checksums in SURVEY.md section 8c). */
 uint64_t orc_fnv1a64( const void* p, uint64_t bytes );
 

@@ -74,6 +74,29 @@ def test_render_primary_matches_oracle(hk, ctx, oracle, bunny, golden, grid, W, 
     g.cleanUp()
 
 
+def test_render_views_equals_per_frame_calls(hk, ctx, oracle, bunny):
+    """hako_render_primary_views (a ring of 4 device frames, frame i+1 traced while frame i is copied out) returns what one
+    hako_render_primary call per camera returns -- more views than ring slots, odd image size, both output kinds"""
+    tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 64)
+    g, attrs = _import(hk, ctx, tree, mc, me, dps)
+    W, H = 203, 117
+    cams = [hk.camera_lookat((4 * np.cos(a), 1.0 + 0.5 * k, 4 * np.sin(a)), (0, 0, 0), width=W, height=H) for k, a in enumerate(np.linspace(0, 5, 11))]
+    rgba, t, nm, vi = g.render_views(cams, W, H, showVertexColor=True)
+    assert rgba.shape == (11, H, W, 4) and t.shape == (11, H, W)
+    for k, cam in enumerate(cams):
+        r1, t1, nm1, vi1 = g.render(cam, W, H, showVertexColor=True)
+        np.testing.assert_array_equal(rgba[k], r1)
+        np.testing.assert_array_equal(t[k].view(np.uint32), t1.view(np.uint32))
+        np.testing.assert_array_equal(nm[k], nm1)
+        np.testing.assert_array_equal(vi[k], vi1)
+    assert len({int((t[k] != FLT_MAX).sum()) for k in range(11)}) > 3     # the views differ
+    # one output kind only, fewer views than ring slots, and the empty run
+    only = g.render_views(cams[:2], W, H, rgba=True, ids=False)
+    assert only[1] is None and np.array_equal(only[0], g.render_views(cams[:2], W, H, showVertexColor=False)[0])
+    assert g.render_views([], W, H)[0].shape == (0, H, W, 4)
+    g.cleanUp()
+
+
 def test_export_roundtrip(hk, ctx, oracle, bunny):
     tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 64)
     g, attrs = _import(hk, ctx, tree, mc, me, dps)
