@@ -423,8 +423,18 @@ def run_ours(args):
                 "algorithmic_bytes_per_ray": bytes_per_ray, "descents_per_ray": dbar, "rays_per_launch": nrays_view, "avg_launch_ms": launch_ms,
                 "ncu": {k: load_profile_value(k, None) for k in ("render_issue_active_pct", "render_lanes_active_per_instruction", "render_l2_throughput_pct_of_peak",
                                                                   "render_l1_hit_pct", "render_l2_hit_pct", "render_warp_instructions_per_launch", "source")},
-                "note": "pointer-chasing traversal: latency/issue-bound with the %.0f MB octree L2-resident; see profiles/ for L2 throughput, issue utilisation and warp efficiency"
-                        % (info.numberOfNodes * 64 / 1e6)}
+                "note": "pointer-chasing traversal with the %.0f MB octree L2-resident: the binding limit is the warp-instruction issue rate, not HBM (issue_bound below); a launch "
+                        "timed ALONE is bound by its longest rays (a ray is a serial chain of dependent node fetches; ~29 %% of such a launch the average SM idles), which is why "
+                        "the frames of a step are overlapped on several streams" % (info.numberOfNodes * 64 / 1e6)}
+    winst = load_profile_value("render_warp_instructions_per_launch", None)
+    if winst:
+        # issue roofline: every SM has 4 warp schedulers issuing at most 1 warp instruction per clock
+        sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+        clocks = sampler.summary()
+        mhz = float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)
+        floor_ms = float(winst) / (sm_count * 4 * mhz * 1e6) * 1e3
+        roofline["issue_bound"] = {"warp_instructions_per_launch": winst, "schedulers": sm_count * 4, "sm_mhz": mhz, "floor_ms_per_launch": floor_ms,
+                                   "frac": floor_ms / launch_ms, "source": "instruction count from the ncu capture named in roofline.ncu.source"}
     cfg = base_config(world)
     cfg["l2"] = "outputs of a step (%.0f MB) exceed the 126 MB L2; the octree (%.0f MB) is L2-resident by design; no explicit flush" % (
         VIEWS * nrays_view * 12 / 1e6, info.numberOfNodes * 65 / 1e6)
