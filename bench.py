@@ -53,6 +53,11 @@ def view_eye(k, n_views_total):
     return (float(4 * c + 4 * s), 4.0, float(-4 * s + 4 * c))
 
 
+def rank_views(rank, world):
+    """the views of a step are dealt round-robin: every rank's 16 views span the whole orbit, so the ranks do the same work"""
+    return [rank + i * world for i in range(VIEWS)]
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)"""
 
@@ -119,10 +124,10 @@ def cpu_cast(o, tree, views_total, view_ids, threads, bands, stats=None):
     st = np.zeros(4, np.uint64)
     rays = 0
     secs = 0.0
-    for k in view_ids:
+    for i, k in enumerate(view_ids):
         cam = o.camera_lookat(view_eye(k, views_total), (0, 0, 0), (0, 1, 0), None, W, H)
         if bands:
-            j = k % VIEWS
+            j = i % VIEWS
             y0, y1 = (H * j) // VIEWS, (H * (j + 1)) // VIEWS
         else:
             y0, y1 = 0, H
@@ -158,7 +163,7 @@ def base_config(n_gpus):
                         "missing from the reference checkout) voxelized at %d^3, %dx%d pixel-centre primary rays, %d orbit views per step per GPU"
                         % (MESH_LEVELS, 5110 * 4 ** MESH_LEVELS, GRID, W, H, VIEWS),
             "grid": GRID, "image": [W, H], "views_per_step_per_gpu": VIEWS,
-            "parallelism": "octree built on rank 0 + NCCL broadcast; views sharded over %d GPU(s), no data-path collective" % n_gpus,
+            "parallelism": "octree built on rank 0 + NCCL broadcast; views dealt round-robin over %d GPU(s) (every rank spans the whole orbit), no data-path collective" % n_gpus,
             "streams": "the frames of a step alternate between CUDA streams (4 per GPU unless HAKO_BENCH_STREAMS says otherwise; tail of frame i overlaps the head of frame i+1); "
                        "timed with events on the stream that forks and joins them"}
 
@@ -175,11 +180,11 @@ def run_reference(args):
     views_total = VIEWS * args.gpus
     # one step = a bounded sample of the workload's step: row band k of each of the VIEWS views (= one frame's worth of rays)
     for _ in range(args.warmup):
-        cpu_cast(o, tree, views_total, range(VIEWS), threads, True)
+        cpu_cast(o, tree, views_total, rank_views(0, views_total // VIEWS), threads, True)
     rays = 0
     secs = 0.0
     for _ in range(args.steps):
-        r, s = cpu_cast(o, tree, views_total, range(VIEWS), threads, True)
+        r, s = cpu_cast(o, tree, views_total, rank_views(0, views_total // VIEWS), threads, True)
         rays += r
         secs += s
     value = rays / secs / 1e6
@@ -242,7 +247,7 @@ def run_ours(args):
             build["nccl_broadcast_ms"] = (time.perf_counter() - t0) * 1e3
     info = octree.info()
 
-    my_views = list(range(rank * VIEWS, (rank + 1) * VIEWS))
+    my_views = rank_views(rank, world)
     cams = [hk.camera_lookat(view_eye(k, views_total), (0, 0, 0), width=W, height=H) for k in my_views]
     # one output set per view: 16 x 24.9 MB = 398 MB per step, larger than the 126 MB L2
     t_d = torch.empty((VIEWS, nrays_view), dtype=torch.float32, device=dev)
@@ -387,14 +392,14 @@ def run_ours(args):
         rays_c, secs_c = 0, 0.0
         reps = 0
         while secs_c < 3.0 and reps < 8:
-            r, s = cpu_cast(o, tree, views_total, range(VIEWS), threads, True)
+            r, s = cpu_cast(o, tree, views_total, rank_views(0, views_total // VIEWS), threads, True)
             rays_c += r
             secs_c += s
             reps += 1
-        r1, s1 = cpu_cast(o, tree, views_total, range(VIEWS), 1, True)
+        r1, s1 = cpu_cast(o, tree, views_total, rank_views(0, views_total // VIEWS), 1, True)
         ptree = tree if o is port else port.build_octree(mk, origin, dps, GRID)
         stats = np.zeros(4, np.uint64)
-        rs, _ = cpu_cast(port, ptree, views_total, range(VIEWS), threads, True, stats)
+        rs, _ = cpu_cast(port, ptree, views_total, rank_views(0, views_total // VIEWS), threads, True, stats)
         dbar = float(stats[1]) / rs
         cpu = {"value": rays_c / secs_c / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference" if ref is not None else "port",
                "sample": "row band k of view k for the %d views of a step (%d rays), repeated %d times; %d host threads over image rows" % (VIEWS, rs, reps, threads),
