@@ -98,8 +98,9 @@ typedef struct hako_build_stats
 	uint64_t uniqueVoxels; /* U */
 	uint32_t numberOfNodes;
 	uint32_t sortPasses;
-	/* device times between stream events.  hako_octree_build uploads the positions first (ms_h2d) and the colour / emission arrays
-	 * behind the voxelizer's counting pass, so the exposed remainder of that upload is inside ms_voxelize. */
+	/* device times between stream events.  hako_octree_build uploads the positions first (ms_h2d); the colour / emission arrays
+	 * follow by triangle range behind the voxelizer's counting pass and the emission of earlier ranges, so the exposed
+	 * remainder of that upload is inside ms_voxelize. */
 	float ms_h2d, ms_voxelize, ms_sort, ms_unique, ms_octree, ms_total;
 	uint32_t hostSyncs;
 	uint32_t kernelLaunches;

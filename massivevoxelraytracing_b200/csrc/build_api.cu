@@ -6,6 +6,8 @@
 // -> embedMasks, with ~12 oroMalloc/oroFree.  Here: columns -> [read] -> count -> [read D] -> emit -> histogram + P onesweep
 // passes -> unique -> [read U] -> level histogram -> [read] -> 4 kernels per level -> [read node count] -> D2D copy.
 // Allocations come from the context's stream-ordered pool.
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 
 #include "internal.cuh"
@@ -52,7 +54,7 @@ static void initOctree( hako_octree* o, hako_ctx* ctx, const float origin[3], fl
 
 static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float* pos_d, const float* col_d, const float* emi_d, uint32_t nTriangles,
 									 const float origin[3], float dps, int gridRes, hako_octree** out,
-									 const std::function<int()>& beforeAttributesAreRead = std::function<int()>() )
+									 const std::function<int( int )>& beforeAttributesAreRead = std::function<int( int )>(), int emitSlices = 1 )
 {
 	hako_build_stats& st = ctx->stats;
 	const uint64_t launches0 = ctx->launches.load();
@@ -72,7 +74,7 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 		CK( cudaEventRecord( ctx->ev[1], s ) );
 		uint64_t D = 0;
 		if( ( r = voxelizeDevice( ctx, s, pos_d, col_d, emi_d, nTriangles, o->lower, dps, gridRes, 1 /* sixSeparating: voxKernel.cu:68,109 */, &keys, &values, &D,
-								   beforeAttributesAreRead ) ) )
+								   beforeAttributesAreRead, emitSlices ) ) )
 			break;
 		st.dumpedVoxels = D;
 		CK( cudaEventRecord( ctx->ev[2], s ) );
@@ -179,10 +181,18 @@ int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, cons
 	const uint64_t nf = (uint64_t)nTriangles * 9;
 	HAKO_TRY( dalloc( ctx, &d, nf * 3, s ) );
 	int r = 0;
-	// The positions go up first; the colour / emission arrays follow on a helper thread while the counting pass of the voxelizer
-	// (which reads positions only) already runs: their copies are joined right before the first kernel that reads them.
+	// The positions go up first; the colour / emission arrays follow on a helper thread, in SLICES triangle ranges (colour and
+	// emission of a range together), while the counting pass of the voxelizer (which reads positions only) and then the emit
+	// pass of the earlier ranges already run: slice k of the emit pass is ordered behind the copies of ranges 0..k only.
+	static const int slicesEnv = getenv( "HAKO_BUILD_SLICES" ) ? atoi( getenv( "HAKO_BUILD_SLICES" ) ) : 6;
+	const int SLICES = std::max( 1, std::min( { slicesEnv, 16, (int)std::max<uint32_t>( 1u, nTriangles / 65536u ) } ) ); // = voxelizeDevice's clamp
 	std::thread helper;
 	int helperResult = 0;
+	std::mutex mtx;
+	std::condition_variable cv;
+	int slicesUp = 0; // ranges whose copies are enqueued and whose event is recorded
+	bool helperDone = false;
+	cudaEvent_t sliceEv[16] = {};
 	if( nf && nf * 4 < ( 4u << 20 ) )
 	{
 		// small meshes: three plain copies, no staging threads
@@ -195,23 +205,65 @@ int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, cons
 	{
 		const H2DSegment segPos = { d, pos, nf * 4 };
 		r = uploadSegments( ctx, s, &segPos, 1 );
+		for( int k = 0; k < SLICES && r == 0; k++ )
+		{
+			cudaError_t e = cudaEventCreateWithFlags( &sliceEv[k], cudaEventDisableTiming );
+			if( e != cudaSuccess ) r = cudaFail( e, "cudaEventCreate", __FILE__, __LINE__ );
+		}
 		if( r == 0 )
 			helper = std::thread( [&]() {
-				const H2DSegment segs[2] = { { d + nf, col, nf * 4 }, { d + 2 * nf, emi, nf * 4 } };
-				helperResult = cudaSetDevice( ctx->device ) == cudaSuccess ? uploadBegin( ctx, s, segs, 2, false ) : HAKO_E_CUDA;
+				// ONE staged upload of all ranges (range-major: colour k, emission k, colour k+1, ...) keeps every worker busy; a
+				// range is published when the contiguous prefix of completed ranges reaches it
+				std::vector<H2DSegment> segs;
+				for( int k = 0; k < SLICES; k++ )
+				{
+					const uint64_t f0 = (uint64_t)nTriangles * k / SLICES * 9, f1 = (uint64_t)nTriangles * ( k + 1 ) / SLICES * 9;
+					segs.push_back( { d + nf + f0, col + f0, ( f1 - f0 ) * 4 } );
+					segs.push_back( { d + 2 * nf + f0, emi + f0, ( f1 - f0 ) * 4 } );
+				}
+				bool done[16] = {};
+				int markResult = 0;
+				auto onRange = [&]( int g ) {
+					std::lock_guard<std::mutex> lk( mtx );
+					done[g] = true;
+					while( slicesUp < SLICES && done[slicesUp] && markResult == 0 )
+					{
+						cudaSetDevice( ctx->device ); // worker threads of the stager have set it; the direct-copy path runs here
+						markResult = uploadMark( ctx, sliceEv[slicesUp] );
+						if( markResult == 0 ) slicesUp++;
+					}
+					cv.notify_all();
+				};
+				int hr = cudaSetDevice( ctx->device ) == cudaSuccess ? 0 : HAKO_E_CUDA;
+				if( hr == 0 ) hr = uploadBegin( ctx, s, segs.data(), (int)segs.size(), false, 2, onRange );
+				{
+					std::lock_guard<std::mutex> lk( mtx );
+					helperResult = hr ? hr : markResult;
+					helperDone = true;
+				}
+				cv.notify_all();
 			} );
 	}
-	auto join = [&]() -> int {
-		if( helper.joinable() ) helper.join();
-		if( helperResult )
+	// beforeEmit( k ): ranges 0..k are needed; -1: everything
+	auto join = [&]( int k ) -> int {
+		if( !helper.joinable() && !helperDone ) return 0; // small mesh: plain copies on `s`
+		const int need = k < 0 ? SLICES : std::min( SLICES, k + 1 );
 		{
-			setError( "hako_octree_build: staged upload of the colour / emission arrays failed" );
-			return helperResult;
+			std::unique_lock<std::mutex> lk( mtx );
+			cv.wait( lk, [&]() { return slicesUp >= need || helperDone; } );
+			if( helperResult )
+			{
+				setError( "hako_octree_build: staged upload of the colour / emission arrays failed" );
+				return helperResult;
+			}
 		}
-		return uploadFinish( ctx, s );
+		HAKO_CUDA( cudaStreamWaitEvent( s, sliceEv[need - 1], 0 ) );
+		return 0;
 	};
-	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out, join );
+	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out, join, SLICES );
 	if( helper.joinable() ) helper.join();
+	for( int k = 0; k < 16; k++ )
+		if( sliceEv[k] ) cudaEventDestroy( sliceEv[k] );
 	dfree( d, s );
 	return r;
 }

@@ -12,6 +12,7 @@
 #include <thread>
 #include <vector>
 
+#include <functional>
 #include "internal.cuh"
 
 namespace hako
@@ -25,6 +26,8 @@ struct Stager
 	cudaStream_t stream[MAX_WORKERS] = {};
 	cudaEvent_t ev[MAX_WORKERS][NBUF] = {};
 	cudaEvent_t start = nullptr;
+	cudaStream_t joinStream = nullptr; // uploadMark: gathers the worker streams behind one event
+	cudaEvent_t markEv[MAX_WORKERS] = {};
 };
 
 static int makeStager( hako_ctx* ctx )
@@ -39,9 +42,11 @@ static int makeStager( hako_ctx* ctx )
 	st->workers = std::max( 1, std::min( w, (int)Stager::MAX_WORKERS ) );
 	ctx->stager = st;
 	HAKO_CUDA( cudaEventCreateWithFlags( &st->start, cudaEventDisableTiming ) );
+	HAKO_CUDA( cudaStreamCreateWithFlags( &st->joinStream, cudaStreamNonBlocking ) );
 	for( int t = 0; t < st->workers; t++ )
 	{
 		HAKO_CUDA( cudaStreamCreateWithFlags( &st->stream[t], cudaStreamNonBlocking ) );
+		HAKO_CUDA( cudaEventCreateWithFlags( &st->markEv[t], cudaEventDisableTiming ) );
 		for( int b = 0; b < Stager::NBUF; b++ )
 		{
 			HAKO_CUDA( cudaMallocHost( &st->buf[t][b], Stager::CHUNK ) );
@@ -63,8 +68,10 @@ void destroyStager( hako_ctx* ctx )
 			if( st->ev[t][b] ) cudaEventDestroy( st->ev[t][b] );
 		}
 		if( st->stream[t] ) cudaStreamDestroy( st->stream[t] );
+		if( st->markEv[t] ) cudaEventDestroy( st->markEv[t] );
 	}
 	if( st->start ) cudaEventDestroy( st->start );
+	if( st->joinStream ) cudaStreamDestroy( st->joinStream );
 	delete st;
 	ctx->stager = nullptr;
 }
@@ -83,13 +90,16 @@ static bool isPinned( const void* p )
 // Puts the copies in flight on the stager's own streams (ordered behind everything enqueued on `s` so far) and returns when the
 // last chunk has been handed to the DMA engine.  `s` does NOT wait for them until uploadFinish( ctx, s ) is called, so a caller
 // may run this on a helper thread and keep launching kernels that do not need the data on `s`.
-int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, bool orderBehindStream )
+int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, bool orderBehindStream, int groupSegs, const std::function<void( int )>& onGroup )
 {
+	// groups: every `groupSegs` consecutive segments form a group; onGroup( g ) is called (from whichever worker thread gets
+	// there) as soon as the last chunk of group g has been handed to the DMA engine -- groups may complete out of order
 	struct Job
 	{
 		char* dst;
 		const char* src;
 		size_t bytes;
+		int group;
 	};
 	HAKO_TRY( makeStager( ctx ) );
 	Stager* st = ctx->stager;
@@ -101,8 +111,12 @@ int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, b
 		for( int t = 0; t < st->workers; t++ ) HAKO_CUDA( cudaStreamWaitEvent( st->stream[t], st->start, 0 ) );
 	}
 	std::vector<Job> jobs;
+	const int nGroups = groupSegs > 0 ? ( n + groupSegs - 1 ) / groupSegs : 0;
+	std::vector<std::atomic<int>> groupLeft( nGroups );
+	for( auto& g : groupLeft ) g.store( 0 );
 	for( int i = 0; i < n; i++ )
 	{
+		const int group = groupSegs > 0 ? i / groupSegs : 0;
 		if( segs[i].bytes == 0 ) continue;
 		if( segs[i].bytes < ( 1u << 20 ) || isPinned( segs[i].src ) )
 		{
@@ -111,8 +125,15 @@ int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, b
 			continue;
 		}
 		for( size_t off = 0; off < segs[i].bytes; off += Stager::CHUNK )
-			jobs.push_back( { (char*)segs[i].dst + off, (const char*)segs[i].src + off, std::min( Stager::CHUNK, segs[i].bytes - off ) } );
+		{
+			jobs.push_back( { (char*)segs[i].dst + off, (const char*)segs[i].src + off, std::min( Stager::CHUNK, segs[i].bytes - off ), group } );
+			if( nGroups ) groupLeft[group].fetch_add( 1 );
+		}
 	}
+	// groups without staged chunks (empty, small or pinned segments) are complete once their direct copies are enqueued: now
+	if( onGroup )
+		for( int g = 0; g < nGroups; g++ )
+			if( groupLeft[g].load() == 0 ) onGroup( g );
 	const int W = std::max( 1, std::min<int>( st->workers, (int)jobs.size() ) );
 	std::atomic<int> err{ 0 };
 	const int device = ctx->device;
@@ -138,6 +159,7 @@ int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, b
 				err.store( (int)e );
 				return;
 			}
+			if( nGroups && groupLeft[jobs[j].group].fetch_sub( 1 ) == 1 && onGroup ) onGroup( jobs[j].group );
 		}
 	};
 	std::vector<std::thread> threads;
@@ -159,9 +181,24 @@ int uploadFinish( hako_ctx* ctx, cudaStream_t s )
 		for( int b = 0; b < Stager::NBUF; b++ ) HAKO_CUDA( cudaStreamWaitEvent( s, st->ev[t][b], 0 ) );
 	return 0;
 }
+// records `ev` behind every copy begun so far (a partial uploadFinish that another thread can wait on later)
+int uploadMark( hako_ctx* ctx, cudaEvent_t ev )
+{
+	Stager* st = ctx->stager;
+	if( !st ) return 0;
+	// a point in every worker stream behind whatever has been enqueued on it so far (callers order themselves after the
+	// enqueues they care about); safe while the workers keep enqueueing later chunks
+	for( int t = 0; t < st->workers; t++ )
+	{
+		HAKO_CUDA( cudaEventRecord( st->markEv[t], st->stream[t] ) );
+		HAKO_CUDA( cudaStreamWaitEvent( st->joinStream, st->markEv[t], 0 ) );
+	}
+	HAKO_CUDA( cudaEventRecord( ev, st->joinStream ) );
+	return 0;
+}
 int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n )
 {
-	HAKO_TRY( uploadBegin( ctx, s, segs, n, true ) );
+	HAKO_TRY( uploadBegin( ctx, s, segs, n, true, 0, std::function<void( int )>() ) );
 	return uploadFinish( ctx, s );
 }
 } // namespace hako

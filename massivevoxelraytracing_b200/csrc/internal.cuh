@@ -112,15 +112,17 @@ struct H2DSegment
 	size_t bytes;
 };
 int uploadSegments( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n );
-int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, bool orderBehindStream ); // copies in flight; s does not wait yet
+int uploadBegin( hako_ctx* ctx, cudaStream_t s, const H2DSegment* segs, int n, bool orderBehindStream, int groupSegs = 0,
+				 const std::function<void( int )>& onGroup = std::function<void( int )>() ); // copies in flight; s does not wait yet
 int uploadFinish( hako_ctx* ctx, cudaStream_t s );								  // s waits for every copy begun so far
+int uploadMark( hako_ctx* ctx, cudaEvent_t ev );									  // ev is recorded behind every copy begun so far
 void destroyStager( hako_ctx* ctx );
 
 // voxelize.cu
 // beforeEmit (may be empty): called once, after the counting pass, before the first kernel that reads col / emi is launched
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
 					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D,
-					const std::function<int()>& beforeEmit = std::function<int()>() );
+					const std::function<int( int )>& beforeEmit = std::function<int( int )>(), int emitSlices = 1 );
 // sort.cu
 int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* values, uint64_t* keysTmp, uint64_t* valuesTmp,
 					 uint64_t n, int beginBit, int endBit, int* resultInTmp );

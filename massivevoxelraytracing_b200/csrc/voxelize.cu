@@ -214,14 +214,14 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 															uint32_t nTriangles, const uint32_t* __restrict__ colOffset, uint32_t nColumns,
 															V3 origin, float dps, int gridRes, int sixSeparating,
 															uint32_t* __restrict__ colCount, const uint32_t* __restrict__ voxOffset, uint32_t totalVoxels,
-															uint64_t* __restrict__ keys, uint64_t* __restrict__ values )
+															uint64_t* __restrict__ keys, uint64_t* __restrict__ values, uint32_t blockBase )
 {
 	// column -> triangle: colOffset is the exclusive scan of columns per triangle; the owner of column c is the last
 	// triangle whose offset is <= c.  A 128-column block spans at most 128 owners, so their offsets are staged once
 	// in shared memory (zero-column triangles in between are handled by the global fallback search).
 	__shared__ uint32_t s_off[129];
 	__shared__ uint32_t s_triFirst;
-	const uint32_t c0 = blockIdx.x * 128u;
+	const uint32_t c0 = ( blockIdx.x + blockBase ) * 128u; // blockBase: the emit pass may be launched in slices (voxelizeDevice)
 	if( threadIdx.x == 0 )
 	{
 		uint32_t lo = 0, hi = nTriangles; // last tri with colOffset[tri] <= c0
@@ -461,13 +461,13 @@ __global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __rest
 
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
 					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D,
-					const std::function<int()>& beforeEmit )
+					const std::function<int( int )>& beforeEmit, int emitSlices )
 {
 	bool emitHookRun = false;
 	*D = 0;
 	if( keysOut ) *keysOut = nullptr;
 	if( valuesOut ) *valuesOut = nullptr;
-	if( nTriangles == 0 ) return beforeEmit ? beforeEmit() : 0;
+	if( nTriangles == 0 ) return beforeEmit ? beforeEmit( -1 ) : 0;
 	uint32_t* colOffset = nullptr;
 	uint32_t* colCount = nullptr;
 	uint64_t* totals = nullptr; // [0] columns, [1] voxels
@@ -478,7 +478,13 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		if( ( r = dalloc( ctx, &totals, 2, s ) ) ) break;
 		HAKO_LAUNCH( ctx, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset );
 		if( ( r = scanU32( ctx, s, colOffset, colOffset, nTriangles, totals ) ) ) break;
+		// Emit slices: slice k covers the triangles [ T_k, T_k+1 ), T_k = nTriangles * k / emitSlices, i.e. the columns
+		// [ colOffset[T_k], colOffset[T_k+1] ); the caller's hook beforeEmit( k ) returns once the attributes of those triangles
+		// are on their way (ordered into `s`), so that an upload of the attribute arrays overlaps the emission of earlier slices.
+		emitSlices = std::max( 1, std::min( { emitSlices, 16, (int)std::max<uint32_t>( 1u, nTriangles / 65536u ) } ) );
 		cudaError_t e = cudaMemcpyAsync( ctx->pinned, totals, 8, cudaMemcpyDeviceToHost, s );
+		for( int k = 1; k < emitSlices && e == cudaSuccess; k++ )
+			e = cudaMemcpyAsync( (uint32_t*)( ctx->pinned + 1 ) + k, colOffset + (uint64_t)nTriangles * k / emitSlices, 4, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
 		ctx->stats.hostSyncs++;
 		if( e != cudaSuccess )
@@ -487,6 +493,8 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 			break;
 		}
 		const uint64_t nColumns = ctx->pinned[0];
+		uint32_t sliceColumn[17];
+		for( int k = 1; k < emitSlices; k++ ) sliceColumn[k] = ( (const uint32_t*)( ctx->pinned + 1 ) )[k];
 		if( nColumns >= 0xFFFFFFFFull )
 		{
 			setError( "voxelize: %llu (triangle, x) columns exceed the 32-bit work index", (unsigned long long)nColumns );
@@ -498,7 +506,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		auto kCount = columnVoxelsKernel<false>;
 		auto kEmit = columnVoxelsKernel<true>;
 		HAKO_LAUNCH( ctx, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
-					 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, 0u, (uint64_t*)nullptr, (uint64_t*)nullptr );
+					 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, 0u, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
 		if( ( r = scanU32( ctx, s, colCount, colCount, nColumns, totals + 1 ) ) ) break;
 		e = cudaMemcpyAsync( ctx->pinned, totals + 1, 8, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
@@ -521,13 +529,24 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		if( ( r = dalloc( ctx, keysOut, total, s ) ) ) break;
 		if( ( r = dalloc( ctx, valuesOut, total, s ) ) ) break;
 		emitHookRun = true;
-		if( beforeEmit && ( r = beforeEmit() ) ) break;
-		HAKO_LAUNCH( ctx, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
-					 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, (uint32_t)total, *keysOut, *valuesOut );
+		// a block belongs to the last slice any of its columns belongs to: slice k launches the blocks that lie entirely below
+		// the first column of slice k+1 and were not launched before
+		const uint32_t nBlocks = (uint32_t)divUp( nColumns, 128 );
+		uint32_t blockBase = 0;
+		for( int k = 0; k < emitSlices && r == 0; k++ )
+		{
+			const uint32_t blockEnd = k + 1 < emitSlices ? std::min( nBlocks, sliceColumn[k + 1] / 128u ) : nBlocks;
+			if( beforeEmit && ( r = beforeEmit( k + 1 < emitSlices ? k : -1 ) ) ) break; // -1: everything (the last slice)
+			if( blockEnd > blockBase )
+				HAKO_LAUNCH( ctx, kEmit, blockEnd - blockBase, 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
+							 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, (uint32_t)total, *keysOut, *valuesOut, blockBase );
+			blockBase = std::max( blockBase, blockEnd );
+		}
+		if( r ) break;
 	} while( 0 );
 	if( beforeEmit && !emitHookRun )
 	{
-		const int rh = beforeEmit(); // the caller's upload must be joined on every path
+		const int rh = beforeEmit( -1 ); // the caller's upload must be joined on every path
 		if( r == 0 ) r = rh;
 	}
 	dfree( colOffset, s ), dfree( colCount, s ), dfree( totals, s );
