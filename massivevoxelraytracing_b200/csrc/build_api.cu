@@ -184,7 +184,7 @@ int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, cons
 	// The positions go up first; the colour / emission arrays follow on a helper thread, in SLICES triangle ranges (colour and
 	// emission of a range together), while the counting pass of the voxelizer (which reads positions only) and then the emit
 	// pass of the earlier ranges already run: slice k of the emit pass is ordered behind the copies of ranges 0..k only.
-	static const int slicesEnv = getenv( "HAKO_BUILD_SLICES" ) ? atoi( getenv( "HAKO_BUILD_SLICES" ) ) : 6;
+	const int slicesEnv = getenv( "HAKO_BUILD_SLICES" ) ? atoi( getenv( "HAKO_BUILD_SLICES" ) ) : 6;
 	const int SLICES = std::max( 1, std::min( { slicesEnv, 16, (int)std::max<uint32_t>( 1u, nTriangles / 65536u ) } ) ); // = voxelizeDevice's clamp
 	std::thread helper;
 	int helperResult = 0;

@@ -246,6 +246,32 @@ def test_build_large_grid_subset_matches_golden(hk, ctx, oracle, bunny, golden, 
     g.cleanUp()
 
 
+def test_build_is_independent_of_the_upload_slicing(hk, ctx, monkeypatch):
+    """hako_octree_build sends colours / emissions up in triangle ranges and launches the emit pass per range behind its own
+    copies (HAKO_BUILD_SLICES): nodes, keys and attributes are the same bytes for 1, 2, 3 and the clamped maximum of ranges,
+    and equal to the build from device-resident vertex data (no staging at all)"""
+    import torch
+    from scenes import dragon_standin
+    tris, col, emi = dragon_standin(3, 0.15)          # 327 040 triangles, 35 MB of vertex data: the staged path, up to 4 ranges
+    grid = 1024
+    origin, dps = scene_params(tris, grid)
+    outs = []
+    for slices in ("1", "2", "3", "16"):
+        monkeypatch.setenv("HAKO_BUILD_SLICES", slices)
+        g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+        outs.append(tuple(a.copy() for a in g.export(True, True, True)))
+        g.cleanUp()
+    monkeypatch.delenv("HAKO_BUILD_SLICES")
+    dev = [torch.from_numpy(np.ascontiguousarray(a, np.float32)).cuda() for a in (tris, col, emi)]
+    g = hk.IntersectorOctreeGPU(ctx).build_device(dev[0], dev[1], dev[2], None, origin, float(dps), grid)
+    outs.append(tuple(a.copy() for a in g.export(True, True, True)))
+    g.cleanUp()
+    assert outs[0][1].size > 1_000_000 and np.unique(outs[0][2]["color"], axis=0).shape[0] > 1000
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8))
+
+
 @pytest.mark.parametrize("grid", [2048, 8192, 16384])
 def test_build_sweep_full_mesh_invariants(hk, ctx, bunny, golden, grid):
     """BASELINE config 4: the whole bunny at 2^11 / 2^13 / 2^14 (up to 554 M dumped voxels).  No CPU oracle finishes these in
