@@ -209,8 +209,14 @@ int scanU32( hako_ctx* ctx, cudaStream_t s, const uint32_t* in, uint32_t* out, u
 }
 
 // ---- 3./5. per-column enumeration ----
+#ifndef HAKO_EMIT_CTAS
+#define HAKO_EMIT_CTAS 6 // B200, bench scene: 4 / 5 / 6 / 8 CTAs per SM = 7.58 / 6.86 / 6.57 / 6.67 ms for the voxelize stage (80 B of spills at 6)
+#endif
+#ifndef HAKO_COUNT_CTAS
+#define HAKO_COUNT_CTAS 12 // 8 -> 12: another 0.15 ms (192 B of spills)
+#endif
 template <bool EMIT>
-__global__ void __launch_bounds__( 128 ) columnVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
+__global__ void __launch_bounds__( 128, EMIT ? HAKO_EMIT_CTAS : HAKO_COUNT_CTAS ) columnVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
 															uint32_t nTriangles, const uint32_t* __restrict__ colOffset, uint32_t nColumns,
 															V3 origin, float dps, int gridRes, int sixSeparating,
 															uint32_t* __restrict__ colCount, const uint32_t* __restrict__ voxOffset, uint32_t totalVoxels,
