@@ -38,6 +38,7 @@ extern "C" {
 typedef struct hako_ctx hako_ctx;
 typedef struct hako_octree hako_octree;
 typedef struct hako_pt hako_pt;
+typedef struct hako_pairs hako_pairs; /* sorted dumped voxels of one triangle shard, resident on the device */
 typedef struct hako_mesh hako_mesh;
 typedef struct hako_seq hako_seq;
 typedef void* hako_stream; /* cudaStream_t */
@@ -143,6 +144,22 @@ int hako_octree_device_arrays( const hako_octree* o, void** nodes_d, uint64_t* n
 							   void** attrs_d, uint64_t* attrBytes );
 /* allocate an empty replica of given sizes to receive a broadcast; fill via hako_octree_device_arrays */
 int hako_octree_create_replica( hako_ctx* ctx, const hako_octree_info* info, hako_octree** out );
+
+/* ---- a build sharded over GPUs (SURVEY.md 8e "sharding the build by Morton range"; no counterpart in the reference, whose
+ * IntersectorOctreeGPU::build runs on one device).  The same stages as hako_octree_build, cut where the exchanges go:
+ *   1. hako_voxelize_sorted       a rank's shard of the triangles (HOST arrays, scene frame) -> sorted (key, packed attribute)
+ *                                 pairs on the device; the caller exchanges them by Morton range (NCCL all-to-all);
+ *   2. hako_sort_unique_device    the pairs a rank received for its range (DEVICE, any order) -> sorted unique keys and
+ *                                 integer-mean attributes (== the `unique` kernel) in place at the front of the same arrays;
+ *   3. hako_octree_build_from_morton_device   the gathered unique voxels (DEVICE) -> octree, on every rank.
+ * Results are the bytes hako_octree_build produces on one GPU (tests/test_gpu_build.py, tests/test_dist_gpu.py). */
+int hako_voxelize_sorted( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+						  const float origin[3], float dps, int gridRes, hako_pairs** out );
+int hako_pairs_info( const hako_pairs* p, uint64_t* n, void** keys_d, void** values_d );
+void hako_pairs_destroy( hako_pairs* p );
+int hako_sort_unique_device( hako_ctx* ctx, hako_stream stream, uint64_t* keys_d, uint64_t* values_d, uint64_t n, int gridRes, uint64_t* U, uint32_t* hasEmission );
+int hako_octree_build_from_morton_device( hako_ctx* ctx, hako_stream stream, const uint64_t* mortons_d, const hako_voxel_attrib* attrs_d,
+										  uint64_t n, const float origin[3], float dps, int gridRes, int dag, int hasEmission, hako_octree** out );
 
 /* ---- build stages, exposed for stage-level parity and the build sweep (BASELINE config 4) ---- */
 /* voxCount + voxelize, voxKernel.cu:58-166.  HOST in, HOST out.  Call with keys == NULL to get D only.

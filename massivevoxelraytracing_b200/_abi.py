@@ -70,6 +70,11 @@ SIGNATURES = {
     "hako_octree_device_arrays": (i32, [vp, pp, pu64, pp, pu64, pp, pu64]),
     "hako_octree_create_replica": (i32, [vp, C.POINTER(OctreeInfo), pp]),
     "hako_voxelize": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, i32, vp, vp, u64, pu64]),
+    "hako_voxelize_sorted": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, pp]),
+    "hako_pairs_info": (i32, [vp, pu64, pp, pp]),
+    "hako_pairs_destroy": (None, [vp]),
+    "hako_sort_unique_device": (i32, [vp, vp, vp, vp, u64, i32, pu64, pu32]),
+    "hako_octree_build_from_morton_device": (i32, [vp, vp, vp, vp, u64, vp, f32, i32, i32, i32, pp]),
     "hako_sort_pairs_device": (i32, [vp, vp, vp, vp, u64, i32, i32]),
     "hako_sort_pairs": (i32, [vp, vp, vp, vp, u64, i32, i32]),
     "hako_unique_merge": (i32, [vp, vp, vp, vp, u64, pu64, pu32]),

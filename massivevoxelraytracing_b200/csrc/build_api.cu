@@ -317,6 +317,167 @@ int hako_octree_build_from_morton( hako_ctx* ctx, hako_stream stream, const uint
 	return HAKO_OK;
 }
 
+// ---- stages of a build sharded over GPUs (massivevoxelraytracing_b200/dist.py: build_sharded) ----
+// rank r voxelizes and sorts ITS triangles; the (key, packed attribute) pairs are exchanged by Morton range; every rank merges the
+// range it owns; the unique voxels are gathered and the DAG octree is built on every rank from the same sorted list.
+
+// stage 1: a shard of the triangle soup (HOST arrays, in the frame of the whole scene) -> sorted dumped voxels on the device
+int hako_voxelize_sorted( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+						  const float origin[3], float dps, int gridRes, hako_pairs** out )
+{
+	CHECK_ARG( ctx && out && origin, "hako_voxelize_sorted: null argument" );
+	CHECK_ARG( nTriangles == 0 || ( pos && col && emi ), "hako_voxelize_sorted: null vertex data" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ) && dps > 0.0f, "hako_voxelize_sorted: bad grid" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	hako_pairs* p = new hako_pairs();
+	p->ctx = ctx;
+	float* d = nullptr;
+	uint64_t *keys = nullptr, *values = nullptr, *keysTmp = nullptr, *valuesTmp = nullptr;
+	const uint64_t nf = (uint64_t)nTriangles * 9;
+	int r = 0;
+	do
+	{
+		uint64_t D = 0;
+		if( nf )
+		{
+			if( ( r = dalloc( ctx, &d, nf * 3, s ) ) ) break;
+			const H2DSegment segs[3] = { { d, pos, nf * 4 }, { d + nf, col, nf * 4 }, { d + 2 * nf, emi, nf * 4 } };
+			if( ( r = uploadSegments( ctx, s, segs, 3 ) ) ) break;
+			if( ( r = voxelizeDevice( ctx, s, d, d + nf, d + 2 * nf, nTriangles, V3{ origin[0], origin[1], origin[2] }, dps, gridRes, 1, &keys, &values, &D ) ) ) break;
+		}
+		if( D )
+		{
+			if( ( r = dalloc( ctx, &keysTmp, D, s ) ) ) break;
+			if( ( r = dalloc( ctx, &valuesTmp, D, s ) ) ) break;
+			int inTmp = 0;
+			if( ( r = sortPairsDevice( ctx, s, keys, values, keysTmp, valuesTmp, D, 0, sortEndBit( gridRes ), &inTmp ) ) ) break;
+			if( inTmp ) std::swap( keys, keysTmp ), std::swap( values, valuesTmp );
+		}
+		cudaError_t e = cudaStreamSynchronize( s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "hako_voxelize_sorted", __FILE__, __LINE__ );
+			break;
+		}
+		p->keys = keys, p->values = values, p->n = D;
+		keys = values = nullptr;
+	} while( 0 );
+	dfree( d, s ), dfree( keys, s ), dfree( values, s ), dfree( keysTmp, s ), dfree( valuesTmp, s );
+	if( r )
+	{
+		delete p;
+		return r;
+	}
+	*out = p;
+	return HAKO_OK;
+}
+int hako_pairs_info( const hako_pairs* p, uint64_t* n, void** keys_d, void** values_d )
+{
+	CHECK_ARG( p, "hako_pairs_info: null argument" );
+	if( n ) *n = p->n;
+	if( keys_d ) *keys_d = p->keys;
+	if( values_d ) *values_d = p->values;
+	return HAKO_OK;
+}
+void hako_pairs_destroy( hako_pairs* p )
+{
+	if( !p ) return;
+	cudaSetDevice( p->ctx->device );
+	dfree( p->keys, (cudaStream_t) nullptr ), dfree( p->values, (cudaStream_t) nullptr );
+	delete p;
+}
+
+// stage 2: pairs received from every rank for the Morton range this rank owns (DEVICE arrays, a concatenation of sorted runs)
+// -> sorted unique keys + integer-mean attributes, in place at the front of the same arrays
+int hako_sort_unique_device( hako_ctx* ctx, hako_stream stream, uint64_t* keys_d, uint64_t* values_d, uint64_t n, int gridRes, uint64_t* U, uint32_t* hasEmission )
+{
+	CHECK_ARG( ctx && U && ( n == 0 || ( keys_d && values_d ) ), "hako_sort_unique_device: null argument" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_sort_unique_device: bad grid" );
+	CHECK_ARG( n < 0xFFFFFFFFull, "hako_sort_unique_device: more than 2^32 - 1 pairs" );
+	*U = 0;
+	if( hasEmission ) *hasEmission = 0;
+	if( n == 0 ) return HAKO_OK;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	uint64_t *keysTmp = nullptr, *valuesTmp = nullptr;
+	int r = 0;
+	do
+	{
+		if( ( r = dalloc( ctx, &keysTmp, n, s ) ) ) break;
+		if( ( r = dalloc( ctx, &valuesTmp, n, s ) ) ) break;
+		int inTmp = 0;
+		if( ( r = sortPairsDevice( ctx, s, keys_d, values_d, keysTmp, valuesTmp, n, 0, sortEndBit( gridRes ), &inTmp ) ) ) break;
+		uint64_t* sk = inTmp ? keysTmp : keys_d;
+		uint64_t* sv = inTmp ? valuesTmp : values_d;
+		uint64_t* uk = inTmp ? keys_d : keysTmp;
+		uint64_t* ua = inTmp ? values_d : valuesTmp;
+		uint32_t he = 0;
+		if( ( r = uniqueMergeDevice( ctx, s, sk, sv, n, uk, (hako_voxel_attrib*)ua, U, &he ) ) ) break; // synchronises to read U
+		if( hasEmission ) *hasEmission = he;
+		if( uk != keys_d )
+		{
+			cudaError_t e = cudaMemcpyAsync( keys_d, uk, *U * 8, cudaMemcpyDeviceToDevice, s );
+			if( e == cudaSuccess ) e = cudaMemcpyAsync( values_d, ua, *U * 8, cudaMemcpyDeviceToDevice, s );
+			if( e != cudaSuccess )
+			{
+				r = cudaFail( e, "hako_sort_unique_device", __FILE__, __LINE__ );
+				break;
+			}
+		}
+	} while( 0 );
+	dfree( keysTmp, s ), dfree( valuesTmp, s );
+	return r;
+}
+
+// stage 3: the gathered sorted unique voxels (DEVICE arrays) -> octree; == hako_octree_build_from_morton without the upload
+int hako_octree_build_from_morton_device( hako_ctx* ctx, hako_stream stream, const uint64_t* mortons_d, const hako_voxel_attrib* attrs_d,
+										  uint64_t n, const float origin[3], float dps, int gridRes, int dag, int hasEmission, hako_octree** out )
+{
+	CHECK_ARG( ctx && out && origin && ( n == 0 || mortons_d ), "hako_octree_build_from_morton_device: null argument" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build_from_morton_device: gridRes must be a power of two <= 2^21" );
+	CHECK_ARG( n < 0xFFFFFFFFull, "hako_octree_build_from_morton_device: more than 2^32 - 1 voxels" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	hako_octree* o = new hako_octree();
+	initOctree( o, ctx, origin, dps, gridRes );
+	o->numberOfVoxels = (uint32_t)n;
+	o->hasEmission = hasEmission ? 1u : 0u;
+	int r = 0;
+	do
+	{
+		cudaError_t e = cudaSuccess;
+		if( ( r = dalloc( ctx, &o->mortons, n, s ) ) ) break;
+		if( n ) e = cudaMemcpyAsync( o->mortons, mortons_d, n * 8, cudaMemcpyDeviceToDevice, s );
+		if( e == cudaSuccess && attrs_d && n )
+		{
+			if( ( r = dalloc( ctx, &o->attrs, n, s ) ) ) break;
+			e = cudaMemcpyAsync( o->attrs, attrs_d, n * 8, cudaMemcpyDeviceToDevice, s );
+		}
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "D2D voxels", __FILE__, __LINE__ );
+			break;
+		}
+		uint32_t launches = 0;
+		if( ( r = buildOctreeDevice( ctx, s, o->mortons, n, gridRes, dag, &o->nodes, &o->masks, &o->numberOfNodes, &launches, &o->wide ) ) ) break;
+		ctx->stats.uniqueVoxels = n;
+		ctx->stats.numberOfNodes = o->numberOfNodes;
+		ctx->stats.kernelLaunches = launches;
+		if( ( e = cudaStreamSynchronize( s ) ) != cudaSuccess ) r = cudaFail( e, "sync", __FILE__, __LINE__ );
+	} while( 0 );
+	if( r )
+	{
+		hako_octree_destroy( o );
+		return r;
+	}
+	*out = o;
+	return HAKO_OK;
+}
+
 int hako_voxelize( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
 				   const float origin[3], float dps, int gridRes, int sixSeparating,
 				   uint64_t* keys, hako_voxel_attrib* attrs, uint64_t capacity, uint64_t* D )

@@ -31,6 +31,15 @@ struct hako_ctx
 	hako::Stager* stager = nullptr;
 };
 
+// sorted dumped voxels of one shard (hako_voxelize_sorted)
+struct hako_pairs
+{
+	hako_ctx* ctx = nullptr;
+	uint64_t* keys = nullptr;
+	uint64_t* values = nullptr;
+	uint64_t n = 0;
+};
+
 struct hako_octree
 {
 	hako_ctx* ctx = nullptr;

@@ -79,3 +79,192 @@ def reduce_accum(tensor, dst=0, group=None):
     """sum the per-rank float4 accumulators onto rank dst (in place)"""
     dist.reduce(tensor, dst, op=dist.ReduceOp.SUM, group=group)
     return tensor
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# Build sharded over the ranks (SURVEY.md 8e: "sharding the build by Morton range (one all-to-all of keys by top digits)").
+#
+#   rank r:  triangles [T r / G, T (r+1) / G)  --voxelize + sort-->  sorted (key, packed attribute) pairs          (own GPU)
+#            splitters = weighted quantiles of evenly spaced key samples of every rank                    (all_gather, tiny)
+#            pairs with splitter[j-1] <= key < splitter[j] go to rank j                          (ONE all-to-all over NVLink)
+#            received runs --sort + unique / integer-mean merge-->  the unique voxels of the rank's Morton range   (own GPU)
+#            unique voxels of every range, in range order = the sorted unique list of the scene        (gather, broadcasts)
+#            DAG octree from that list on every rank (its node numbering is global, so this stage is replicated)   (own GPU)
+#
+# Every dumped voxel of a key lands on the rank that owns the key, so the merged attributes are the single-GPU integer means
+# and the octree is the single-GPU octree, byte for byte (tests/test_dist_gpu.py; host logic: tests/test_dist_cpu.py on gloo).
+# No rank ever holds the whole triangle soup or the whole dumped-voxel list, and no octree broadcast is needed afterwards.
+# ---------------------------------------------------------------------------------------------------------------------------
+SPLITTER_SAMPLES = 2048
+
+
+def triangle_shard(n_triangles, rank, world):
+    """contiguous triangle range [t0, t1) of rank `rank`"""
+    return (n_triangles * rank) // world, (n_triangles * (rank + 1)) // world
+
+
+def choose_splitters(samples, counts, world):
+    """samples: [world, S] evenly spaced keys of every rank's sorted pairs (int64); counts: [world] pairs per rank.
+    Returns world-1 keys that cut the union into ranges of about equal size (weighted quantiles: a sample of rank r stands for
+    counts[r] / S pairs).  Pure host arithmetic -- every rank computes the same splitters from the same gathered input."""
+    samples = np.asarray(samples, np.int64)
+    counts = np.asarray(counts, np.float64)
+    S = samples.shape[1]
+    w = np.repeat(counts / max(S, 1), S)
+    flat = samples.reshape(-1)
+    keep = np.repeat(counts > 0, S)
+    flat, w = flat[keep], w[keep]
+    if flat.size == 0:
+        return np.zeros(world - 1, np.int64)
+    order = np.argsort(flat, kind="stable")
+    flat, cw = flat[order], np.cumsum(w[order])
+    total = cw[-1]
+    cuts = [flat[min(int(np.searchsorted(cw, total * j / world, side="left")), flat.size - 1)] for j in range(1, world)]
+    return np.maximum.accumulate(np.asarray(cuts, np.int64))
+
+
+def _all_to_all_v(send, send_counts, recv_counts, group=None):
+    """variable all-to-all of a 1-D tensor: NCCL all_to_all_single; on gloo (CPU tests) a loop of broadcasts"""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    recv = torch.empty(int(sum(recv_counts)), dtype=send.dtype, device=send.device)
+    if dist.get_backend(group) == "nccl":
+        dist.all_to_all_single(recv, send, [int(c) for c in recv_counts], [int(c) for c in send_counts], group=group)
+        return recv
+    sizes = [None] * world
+    dist.all_gather_object(sizes, [int(c) for c in send_counts], group=group)
+    roff = np.concatenate([[0], np.cumsum(recv_counts)]).astype(np.int64)
+    for src in range(world):
+        buf = send if src == rank else torch.empty(int(sum(sizes[src])), dtype=send.dtype, device=send.device)
+        if buf.numel():
+            dist.broadcast(buf, src, group=group)
+        o = int(sum(sizes[src][:rank]))
+        recv[roff[src]:roff[src + 1]] = buf[o:o + sizes[src][rank]]
+    return recv
+
+
+class LibStages:
+    """the three device stages of a sharded build, on libhako_b200.so (include/hako.h: hako_voxelize_sorted,
+    hako_sort_unique_device, hako_octree_build_from_morton_device)"""
+
+    def __init__(self, ctx, octree_cls):
+        self.ctx, self.octree_cls = ctx, octree_cls
+        self.device = torch.device("cuda", ctx.device)
+        self._pairs = None
+
+    def voxelize_sorted(self, tris, col, emi, origin, dps, grid):
+        f = lambda a: np.ascontiguousarray(a, np.float32)
+        tris, col, emi = f(tris), f(col), f(emi)
+        h = C.c_void_p()
+        org = np.ascontiguousarray(origin, np.float32)
+        check(self.ctx.lib.hako_voxelize_sorted(self.ctx.h, None, tris.ctypes.data, col.ctypes.data, emi.ctypes.data, tris.size // 9,
+                                                org.ctypes.data, float(dps), int(grid), C.byref(h)))
+        n, k, v = C.c_uint64(), C.c_void_p(), C.c_void_p()
+        check(self.ctx.lib.hako_pairs_info(h, C.byref(n), C.byref(k), C.byref(v)))
+        self._pairs = h
+        keys = as_tensor(k.value or 0, n.value * 8, self.device).view(torch.int64)
+        vals = as_tensor(v.value or 0, n.value * 8, self.device).view(torch.int64)
+        return keys, vals
+
+    def release_pairs(self):
+        if self._pairs is not None:
+            self.ctx.lib.hako_pairs_destroy(self._pairs)
+            self._pairs = None
+
+    def sort_unique(self, keys, vals, grid):
+        U, he = C.c_uint64(), C.c_uint32()
+        check(self.ctx.lib.hako_sort_unique_device(self.ctx.h, None, keys.data_ptr() if keys.numel() else None, vals.data_ptr() if vals.numel() else None,
+                                                   keys.numel(), int(grid), C.byref(U), C.byref(he)))
+        return int(U.value), bool(he.value)
+
+    def build_from_unique(self, mortons, attrs, origin, dps, grid, has_emission):
+        h = C.c_void_p()
+        org = np.ascontiguousarray(origin, np.float32)
+        check(self.ctx.lib.hako_octree_build_from_morton_device(self.ctx.h, None, mortons.data_ptr() if mortons.numel() else None,
+                                                                attrs.data_ptr() if attrs.numel() else None, mortons.numel(), org.ctypes.data,
+                                                                float(dps), int(grid), 1, int(bool(has_emission)), C.byref(h)))
+        o = self.octree_cls(self.ctx)
+        o._adopt(h)
+        return o
+
+    def sync(self):
+        torch.cuda.synchronize(self.device)
+
+
+def build_sharded(stages, tris, col, emi, origin, dps, grid, group=None, times=None):
+    """Build the octree of the whole triangle soup with every rank doing 1/G of the voxelization, sort and merge.
+    `tris / col / emi`: float32 [T, 3, 3] host arrays -- every rank passes the SAME arrays (or at least its own shard's rows
+    valid); `stages`: LibStages (GPU) or a test double with the same four methods.  Returns the octree object of this rank
+    (identical on every rank).  `times`, if a dict, receives wall-clock milliseconds per phase (synchronised)."""
+    import time
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    T = int(np.asarray(tris).reshape(-1, 9).shape[0])
+
+    def mark(name, t0):
+        if times is not None:
+            stages.sync()
+            times[name] = times.get(name, 0.0) + (time.perf_counter() - t0) * 1e3
+        return time.perf_counter()
+
+    t = time.perf_counter()
+    t0, t1 = triangle_shard(T, rank, world)
+    sl = lambda a: np.asarray(a, np.float32).reshape(-1, 9)[t0:t1]
+    keys, vals = stages.voxelize_sorted(sl(tris), sl(col), sl(emi), origin, dps, grid)
+    dev = keys.device
+    t = mark("voxelize_sort_ms", t)
+
+    # splitters from evenly spaced samples of every rank's sorted keys
+    n = keys.numel()
+    S = SPLITTER_SAMPLES
+    if n:
+        idx = torch.linspace(0, n - 1, S, device=dev).round().long()
+        mine = torch.cat([keys[idx], torch.tensor([n], dtype=torch.int64, device=dev)])
+    else:
+        mine = torch.zeros(S + 1, dtype=torch.int64, device=dev)
+    gathered = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(gathered, mine, group=group)
+    g = torch.stack(gathered).cpu().numpy()
+    splitters = choose_splitters(g[:, :S], g[:, S], world)
+    cuts = torch.searchsorted(keys, torch.from_numpy(splitters).to(dev), right=False) if n else torch.zeros(world - 1, dtype=torch.int64, device=dev)
+    bounds = np.concatenate([[0], cuts.cpu().numpy(), [n]]).astype(np.int64)
+    send_counts = np.diff(bounds)
+    cm = [torch.empty(world, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(cm, torch.from_numpy(send_counts).to(dev), group=group)
+    recv_counts = torch.stack(cm).cpu().numpy()[:, rank]
+    t = mark("splitters_ms", t)
+
+    rk = _all_to_all_v(keys, send_counts, recv_counts, group)
+    rv = _all_to_all_v(vals, send_counts, recv_counts, group)
+    del keys, vals
+    if hasattr(stages, "release_pairs"):
+        stages.sync()
+        stages.release_pairs()
+    t = mark("exchange_ms", t)
+
+    U, he = stages.sort_unique(rk, rv, grid)
+    t = mark("sort_unique_ms", t)
+
+    meta = [torch.empty(2, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(meta, torch.tensor([U, int(he)], dtype=torch.int64, device=dev), group=group)
+    meta = torch.stack(meta).cpu().numpy()
+    offs = np.concatenate([[0], np.cumsum(meta[:, 0])]).astype(np.int64)
+    total = int(offs[-1])
+    mortons = torch.empty(total, dtype=torch.int64, device=dev)
+    attrs = torch.empty(total, dtype=torch.int64, device=dev)
+    mortons[offs[rank]:offs[rank + 1]] = rk[:U]
+    attrs[offs[rank]:offs[rank + 1]] = rv[:U]
+    del rk, rv
+    for r in range(world):
+        if offs[r + 1] > offs[r]:
+            dist.broadcast(mortons[offs[r]:offs[r + 1]], r, group=group)
+            dist.broadcast(attrs[offs[r]:offs[r + 1]], r, group=group)
+    t = mark("gather_unique_ms", t)
+
+    octree = stages.build_from_unique(mortons, attrs, origin, dps, grid, bool(meta[:, 1].any()))
+    mark("octree_ms", t)
+    if times is not None:
+        times["dumped_voxels_this_rank"] = int(n)
+        times["range_voxels_this_rank"] = int(U)
+        times["unique_voxels"] = total
+    return octree

@@ -73,3 +73,106 @@ def test_gloo_world2_reduce_and_header():
     np.testing.assert_allclose(r0[0], r0[1], rtol=1e-6)
     assert (r0[0][..., 3] == 96.0).all()
     assert r0[2] and other
+
+
+# ---- sharded build: the host logic of hdist.build_sharded on gloo, with the CPU oracle standing in for the device stages ----
+class _OracleStages:
+    """test double of hdist.LibStages: the same four methods on host tensors, computed by the oracle"""
+
+    def __init__(self, oracle):
+        self.o = oracle
+
+    def voxelize_sorted(self, tris, col, emi, origin, dps, grid):
+        if tris.shape[0] == 0:
+            return torch.zeros(0, dtype=torch.int64), torch.zeros(0, dtype=torch.int64)
+        keys, c, e = self.o.voxelize(tris.reshape(-1, 3, 3), col.reshape(-1, 3, 3), emi.reshape(-1, 3, 3), origin, float(dps), grid)
+        vals = np.ascontiguousarray(np.concatenate([c, e], axis=1)).view(np.uint64).reshape(-1)   # colour | emission << 32
+        order = np.argsort(keys, kind="stable")
+        return torch.from_numpy(keys[order].view(np.int64).copy()), torch.from_numpy(vals[order].view(np.int64).copy())
+
+    def sort_unique(self, keys, vals, grid):
+        k = keys.numpy().view(np.uint64)
+        order = np.argsort(k, kind="stable")
+        a = np.ascontiguousarray(vals.numpy()[order]).view(np.uint8).reshape(-1, 8)
+        mk, mc, me = self.o.merge_voxels(k[order], a[:, :4].copy(), a[:, 4:].copy())
+        U = mk.size
+        keys[:U] = torch.from_numpy(mk.view(np.int64).copy())
+        vals[:U] = torch.from_numpy(np.ascontiguousarray(np.concatenate([mc, me], axis=1)).view(np.int64).reshape(-1))
+        return U, bool(me[:, :3].any())
+
+    def build_from_unique(self, mortons, attrs, origin, dps, grid, has_emission):
+        return mortons.numpy().view(np.uint64).copy(), attrs.numpy().copy().view(np.uint8).reshape(-1, 8), has_emission
+
+    def sync(self):
+        pass
+
+
+def _shard_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from massivevoxelraytracing_b200 import dist as hdist
+    from oracle import orc
+    from scenes import bunny_scene, scene_params
+    o = orc.Oracle("port")
+    tris, col, emi = bunny_scene()
+    grid = 64
+    origin, dps = scene_params(tris, grid)
+    times = {}
+    mk, at, he = hdist.build_sharded(_OracleStages(o), tris, col, emi, origin, dps, grid, times=times)
+    q.put((rank, mk, at, he, times))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_sharded_build_equals_single_rank(world, oracle, bunny):
+    """every rank ends with the sorted unique voxel list (keys + integer-mean attributes) of the whole mesh: the shards are
+    voxelized separately, exchanged by Morton range (splitters from samples), merged per range and gathered"""
+    from scenes import scene_params
+    tris, col, emi = bunny
+    grid = 64
+    origin, dps = scene_params(tris, grid)
+    keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), grid)
+    mk, mc, me = oracle.merge_voxels(keys, c, e)
+    ctxm = mp.get_context("spawn")
+    q = ctxm.Queue()
+    port = 29600 + (os.getpid() % 1000) + world
+    procs = [ctxm.Process(target=_shard_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    ranges = []
+    for rank, gk, ga, he, times in res:
+        assert np.array_equal(gk, mk)
+        assert np.array_equal(ga[:, :4], mc) and np.array_equal(ga[:, 4:], me)
+        assert he == bool(me[:, :3].any())
+        ranges.append(times["range_voxels_this_rank"])
+        assert times["unique_voxels"] == mk.size
+    # the splitters balance the ranges (bunny at 64^3: within a factor of two of the mean)
+    assert sum(ranges) == mk.size and max(ranges) < 2.0 * mk.size / world
+
+
+def test_choose_splitters_and_shards():
+    from massivevoxelraytracing_b200.dist import choose_splitters, triangle_shard
+    for T in (0, 1, 7, 5110):
+        for world in (1, 2, 3, 8):
+            cover = []
+            for r in range(world):
+                t0, t1 = triangle_shard(T, r, world)
+                cover += list(range(t0, t1))
+            assert cover == list(range(T))
+    rng = np.random.default_rng(0)
+    a = np.sort(rng.integers(0, 1 << 40, (4, 256)), axis=1)
+    s = choose_splitters(a, [1000, 1000, 1000, 1000], 4)
+    assert s.shape == (3,) and (np.diff(s) >= 0).all()
+    frac = [(a < x).mean() for x in s]
+    assert np.allclose(frac, [0.25, 0.5, 0.75], atol=0.03)
+    # a rank without pairs carries no weight; all-empty input is legal
+    s2 = choose_splitters(np.stack([a[0], np.zeros(256, np.int64)]), [1000, 0], 2)
+    assert abs((a[0] < s2[0]).mean() - 0.5) < 0.03
+    assert choose_splitters(np.zeros((2, 16), np.int64), [0, 0], 2).tolist() == [0]
