@@ -160,6 +160,11 @@ void hako_pairs_destroy( hako_pairs* p );
 int hako_sort_unique_device( hako_ctx* ctx, hako_stream stream, uint64_t* keys_d, uint64_t* values_d, uint64_t n, int gridRes, uint64_t* U, uint32_t* hasEmission );
 int hako_octree_build_from_morton_device( hako_ctx* ctx, hako_stream stream, const uint64_t* mortons_d, const hako_voxel_attrib* attrs_d,
 										  uint64_t n, const float origin[3], float dps, int gridRes, int dag, int hasEmission, hako_octree** out );
+/* stage 3 without the staging copy: the octree object first -- its resident key / attribute arrays, sized for n voxels, are
+ * returned so that the gathering collective can write into them -- then the nodes, built from those arrays in place */
+int hako_octree_create_for_voxels( hako_ctx* ctx, hako_stream stream, uint64_t n, const float origin[3], float dps, int gridRes, hako_octree** out,
+								   void** mortons_d, void** attrs_d );
+int hako_octree_build_nodes( hako_octree* octree, hako_stream stream, int dag, int hasEmission );
 
 /* ---- build stages, exposed for stage-level parity and the build sweep (BASELINE config 4) ---- */
 /* voxCount + voxelize, voxKernel.cu:58-166.  HOST in, HOST out.  Call with keys == NULL to get D only.

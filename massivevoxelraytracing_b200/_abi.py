@@ -75,6 +75,8 @@ SIGNATURES = {
     "hako_pairs_destroy": (None, [vp]),
     "hako_sort_unique_device": (i32, [vp, vp, vp, vp, u64, i32, pu64, pu32]),
     "hako_octree_build_from_morton_device": (i32, [vp, vp, vp, vp, u64, vp, f32, i32, i32, i32, pp]),
+    "hako_octree_create_for_voxels": (i32, [vp, vp, u64, vp, f32, i32, pp, pp, pp]),
+    "hako_octree_build_nodes": (i32, [vp, vp, i32, i32]),
     "hako_sort_pairs_device": (i32, [vp, vp, vp, vp, u64, i32, i32]),
     "hako_sort_pairs": (i32, [vp, vp, vp, vp, u64, i32, i32]),
     "hako_unique_merge": (i32, [vp, vp, vp, vp, u64, pu64, pu32]),

@@ -145,38 +145,11 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 	return HAKO_OK;
 }
 
-extern "C" {
-
-int hako_octree_build_device( hako_ctx* ctx, hako_stream stream, const float* pos_d, const float* col_d, const float* emi_d,
-							  uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out )
+// The caller's three HOST vertex arrays go up with the call (IntersectorOctreeGPU.hpp:68-70) and `body` runs on the device copies:
+// body( pos_d, col_d, emi_d, beforeAttributesAreRead, slices ) -- see voxelizeDevice for the hook.
+static int withStagedTriangles( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+								const std::function<int( const float*, const float*, const float*, const std::function<int( int )>&, int )>& body )
 {
-	CHECK_ARG( ctx && out && origin, "hako_octree_build_device: null argument" );
-	CHECK_ARG( nTriangles == 0 || ( pos_d && col_d && emi_d ), "hako_octree_build_device: null vertex data" );
-	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build: gridRes must be a power of two <= 2^21 (IntersectorOctreeGPU.hpp:48-51 aborts)" );
-	CHECK_ARG( dps > 0.0f, "hako_octree_build: dps must be positive" );
-	*out = nullptr;
-	cudaStream_t s = (cudaStream_t)stream;
-	HAKO_CUDA( cudaSetDevice( ctx->device ) );
-	ctx->stats = hako_build_stats{};
-	ctx->stats.nTriangles = nTriangles;
-	HAKO_CUDA( cudaEventRecord( ctx->ev[0], s ) );
-	return buildFromDeviceTriangles( ctx, s, pos_d, col_d, emi_d, nTriangles, origin, dps, gridRes, out );
-}
-
-int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi,
-					   uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out )
-{
-	CHECK_ARG( ctx && out && origin, "hako_octree_build: null argument" );
-	CHECK_ARG( nTriangles == 0 || ( pos && col && emi ), "hako_octree_build: null vertex data" );
-	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build: gridRes must be a power of two <= 2^21 (IntersectorOctreeGPU.hpp:48-51 aborts)" );
-	CHECK_ARG( dps > 0.0f, "hako_octree_build: dps must be positive" );
-	*out = nullptr;
-	cudaStream_t s = (cudaStream_t)stream;
-	HAKO_CUDA( cudaSetDevice( ctx->device ) );
-	ctx->stats = hako_build_stats{};
-	ctx->stats.nTriangles = nTriangles;
-	HAKO_CUDA( cudaEventRecord( ctx->ev[0], s ) );
-	// IntersectorOctreeGPU.hpp:68-70: the three vertex arrays go up with the call
 	float* d = nullptr;
 	const uint64_t nf = (uint64_t)nTriangles * 9;
 	HAKO_TRY( dalloc( ctx, &d, nf * 3, s ) );
@@ -253,19 +226,56 @@ int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, cons
 			cv.wait( lk, [&]() { return slicesUp >= need || helperDone; } );
 			if( helperResult )
 			{
-				setError( "hako_octree_build: staged upload of the colour / emission arrays failed" );
+				setError( "staged upload of the colour / emission arrays failed" );
 				return helperResult;
 			}
 		}
 		HAKO_CUDA( cudaStreamWaitEvent( s, sliceEv[need - 1], 0 ) );
 		return 0;
 	};
-	if( r == 0 ) r = buildFromDeviceTriangles( ctx, s, d, d + nf, d + 2 * nf, nTriangles, origin, dps, gridRes, out, join, SLICES );
+	if( r == 0 ) r = body( d, d + nf, d + 2 * nf, join, SLICES );
 	if( helper.joinable() ) helper.join();
 	for( int k = 0; k < 16; k++ )
 		if( sliceEv[k] ) cudaEventDestroy( sliceEv[k] );
 	dfree( d, s );
 	return r;
+}
+
+
+extern "C" {
+
+int hako_octree_build_device( hako_ctx* ctx, hako_stream stream, const float* pos_d, const float* col_d, const float* emi_d,
+							  uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out )
+{
+	CHECK_ARG( ctx && out && origin, "hako_octree_build_device: null argument" );
+	CHECK_ARG( nTriangles == 0 || ( pos_d && col_d && emi_d ), "hako_octree_build_device: null vertex data" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build: gridRes must be a power of two <= 2^21 (IntersectorOctreeGPU.hpp:48-51 aborts)" );
+	CHECK_ARG( dps > 0.0f, "hako_octree_build: dps must be positive" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	ctx->stats.nTriangles = nTriangles;
+	HAKO_CUDA( cudaEventRecord( ctx->ev[0], s ) );
+	return buildFromDeviceTriangles( ctx, s, pos_d, col_d, emi_d, nTriangles, origin, dps, gridRes, out );
+}
+
+int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi,
+					   uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out )
+{
+	CHECK_ARG( ctx && out && origin, "hako_octree_build: null argument" );
+	CHECK_ARG( nTriangles == 0 || ( pos && col && emi ), "hako_octree_build: null vertex data" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_build: gridRes must be a power of two <= 2^21 (IntersectorOctreeGPU.hpp:48-51 aborts)" );
+	CHECK_ARG( dps > 0.0f, "hako_octree_build: dps must be positive" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	ctx->stats.nTriangles = nTriangles;
+	HAKO_CUDA( cudaEventRecord( ctx->ev[0], s ) );
+	return withStagedTriangles( ctx, s, pos, col, emi, nTriangles, [&]( const float* p_d, const float* c_d, const float* e_d, const std::function<int( int )>& join, int slices ) {
+		return buildFromDeviceTriangles( ctx, s, p_d, c_d, e_d, nTriangles, origin, dps, gridRes, out, join, slices );
+	} );
 }
 
 int hako_octree_build_from_morton( hako_ctx* ctx, hako_stream stream, const uint64_t* mortons, const hako_voxel_attrib* attrs,
@@ -333,20 +343,15 @@ int hako_voxelize_sorted( hako_ctx* ctx, hako_stream stream, const float* pos, c
 	HAKO_CUDA( cudaSetDevice( ctx->device ) );
 	hako_pairs* p = new hako_pairs();
 	p->ctx = ctx;
-	float* d = nullptr;
 	uint64_t *keys = nullptr, *values = nullptr, *keysTmp = nullptr, *valuesTmp = nullptr;
-	const uint64_t nf = (uint64_t)nTriangles * 9;
-	int r = 0;
+	uint64_t D = 0;
+	// same staged, range-overlapped upload as hako_octree_build
+	int r = withStagedTriangles( ctx, s, pos, col, emi, nTriangles, [&]( const float* p_d, const float* c_d, const float* e_d, const std::function<int( int )>& join, int slices ) {
+		return voxelizeDevice( ctx, s, p_d, c_d, e_d, nTriangles, V3{ origin[0], origin[1], origin[2] }, dps, gridRes, 1, &keys, &values, &D, join, slices );
+	} );
 	do
 	{
-		uint64_t D = 0;
-		if( nf )
-		{
-			if( ( r = dalloc( ctx, &d, nf * 3, s ) ) ) break;
-			const H2DSegment segs[3] = { { d, pos, nf * 4 }, { d + nf, col, nf * 4 }, { d + 2 * nf, emi, nf * 4 } };
-			if( ( r = uploadSegments( ctx, s, segs, 3 ) ) ) break;
-			if( ( r = voxelizeDevice( ctx, s, d, d + nf, d + 2 * nf, nTriangles, V3{ origin[0], origin[1], origin[2] }, dps, gridRes, 1, &keys, &values, &D ) ) ) break;
-		}
+		if( r ) break;
 		if( D )
 		{
 			if( ( r = dalloc( ctx, &keysTmp, D, s ) ) ) break;
@@ -364,7 +369,7 @@ int hako_voxelize_sorted( hako_ctx* ctx, hako_stream stream, const float* pos, c
 		p->keys = keys, p->values = values, p->n = D;
 		keys = values = nullptr;
 	} while( 0 );
-	dfree( d, s ), dfree( keys, s ), dfree( values, s ), dfree( keysTmp, s ), dfree( valuesTmp, s );
+	dfree( keys, s ), dfree( values, s ), dfree( keysTmp, s ), dfree( valuesTmp, s );
 	if( r )
 	{
 		delete p;
@@ -475,6 +480,54 @@ int hako_octree_build_from_morton_device( hako_ctx* ctx, hako_stream stream, con
 		return r;
 	}
 	*out = o;
+	return HAKO_OK;
+}
+
+// stage 3, without a staging copy: the octree object first (its resident key / attribute arrays sized for the gathered voxels, to
+// be filled in place by the collective), then the nodes
+int hako_octree_create_for_voxels( hako_ctx* ctx, hako_stream stream, uint64_t n, const float origin[3], float dps, int gridRes, hako_octree** out,
+								   void** mortons_d, void** attrs_d )
+{
+	CHECK_ARG( ctx && out && origin, "hako_octree_create_for_voxels: null argument" );
+	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_octree_create_for_voxels: gridRes must be a power of two <= 2^21" );
+	CHECK_ARG( n < 0xFFFFFFFFull, "hako_octree_create_for_voxels: more than 2^32 - 1 voxels" );
+	*out = nullptr;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	hako_octree* o = new hako_octree();
+	initOctree( o, ctx, origin, dps, gridRes );
+	o->numberOfVoxels = (uint32_t)n;
+	int r = dalloc( ctx, &o->mortons, n, s );
+	if( r == 0 ) r = dalloc( ctx, &o->attrs, n, s );
+	if( r == 0 )
+	{
+		cudaError_t e = cudaStreamSynchronize( s ); // the arrays are handed to another library's streams
+		if( e != cudaSuccess ) r = cudaFail( e, "hako_octree_create_for_voxels", __FILE__, __LINE__ );
+	}
+	if( r )
+	{
+		hako_octree_destroy( o );
+		return r;
+	}
+	if( mortons_d ) *mortons_d = o->mortons;
+	if( attrs_d ) *attrs_d = o->attrs;
+	*out = o;
+	return HAKO_OK;
+}
+int hako_octree_build_nodes( hako_octree* o, hako_stream stream, int dag, int hasEmission )
+{
+	CHECK_ARG( o && !o->nodes, "hako_octree_build_nodes: null octree or nodes already built" );
+	hako_ctx* ctx = o->ctx;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	ctx->stats = hako_build_stats{};
+	o->hasEmission = hasEmission ? 1u : 0u;
+	uint32_t launches = 0;
+	HAKO_TRY( buildOctreeDevice( ctx, s, o->mortons, o->numberOfVoxels, o->gridRes, dag, &o->nodes, &o->masks, &o->numberOfNodes, &launches, &o->wide ) );
+	ctx->stats.uniqueVoxels = o->numberOfVoxels;
+	ctx->stats.numberOfNodes = o->numberOfNodes;
+	ctx->stats.kernelLaunches = launches;
+	HAKO_CUDA( cudaStreamSynchronize( s ) );
 	return HAKO_OK;
 }
 

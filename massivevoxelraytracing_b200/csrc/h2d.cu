@@ -37,6 +37,13 @@ static int makeStager( hako_ctx* ctx )
 	// measured on the B200 box (16 vCPU, 565 MB): 1 worker 47.7 ms, 2: 29.2, 4: 14.2, 8: 12.8 (plain pageable copy: 50.2)
 	const unsigned hc = std::thread::hardware_concurrency();
 	int w = hc >= 16 ? 8 : 4;
+	// one process per GPU on the same host (torchrun exports LOCAL_WORLD_SIZE): the ranks stage their uploads at the same time
+	// and share the cores
+	if( const char* e = getenv( "LOCAL_WORLD_SIZE" ) )
+	{
+		const int ranks = atoi( e );
+		if( ranks > 1 && hc ) w = std::max( 2, std::min( w, (int)hc / ranks ) );
+	}
 	if( const char* e = getenv( "HAKO_H2D_WORKERS" ) ) w = atoi( e );
 	if( hc && (unsigned)w > hc ) w = (int)hc;
 	st->workers = std::max( 1, std::min( w, (int)Stager::MAX_WORKERS ) );

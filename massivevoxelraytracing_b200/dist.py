@@ -187,6 +187,21 @@ class LibStages:
         o._adopt(h)
         return o
 
+    def alloc_unique(self, total, origin, dps, grid):
+        """the octree object with its resident key / attribute arrays (library memory) as int64 tensors to gather into"""
+        h, m, a = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        org = np.ascontiguousarray(origin, np.float32)
+        check(self.ctx.lib.hako_octree_create_for_voxels(self.ctx.h, None, int(total), org.ctypes.data, float(dps), int(grid), C.byref(h), C.byref(m), C.byref(a)))
+        self._shell = h
+        return (as_tensor(m.value or 0, total * 8, self.device).view(torch.int64), as_tensor(a.value or 0, total * 8, self.device).view(torch.int64))
+
+    def build_nodes(self, has_emission):
+        h, self._shell = self._shell, None
+        o = self.octree_cls(self.ctx)
+        o._adopt(h)
+        check(self.ctx.lib.hako_octree_build_nodes(h, None, 1, int(bool(has_emission))))
+        return o
+
     def sync(self):
         torch.cuda.synchronize(self.device)
 
@@ -218,7 +233,7 @@ def build_sharded(stages, tris, col, emi, origin, dps, grid, group=None, times=N
     n = keys.numel()
     S = SPLITTER_SAMPLES
     if n:
-        idx = torch.linspace(0, n - 1, S, device=dev).round().long()
+        idx = (torch.arange(S, dtype=torch.int64, device=dev) * (n - 1)) // (S - 1)   # integer arithmetic: float32 cannot index 10^8 pairs
         mine = torch.cat([keys[idx], torch.tensor([n], dtype=torch.int64, device=dev)])
     else:
         mine = torch.zeros(S + 1, dtype=torch.int64, device=dev)
@@ -250,18 +265,34 @@ def build_sharded(stages, tris, col, emi, origin, dps, grid, group=None, times=N
     meta = torch.stack(meta).cpu().numpy()
     offs = np.concatenate([[0], np.cumsum(meta[:, 0])]).astype(np.int64)
     total = int(offs[-1])
-    mortons = torch.empty(total, dtype=torch.int64, device=dev)
-    attrs = torch.empty(total, dtype=torch.int64, device=dev)
+    in_place = hasattr(stages, "alloc_unique")   # LibStages: gather straight into the octree's own arrays
+    if in_place:
+        mortons, attrs = stages.alloc_unique(total, origin, dps, grid)
+    else:
+        mortons = torch.empty(total, dtype=torch.int64, device=dev)
+        attrs = torch.empty(total, dtype=torch.int64, device=dev)
     mortons[offs[rank]:offs[rank + 1]] = rk[:U]
     attrs[offs[rank]:offs[rank + 1]] = rv[:U]
     del rk, rv
-    for r in range(world):
-        if offs[r + 1] > offs[r]:
-            dist.broadcast(mortons[offs[r]:offs[r + 1]], r, group=group)
-            dist.broadcast(attrs[offs[r]:offs[r + 1]], r, group=group)
+    parts_m = [mortons[offs[r]:offs[r + 1]] for r in range(world)]
+    parts_a = [attrs[offs[r]:offs[r + 1]] for r in range(world)]
+    if dist.get_backend(group) == "nccl" and world > 1:
+        # uneven all-gather: torch issues the per-rank broadcasts as one NCCL group, so they share the links
+        dist.all_gather(parts_m, parts_m[rank], group=group)
+        dist.all_gather(parts_a, parts_a[rank], group=group)
+    else:
+        for r in range(world):
+            if offs[r + 1] > offs[r]:
+                dist.broadcast(parts_m[r], r, group=group)
+                dist.broadcast(parts_a[r], r, group=group)
     t = mark("gather_unique_ms", t)
 
-    octree = stages.build_from_unique(mortons, attrs, origin, dps, grid, bool(meta[:, 1].any()))
+    if in_place:
+        stages.sync()
+        del mortons, attrs, parts_m, parts_a
+        octree = stages.build_nodes(bool(meta[:, 1].any()))
+    else:
+        octree = stages.build_from_unique(mortons, attrs, origin, dps, grid, bool(meta[:, 1].any()))
     mark("octree_ms", t)
     if times is not None:
         times["dumped_voxels_this_rank"] = int(n)
