@@ -245,6 +245,39 @@ def run_ours(args):
         dist.barrier()
         if rank == 0:
             build["nccl_broadcast_ms"] = (time.perf_counter() - t0) * 1e3
+        # the alternative to build-on-rank-0 + broadcast: every rank voxelizes / sorts / merges 1/N of the scene, one all-to-all by
+        # Morton range, unique voxels gathered, DAG built on every rank (massivevoxelraytracing_b200/dist.py: build_sharded).
+        # Reported beside the replicated build; the octree used below is the replicated one (they are the same bytes).
+        try:
+            if os.environ.get("HAKO_BENCH_SHARDED", "1") == "0":
+                raise RuntimeError("skipped (HAKO_BENCH_SHARDED=0)")
+            if scene is None:
+                scene = make_scene()            # deterministic generator: every rank derives the same triangles
+            tris, col, emi, origin, dps, _ = scene
+            stages = hdist.LibStages(ctx, hk.IntersectorOctreeGPU)
+            best = None
+            for _ in range(3):
+                times = {}
+                dist.barrier()
+                torch.cuda.synchronize(dev)
+                t0 = time.perf_counter()
+                sh = hdist.build_sharded(stages, tris, col, emi, origin, dps, GRID, times=times)
+                torch.cuda.synchronize(dev)
+                dist.barrier()
+                wall_ms = (time.perf_counter() - t0) * 1e3
+                same = int(sh.info().numberOfNodes == octree.info().numberOfNodes and sh.info().numberOfVoxels == octree.info().numberOfVoxels)
+                sh.cleanUp()
+                if best is None or wall_ms < best[0]:
+                    best = (wall_ms, {k: round(v, 2) for k, v in times.items() if k.endswith("_ms")}, same)
+            ok = torch.tensor([best[2]], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if rank == 0:
+                build["sharded_build"] = {"e2e_ms": best[0], "phases_rank0_ms": best[1], "same_counts_as_replicated_on_every_rank": bool(ok.item()),
+                                          "what": "host triangles in -> identical octree resident on every rank; compare with e2e_host_call_ms + nccl_broadcast_ms"}
+            torch.cuda.empty_cache()
+        except Exception as exc:                # the bench line must survive a failure of this optional leg
+            if rank == 0:
+                build["sharded_build"] = {"error": repr(exc)[:300]}
     info = octree.info()
 
     my_views = rank_views(rank, world)
