@@ -24,6 +24,10 @@ for grid in [int(a) for a in (sys.argv[1:] or ['4096'])]:
         if best is None or wall < best: best = wall; row['phases_ms'] = {k: round(v, 2) for k, v in times.items() if k.endswith('_ms')}; row['range_voxels_this_rank'] = times['range_voxels_this_rank']
         if rep < 2: g.cleanUp()
     row['sharded_build_ms'] = round(best, 2); row['voxels'] = int(info.numberOfVoxels); row['nodes'] = int(info.numberOfNodes)
+    if os.environ.get('HAKO_PROBE_NO_REF') == '1':
+        g.cleanUp()
+        if rank == 0: print(json.dumps(row), flush=True)
+        continue
     # the replicated alternative: rank 0 builds, everybody receives
     best = None
     for rep in range(2):
