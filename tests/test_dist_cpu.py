@@ -91,6 +91,8 @@ class _OracleStages:
         return torch.from_numpy(keys[order].view(np.int64).copy()), torch.from_numpy(vals[order].view(np.int64).copy())
 
     def sort_unique(self, keys, vals, grid):
+        if keys.numel() == 0:
+            return 0, False
         k = keys.numpy().view(np.uint64)
         order = np.argsort(k, kind="stable")
         a = np.ascontiguousarray(vals.numpy()[order]).view(np.uint8).reshape(-1, 8)
@@ -107,7 +109,7 @@ class _OracleStages:
         pass
 
 
-def _shard_worker(rank, world, port, q):
+def _shard_worker(rank, world, port, q, n_tris=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -119,6 +121,8 @@ def _shard_worker(rank, world, port, q):
     tris, col, emi = bunny_scene()
     grid = 64
     origin, dps = scene_params(tris, grid)
+    if n_tris is not None:                       # a mesh with fewer triangles than ranks: some shards are empty
+        tris, col, emi = tris[:n_tris], col[:n_tris], emi[:n_tris]
     times = {}
     mk, at, he = hdist.build_sharded(_OracleStages(o), tris, col, emi, origin, dps, grid, times=times)
     q.put((rank, mk, at, he, times))
@@ -176,3 +180,26 @@ def test_choose_splitters_and_shards():
     s2 = choose_splitters(np.stack([a[0], np.zeros(256, np.int64)]), [1000, 0], 2)
     assert abs((a[0] < s2[0]).mean() - 0.5) < 0.03
     assert choose_splitters(np.zeros((2, 16), np.int64), [0, 0], 2).tolist() == [0]
+
+
+def test_gloo_sharded_build_with_empty_shards(oracle, bunny):
+    """two triangles over three ranks: one shard is empty, and so may be a Morton range"""
+    from scenes import scene_params
+    tris, col, emi = bunny
+    grid = 64
+    origin, dps = scene_params(tris, grid)
+    keys, c, e = oracle.voxelize(tris[:2], col[:2], emi[:2], origin, float(dps), grid)
+    mk, mc, me = oracle.merge_voxels(keys, c, e)
+    world = 3
+    ctxm = mp.get_context("spawn")
+    q = ctxm.Queue()
+    port = 29650 + (os.getpid() % 1000)
+    procs = [ctxm.Process(target=_shard_worker, args=(r, world, port, q, 2)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, gk, ga, he, times in res:
+        assert np.array_equal(gk, mk) and np.array_equal(ga[:, :4], mc) and np.array_equal(ga[:, 4:], me)

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, grid, levels, q):
+def _worker(rank, world, port, grid, levels, q, n_tris=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -25,6 +25,8 @@ def _worker(rank, world, port, grid, levels, q):
     from scenes import bunny_scene, dragon_standin, scene_params
     tris, col, emi = bunny_scene() if levels == 0 else dragon_standin(levels, 0.15)
     origin, dps = scene_params(tris, grid)
+    if n_tris is not None:                       # fewer triangles than ranks: empty shards, possibly empty Morton ranges
+        tris, col, emi = tris[:n_tris], col[:n_tris], emi[:n_tris]
     ctx = hk.Context(rank)
     times = {}
     g = hdist.build_sharded(hdist.LibStages(ctx, hk.IntersectorOctreeGPU), tris, col, emi, origin, dps, grid, times=times)
@@ -72,3 +74,21 @@ def test_sharded_build_equals_single_gpu_build(world, grid, levels):
     if world > 1:
         # ... from a balanced split: no Morton range holds more than twice its share
         assert max(r["times"]["range_voxels_this_rank"] for r in res) < 2.0 * r0["voxels"] / world
+
+
+def test_sharded_build_with_an_empty_shard():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctxm = mp.get_context("spawn")
+    q = ctxm.Queue()
+    port = 29760 + (os.getpid() % 1000)
+    procs = [ctxm.Process(target=_worker, args=(r, 2, port, 256, 0, q, 1)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    r0 = [r for r in res if r["rank"] == 0][0]
+    assert r0["equal"] and r0["voxels"] > 0
+    assert res[0]["n"] == res[1]["n"]
