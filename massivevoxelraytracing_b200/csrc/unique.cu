@@ -24,14 +24,35 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 {
 	const uint32_t tile = scanTakeTicket( st );
 	const uint64_t base = (uint64_t)tile * UQ_TILE + (uint64_t)threadIdx.x * UQ_ITEMS;
-	uint64_t k[UQ_ITEMS];
+	uint64_t k[UQ_ITEMS], v[UQ_ITEMS];
 	uint32_t heads = 0, nHeads = 0;
 	uint64_t prev = ( base > 0 && base <= n ) ? keys[base - 1] : 0ull;
+	// the thread's own values are loaded up front (independent loads); only a run that continues past the thread's last item
+	// is walked through memory
+	if( base + UQ_ITEMS <= n )
+	{
+		// 64 contiguous, 64-byte aligned bytes per thread and array: 16-byte loads halve the L1 requests of the strided pattern
+#pragma unroll
+		for( int i = 0; i < UQ_ITEMS; i += 2 )
+		{
+			const ulonglong2 kk = *reinterpret_cast<const ulonglong2*>( keys + base + i );
+			const ulonglong2 vv = *reinterpret_cast<const ulonglong2*>( values + base + i );
+			k[i] = kk.x, k[i + 1] = kk.y, v[i] = vv.x, v[i + 1] = vv.y;
+		}
+	}
+	else
+	{
+#pragma unroll
+		for( int i = 0; i < UQ_ITEMS; i++ )
+		{
+			k[i] = ( base + i < n ) ? keys[base + i] : 0ull;
+			v[i] = ( base + i < n ) ? values[base + i] : 0ull;
+		}
+	}
 #pragma unroll
 	for( int i = 0; i < UQ_ITEMS; i++ )
 	{
 		const uint64_t idx = base + i;
-		k[i] = ( idx < n ) ? keys[idx] : 0ull;
 		const bool head = ( idx < n ) && ( idx == 0 || k[i] != prev );
 		prev = k[i];
 		if( head )
@@ -51,18 +72,33 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 		if( !( heads & ( 1u << i ) ) ) continue;
 		// walk the run (voxKernel.cu:203-226 does the same serial walk from the first element)
 		uint32_t c[3] = { 0, 0, 0 }, e[3] = { 0, 0, 0 }, cnt = 0;
-		for( uint64_t j = base + i; j < n; j++ )
-		{
-			if( j != base + i && keys[j] != k[i] ) break;
-			const uint64_t v = values[j];
-			c[0] += (uint32_t)( v ) & 0xFFu;
-			c[1] += (uint32_t)( v >> 8 ) & 0xFFu;
-			c[2] += (uint32_t)( v >> 16 ) & 0xFFu;
-			e[0] += (uint32_t)( v >> 32 ) & 0xFFu;
-			e[1] += (uint32_t)( v >> 40 ) & 0xFFu;
-			e[2] += (uint32_t)( v >> 48 ) & 0xFFu;
+		auto add = [&]( const uint64_t x ) {
+			c[0] += (uint32_t)( x ) & 0xFFu;
+			c[1] += (uint32_t)( x >> 8 ) & 0xFFu;
+			c[2] += (uint32_t)( x >> 16 ) & 0xFFu;
+			e[0] += (uint32_t)( x >> 32 ) & 0xFFu;
+			e[1] += (uint32_t)( x >> 40 ) & 0xFFu;
+			e[2] += (uint32_t)( x >> 48 ) & 0xFFu;
 			cnt++;
+		};
+		// the part of the run inside this thread's items: registers
+		bool open = true;
+#pragma unroll
+		for( int j = 0; j < UQ_ITEMS; j++ )
+		{
+			if( j < i || !open ) continue;
+			if( j > i && ( ( heads >> j ) & 1u || base + j >= n ) )
+				open = false;
+			else
+				add( v[j] );
 		}
+		// ... and whatever continues in the items of the following threads (voxKernel.cu:203-226 walks the whole run this way)
+		if( open )
+			for( uint64_t j = base + UQ_ITEMS; j < n; j++ )
+			{
+				if( keys[j] != k[i] ) break;
+				add( values[j] );
+			}
 		const uint32_t er = e[0] / cnt, eg = e[1] / cnt, eb = e[2] / cnt;
 		const uint64_t a = (uint64_t)( c[0] / cnt ) | ( (uint64_t)( c[1] / cnt ) << 8 ) | ( (uint64_t)( c[2] / cnt ) << 16 ) | ( 1ull << 24 ) |
 						   ( (uint64_t)er << 32 ) | ( (uint64_t)eg << 40 ) | ( (uint64_t)eb << 48 ) | ( 1ull << 56 );
