@@ -61,6 +61,7 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 	hako_octree* o = new hako_octree();
 	initOctree( o, ctx, origin, dps, gridRes );
 	uint64_t *keys = nullptr, *values = nullptr, *keysTmp = nullptr, *valuesTmp = nullptr;
+	bool mergeCountersPending = false;
 	int r = 0;
 	do
 	{
@@ -88,24 +89,31 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 			CK( cudaEventRecord( ctx->ev[3], s ) );
 			uint64_t* sk = inTmp ? keysTmp : keys;
 			uint64_t* sv = inTmp ? valuesTmp : values;
-			uint64_t* uk = inTmp ? keys : keysTmp; // unique writes out of place into the idle buffers
-			uint64_t* ua = inTmp ? values : valuesTmp;
-			uint32_t he = 0;
-			if( ( r = uniqueMergeDevice( ctx, s, sk, sv, D, uk, (hako_voxel_attrib*)ua, &U, &he ) ) ) break;
-			o->hasEmission = he;
-			// the sorted input pair is dead: give it back BEFORE the exact-size resident copies are allocated (at billions of
-			// voxels the four D-sized work buffers plus the resident arrays do not fit 180 GB together)
-			dfree( sk, s ), dfree( sv, s );
+			// the idle pair of work buffers goes back first; then the number of runs is counted (one read of the keys) so that
+			// the merge can write straight into the exact-size resident arrays -- no D-sized output pair, no copies
+			dfree( inTmp ? keys : keysTmp, s ), dfree( inTmp ? values : valuesTmp, s );
 			if( inTmp )
-				keysTmp = valuesTmp = nullptr;
-			else
 				keys = values = nullptr;
-			if( ( r = dalloc( ctx, &o->mortons, U, s ) ) ) break;
-			if( ( r = dalloc( ctx, &o->attrs, U, s ) ) ) break;
-			CK( cudaMemcpyAsync( o->mortons, uk, U * 8, cudaMemcpyDeviceToDevice, s ) );
-			CK( cudaMemcpyAsync( o->attrs, ua, U * 8, cudaMemcpyDeviceToDevice, s ) );
-			// ... and the unique output pair before the octree build sizes its node pool
-			dfree( uk, s ), dfree( ua, s );
+			else
+				keysTmp = valuesTmp = nullptr;
+			uint64_t runs = 0;
+			if( ( r = countRunsDevice( ctx, s, sk, D, &runs ) ) ) break;
+			if( ( r = dalloc( ctx, &o->mortons, runs, s ) ) ) break;
+			if( ( r = dalloc( ctx, &o->attrs, runs, s ) ) ) break;
+			// the merge's own counters (U again, hasEmission) are read with the end-of-build synchronisation: no host wait here  (pinned slots 32 / 33: the octree stage uses 0..21)
+			unsigned long long* uc = nullptr;
+			if( ( r = dalloc( ctx, &uc, 2, s ) ) ) break;
+			r = uniqueMergeLaunch( ctx, s, sk, sv, D, o->mortons, o->attrs, uc );
+			if( r == 0 )
+			{
+				e = cudaMemcpyAsync( ctx->pinned + 32, uc, 16, cudaMemcpyDeviceToHost, s );
+				if( e != cudaSuccess ) r = cudaFail( e, "D2H unique counters", __FILE__, __LINE__ );
+			}
+			dfree( uc, s );
+			if( r ) break;
+			U = runs;
+			mergeCountersPending = true;
+			dfree( sk, s ), dfree( sv, s );
 			keys = values = keysTmp = valuesTmp = nullptr;
 		}
 		else
@@ -126,6 +134,16 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 		CK( cudaEventRecord( ctx->ev[5], s ) );
 		CK( cudaStreamSynchronize( s ) );
 		st.hostSyncs++;
+		if( mergeCountersPending )
+		{
+			if( ctx->pinned[32] != U )
+			{
+				setError( "build: unique produced %llu voxels, %llu runs were counted", (unsigned long long)ctx->pinned[32], (unsigned long long)U );
+				r = HAKO_E_STATE;
+				break;
+			}
+			o->hasEmission = ctx->pinned[33] ? 1u : 0u;
+		}
 		cudaEventElapsedTime( &st.ms_voxelize, ctx->ev[1], ctx->ev[2] );
 		cudaEventElapsedTime( &st.ms_sort, ctx->ev[2], ctx->ev[3] );
 		cudaEventElapsedTime( &st.ms_unique, ctx->ev[3], ctx->ev[4] );

@@ -136,6 +136,9 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* values, uint64_t* keysTmp, uint64_t* valuesTmp,
 					 uint64_t n, int beginBit, int endBit, int* resultInTmp );
 // unique.cu
+int uniqueMergeLaunch( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
+					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, unsigned long long* counters_d ); // stream-ordered, no host wait
+int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64_t n, uint64_t* U ); // distinct keys of a sorted array (synchronises)
 int uniqueMergeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
 					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, uint64_t* U, uint32_t* hasEmission );
 // octree.cu

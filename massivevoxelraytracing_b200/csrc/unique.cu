@@ -6,6 +6,8 @@
 // The reference compacts in place through StreamCompaction::filter, whose blocks wait for each other in index order
 // (StreamCompaction.hpp:121-138,186-196).  Here: one fused kernel, out of place -- head flags, block scan, decoupled
 // look-back for the tile prefix, and the head thread of each run walks its run and writes the merged voxel.
+#include <algorithm>
+
 #include "internal.cuh"
 #include "scan.cuh"
 
@@ -112,7 +114,39 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 	if( tile == gridDim.x - 1 && threadIdx.x == 0 ) counters[0] = prefix + total;
 }
 
-// keysOut / attrsOut must hold n entries.  counters_d: 2 x u64 (U, hasEmission), written stream-ordered.
+// number of distinct keys of a sorted array (one read of the keys): lets the caller allocate the exact-size outputs of the merge
+__global__ void __launch_bounds__( 256 ) countRunsKernel( const uint64_t* __restrict__ keys, uint64_t n, unsigned long long* __restrict__ count )
+{
+	uint32_t mine = 0;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for( uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride ) mine += ( i == 0 || keys[i] != keys[i - 1] ) ? 1u : 0u;
+	for( int o = 16; o; o >>= 1 ) mine += __shfl_down_sync( 0xFFFFFFFFu, mine, o );
+	if( ( threadIdx.x & 31u ) == 0 && mine ) atomicAdd( count, (unsigned long long)mine );
+}
+int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64_t n, uint64_t* U )
+{
+	*U = 0;
+	if( n == 0 ) return 0;
+	unsigned long long* counter = nullptr;
+	HAKO_TRY( dalloc( ctx, &counter, 1, s ) );
+	cudaError_t e = cudaMemsetAsync( counter, 0, 8, s );
+	if( e == cudaSuccess )
+	{
+		const uint32_t blocks = (uint32_t)std::min<uint64_t>( (uint64_t)ctx->smCount * 8, ( n + 255 ) / 256 );
+		countRunsKernel<<<blocks, 256, 0, s>>>( keys, n, counter );
+		ctx->launches.fetch_add( 1, std::memory_order_relaxed );
+		e = cudaGetLastError();
+	}
+	if( e == cudaSuccess ) e = cudaMemcpyAsync( ctx->pinned, counter, 8, cudaMemcpyDeviceToHost, s );
+	if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
+	ctx->stats.hostSyncs++;
+	dfree( counter, s );
+	if( e != cudaSuccess ) return cudaFail( e, "countRunsDevice", __FILE__, __LINE__ );
+	*U = ctx->pinned[0];
+	return 0;
+}
+
+// keysOut / attrsOut must hold n entries (or exactly the number of runs).  counters_d: 2 x u64 (U, hasEmission), written stream-ordered.
 int uniqueMergeLaunch( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
 					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, unsigned long long* counters_d )
 {
