@@ -88,6 +88,13 @@ public:
 	{
 		hako::check( hako_render_primary( m_octree, stream, &camera, width, height, 0, height, showVertexColor ? 1 : 0, rgba, t, nMajor, vIndex ) );
 	}
+	// a run of frames, the orbit loop of voxRTGPU.cpp:150-208: frame i+1 is traced while frame i is copied out.  Outputs are
+	// nViews x height x width (HOST), frame-major; any may be null.
+	void renderFrames( hako_stream stream, const hako_camera* cameras, int nViews, int width, int height, bool showVertexColor, uint8_t* rgba,
+					   uint32_t* vIndex = nullptr, float* t = nullptr, int* nMajor = nullptr ) const
+	{
+		hako::check( hako_render_primary_views( m_octree, stream, cameras, nViews, width, height, showVertexColor ? 1 : 0, rgba, t, nMajor, vIndex ) );
+	}
 	// canonical reference layout for parity / tooling: OctreeNode[ ] (68 B), sorted unique Morton keys, VoxelAttirb[ ]
 	void download( std::vector<hako_node68>* nodes, std::vector<uint64_t>* mortons = nullptr, std::vector<hako_voxel_attrib>* attrs = nullptr, hako_stream stream = nullptr ) const
 	{

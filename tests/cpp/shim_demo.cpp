@@ -62,6 +62,28 @@ int main( int argc, char** argv )
 		for( uint32_t id : ids ) hits += id != 0xFFFFFFFFu;
 		printf( "voxels %u nodes %u hits %zu hasEmission %d\n", intersector.m_numberOfVoxels, intersector.m_numberOfNodes, hits, (int)intersector.hasEmission() );
 
+		// ---- a run of frames in one call (pipelined trace / download): frame 0 must equal the single-frame call ----
+		{
+			const int nViews = 5;
+			std::vector<hako_camera> cams( nViews );
+			for( int k = 0; k < nViews; k++ )
+			{
+				const float e[3] = { 4.0f - 0.5f * k, 4.0f, 4.0f + 0.5f * k };
+				hako::check( hako_camera_lookat( e, center, up, 45.0f * 3.14159265f / 180.0f, W, H, 0.01f, 1000.0f, 6.0f, 0.02f, &cams[k] ) );
+			}
+			std::vector<uint8_t> frames( (size_t)nViews * W * H * 4 );
+			std::vector<uint32_t> frameIds( (size_t)nViews * W * H );
+			intersector.renderFrames( nullptr, cams.data(), nViews, W, H, true, frames.data(), frameIds.data() );
+			if( memcmp( frames.data(), image.data(), image.size() ) != 0 || memcmp( frameIds.data(), ids.data(), ids.size() * 4 ) != 0 )
+			{
+				printf( "renderFrames: frame 0 differs from render()\n" );
+				return 3;
+			}
+			size_t h4 = 0;
+			for( size_t i = (size_t)4 * W * H; i < (size_t)5 * W * H; i++ ) h4 += frameIds[i] != 0xFFFFFFFFu;
+			printf( "frames %d, hits in frame 4: %zu\n", nViews, h4 );
+		}
+
 		// ---- IntersectorOctree (CPU class surface): rebuild from the sorted unique Morton list, cast one ray ----
 		std::vector<uint64_t> mortons;
 		std::vector<hako_node68> nodes;
