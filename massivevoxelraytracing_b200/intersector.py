@@ -173,8 +173,10 @@ class _OctreeBase:
         assert nodes68.dtype.itemsize == 68
         attrs = None if attrs is None else np.ascontiguousarray(attrs)
         h = C.c_void_p()
+        lo, up = _f32(lower), _f32(upper)  # named: a temporary would be freed (and its slot reused) before the call runs
+        assert lo.size == 3 and up.size == 3
         check(self.lib.hako_octree_import(self.ctx.h, _stream(stream), _ptr(nodes68), nodes68.size, _ptr(attrs),
-                                          0 if attrs is None else attrs.shape[0], _ptr(_f32(lower)), _ptr(_f32(upper)), float(dps), C.byref(h)))
+                                          0 if attrs is None else attrs.shape[0], _ptr(lo), _ptr(up), float(dps), C.byref(h)))
         self._adopt(h)
         return self
 
@@ -242,7 +244,9 @@ class IntersectorOctreeGPU(_OctreeBase):
         emi = _f32(vemissions).reshape(-1)
         assert pos.size % 9 == 0 and col.size == pos.size and emi.size == pos.size
         h = C.c_void_p()
-        check(self.lib.hako_octree_build(self.ctx.h, _stream(stream), _ptr(pos), _ptr(col), _ptr(emi), pos.size // 9, _ptr(_f32(origin)), float(dps),
+        org = _f32(origin)
+        assert org.size == 3
+        check(self.lib.hako_octree_build(self.ctx.h, _stream(stream), _ptr(pos), _ptr(col), _ptr(emi), pos.size // 9, _ptr(org), float(dps),
                                          int(gridRes), C.byref(h)))
         self._adopt(h)
         return self
@@ -250,8 +254,10 @@ class IntersectorOctreeGPU(_OctreeBase):
     def build_device(self, vertices, vcolors, vemissions, stream=None, origin=(0, 0, 0), dps=1.0, gridRes=256):
         """same with torch CUDA float32 tensors already resident in HBM (no H2D inside)"""
         h = C.c_void_p()
+        org = _f32(origin)
+        assert org.size == 3
         check(self.lib.hako_octree_build_device(self.ctx.h, _stream(stream), _ptr(vertices), _ptr(vcolors), _ptr(vemissions), vertices.numel() // 9,
-                                                _ptr(_f32(origin)), float(dps), int(gridRes), C.byref(h)))
+                                                _ptr(org), float(dps), int(gridRes), C.byref(h)))
         self._adopt(h)
         return self
 
@@ -263,7 +269,9 @@ class IntersectorOctree(_OctreeBase):
         m = np.ascontiguousarray(mortonVoxels, np.uint64)
         attrs = None if attrs is None else np.ascontiguousarray(attrs)
         h = C.c_void_p()
-        check(self.lib.hako_octree_build_from_morton(self.ctx.h, _stream(stream), _ptr(m), _ptr(attrs), m.size, _ptr(_f32(origin)), float(dps), int(gridRes),
+        org = _f32(origin)
+        assert org.size == 3
+        check(self.lib.hako_octree_build_from_morton(self.ctx.h, _stream(stream), _ptr(m), _ptr(attrs), m.size, _ptr(org), float(dps), int(gridRes),
                                                      int(dag), C.byref(h)))
         self._adopt(h)
         return self
