@@ -34,7 +34,12 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 GRID = 4096
 W, H = 1920, 1080
-VIEWS = 16
+VIEWS = 384              # full frames per step per GPU: 796 M rays = ~50 ms of GPU work, so 20 timed steps are ~1 s
+RING = 16                # device output sets kept per GPU (16 x 24.9 MB = 398 MB > the 126 MB L2); view i writes set i % RING
+CHUNK = 64               # views per hako_render_primary_views call of the e2e leg (64 pinned RGBA frames = 531 MB)
+REF_BANDS = 16           # the CPU arm casts row band (k % 16) of view k: 1/16 of the rays of a step, a bounded sample of every view
+STRONG_VIEWS = 128       # strong-scaling block: this many views in TOTAL, split over the ranks
+STRONG_SPP_STEPS = 32    # strong-scaling block: one 512-spp 1080p frame (32 PathTracer steps) in TOTAL, split over the ranks
 MESH_LEVELS = 5          # bunny x 4^5 = 5.23 M triangles (the dragon blob is missing: SURVEY.md 8d)
 
 
@@ -96,16 +101,17 @@ def load_oracle():
 
 
 def cpu_tree(port, ref, tris, col, emi, origin, dps):
-    """reference CPU pipeline (voxRT.cpp:198-270): voxelize -> mergeVoxels -> buildDAGReference, timed per stage"""
-    t = {}
+    """reference CPU pipeline (voxRT.cpp:198-270): voxelize -> mergeVoxels -> buildDAGReference, timed per stage.  Every stage runs
+    the reference's own code (oracle/_ref) when it travelled with the snapshot, else the port; `kind` says which."""
+    o = ref if ref is not None else port
+    t = {"kind": "reference" if ref is not None else "port"}
     t0 = time.time()
-    keys, c, e = port.voxelize(tris, col, emi, origin, dps, GRID)
+    keys, c, e = o.voxelize(tris, col, emi, origin, dps, GRID)
     t["voxelize_ms"] = (time.time() - t0) * 1e3
     t0 = time.time()
-    mk, mc, me = port.merge_voxels(keys, c, e)
+    mk, mc, me = o.merge_voxels(keys, c, e)
     t["sort_unique_ms"] = (time.time() - t0) * 1e3
     del keys, c, e
-    o = ref if ref is not None else port
     t0 = time.time()
     tree = o.build_octree(mk, origin, dps, GRID)
     t["octree_ms"] = (time.time() - t0) * 1e3
@@ -114,7 +120,7 @@ def cpu_tree(port, ref, tris, col, emi, origin, dps):
 
 
 def cpu_cast(o, tree, views_total, view_ids, threads, bands, stats=None):
-    """cast row band k of view k (bands=True: 1/VIEWS of each view) or whole views; returns rays, seconds.
+    """cast row band (k % REF_BANDS) of view k (bands=True: 1/16 of each view) or whole views; returns rays, seconds.
     Output buffers are allocated once, outside the timed calls."""
     import ctypes as C
     from oracle.orc import FLT_MAX
@@ -127,8 +133,8 @@ def cpu_cast(o, tree, views_total, view_ids, threads, bands, stats=None):
     for i, k in enumerate(view_ids):
         cam = o.camera_lookat(view_eye(k, views_total), (0, 0, 0), (0, 1, 0), None, W, H)
         if bands:
-            j = i % VIEWS
-            y0, y1 = (H * j) // VIEWS, (H * (j + 1)) // VIEWS
+            j = i % REF_BANDS
+            y0, y1 = (H * j) // REF_BANDS, (H * (j + 1)) // REF_BANDS
         else:
             y0, y1 = 0, H
         t0 = time.time()
@@ -163,6 +169,8 @@ def base_config(n_gpus):
                         "missing from the reference checkout) voxelized at %d^3, %dx%d pixel-centre primary rays, %d orbit views per step per GPU"
                         % (MESH_LEVELS, 5110 * 4 ** MESH_LEVELS, GRID, W, H, VIEWS),
             "grid": GRID, "image": [W, H], "views_per_step_per_gpu": VIEWS,
+            "reference_arm_sample": "--impl reference casts row band (k mod %d) of view k for the same %d views: 1/%d of the rays of a step (a rate, so the ratio stands)" % (REF_BANDS, VIEWS, REF_BANDS),
+            "l2": "the outputs of a step cycle through %d sets of 24.9 MB (%.0f MB > the 126 MB L2); the octree is L2-resident by design; no explicit flush" % (RING, RING * 24.9),
             "parallelism": "octree built on rank 0 + NCCL broadcast; views dealt round-robin over %d GPU(s) (every rank spans the whole orbit), no data-path collective" % n_gpus,
             "streams": "the frames of a step alternate between CUDA streams (4 per GPU unless HAKO_BENCH_STREAMS says otherwise; tail of frame i overlaps the head of frame i+1); "
                        "timed with events on the stream that forks and joins them"}
@@ -188,7 +196,8 @@ def run_reference(args):
         rays += r
         secs += s
     value = rays / secs / 1e6
-    sample = "row band k of view k for the %d views of a step (%d rays per step), %d host threads over image rows" % (VIEWS, rays // max(args.steps, 1), threads)
+    sample = "row band (k mod %d) of view k for the %d views of a step (%d rays per step = 1/%d of the step), %d host threads over image rows" % (
+        REF_BANDS, VIEWS, rays // max(args.steps, 1), REF_BANDS, threads)
     line = {"impl": "reference", "metric": "Mrays/s (octree traversal, primary rays)", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(args.steps, 1) * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": base_config(args.gpus),
@@ -436,7 +445,7 @@ def run_ours(args):
         dbar = float(stats[1]) / rs
         cpu = {"value": rays_c / secs_c / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference" if ref is not None else "port",
                "sample": "row band k of view k for the %d views of a step (%d rays), repeated %d times; %d host threads over image rows" % (VIEWS, rs, reps, threads),
-               "single_thread_mrays": r1 / s1 / 1e6, "cpu": cpu_model(), "build_ms": {k: round(v, 1) for k, v in cpu_build.items()},
+               "single_thread_mrays": r1 / s1 / 1e6, "cpu": cpu_model(), "build_ms": {k: (round(v, 1) if isinstance(v, float) else v) for k, v in cpu_build.items()},
                "traversal_stats_per_ray": {"loop_visits": float(stats[0]) / rs, "descents": dbar, "pushes": float(stats[2]) / rs, "max_stack": int(stats[3])}}
         # parity spot check: view 0 complete, GPU (device buffers of the last step) vs the CPU reference
         cam0 = o.camera_lookat(view_eye(0, views_total), (0, 0, 0), (0, 1, 0), None, W, H)
@@ -474,8 +483,6 @@ def run_ours(args):
         roofline["issue_bound"] = {"warp_instructions_per_launch": winst, "schedulers": sm_count * 4, "sm_mhz": mhz, "floor_ms_per_launch": floor_ms,
                                    "frac": floor_ms / launch_ms, "source": "instruction count from the ncu capture named in roofline.ncu.source"}
     cfg = base_config(world)
-    cfg["l2"] = "outputs of a step (%.0f MB) exceed the 126 MB L2; the octree (%.0f MB) is L2-resident by design; no explicit flush" % (
-        VIEWS * nrays_view * 12 / 1e6, info.numberOfNodes * 65 / 1e6)
     line = {"metric": "Mrays/s (octree traversal, primary rays)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": cfg, "clocks": sampler.summary(),

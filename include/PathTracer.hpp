@@ -3,23 +3,37 @@
 // updateScene / step / resolve / toImageAsync / getSteps / getNumberOfVoxels / getOctreeBytes, in the call order of
 // voxPTGPU.cpp:88-91,169,177-193 and RTCamp.cpp:111-123,147-169.
 //
-// Differences a caller sees
-//   - setup() takes no kernel path / include dir / isNvidia flag (no nvrtc), and allocates no 1 GiB stack pool;
-//   - loadHDRI( stream, file, filePrimary ) as in the reference (Radiance .hdr, decoded by hako_image_load_hdr exactly as
-//     stbi_loadf( .., 4 ) does, libs/prlib/src/prp.cpp:353-366), plus an overload taking decoded RGBA32F pixels;
-//   - step() takes the pinhole camera directly (hako_camera == CameraPinhole).  A pr::Camera3D caller builds it with
-//     hako_camera_lookat( origin, lookat, up, fovy, width, height, zNear, zFar, focus, lensR ), which is
-//     pr::GetCameraMatrix + CameraPinhole::initFromPerspective (PathTracer.hpp:152-156);
-//   - toImageAsync() fills a caller buffer (width * height * 4 bytes) instead of a pr::Image2DRGBA8 and returns after
-//     the copy has landed;
+// Every method keeps the reference's argument list, so voxPTGPU.cpp:88-91,177-193 compiles with only the include swapped:
+//   - PathTracer() default-constructs (device 0, or $HAKO_DEVICE) as the reference's does; PathTracer( hako::Context* ) shares a context;
+//   - setup( stream, kernel, includeDir, isNvidia ) (:43): the three nvrtc arguments are accepted and ignored (ahead-of-time sm_100a
+//     code, no 1 GiB stack pool); setup( stream ) is the short form;
+//   - loadHDRI( stream, file, filePrimary ) (:104): Radiance .hdr decoded by hako_image_load_hdr exactly as stbi_loadf( .., 4 )
+//     (libs/prlib/src/prp.cpp:353-366); an overload takes decoded RGBA32F pixels;
+//   - step( stream, camera, focus, lensR ) (:150): `camera` is any pr::Camera3D-like struct (origin, lookat, up, fovy, zNear, zFar;
+//     libs/prlib/src/pr.hpp:189-198) and goes through hako_camera_lookat == pr::GetCameraMatrix + CameraPinhole::initFromPerspective
+//     (:152-156); step( stream, hako_camera ) takes the pinhole directly;
+//   - toImageAsync( stream, image* ) (:118): `image` is any pr::Image2DRGBA8-like object (allocate( w, h ), data()); resolve and
+//     the D2H copy are ENQUEUED, the caller synchronises the stream as voxPTGPU.cpp:188-189 does; toImage( stream, uint8_t* ) waits;
 //   - m_maxDepth is a member (reference: the literal 8 at voxKernel.cu:691; BASELINE config 3 uses 4).
 #pragma once
+
+#include <cstdlib>
+#include <memory>
 
 #include "IntersectorOctreeGPU.hpp"
 
 class PathTracer
 {
+	static hako::Context* ownContext( std::unique_ptr<hako::Context>& slot )
+	{
+		const char* dev = getenv( "HAKO_DEVICE" );
+		slot.reset( new hako::Context( dev ? atoi( dev ) : 0 ) );
+		return slot.get();
+	}
+	std::unique_ptr<hako::Context> m_ownCtx; // declared first: it must outlive every member that uses it
+
 public:
+	PathTracer() : m_ctx( ownContext( m_ownCtx ) ), m_intersectorOctreeGPU( m_ctx ) {} // `PathTracer pt;`, voxPTGPU.cpp:88
 	explicit PathTracer( hako::Context* ctx ) : m_ctx( ctx ), m_intersectorOctreeGPU( ctx ) {}
 	~PathTracer() { cleanUp(); }
 	PathTracer( const PathTracer& ) = delete;
@@ -34,6 +48,8 @@ public:
 		cleanUp();
 		hako::check( hako_pt_create( m_ctx->get(), stream, &m_pt ) );
 	}
+	// the reference's argument list (:43): kernel source path, include directory and vendor flag fed nvrtc; nothing to compile here
+	void setup( hako_stream stream, const char* /*kernel*/, const char* /*includeDir*/, bool /*isNvidia*/ ) { setup( stream ); }
 	void cleanUp() // :70-79
 	{
 		m_intersectorOctreeGPU.cleanUp();
@@ -87,13 +103,34 @@ public:
 	{
 		hako::check( hako_pt_step( m_pt, m_intersectorOctreeGPU.handle(), stream, &pinhole, m_steps++, 0, m_height, m_maxDepth ) );
 	}
+	// the reference's argument list (:150): a pr::Camera3D-like camera -> view / projection matrices -> CameraPinhole (:152-156)
+	template <class Camera3D>
+	void step( hako_stream stream, const Camera3D& camera, float focus, float lensR )
+	{
+		const float eye[3] = { camera.origin.x, camera.origin.y, camera.origin.z };
+		const float center[3] = { camera.lookat.x, camera.lookat.y, camera.lookat.z };
+		const float up[3] = { camera.up.x, camera.up.y, camera.up.z };
+		hako_camera pinhole;
+		hako::check( hako_camera_lookat( eye, center, up, camera.fovy, m_width, m_height, camera.zNear, camera.zFar, focus, lensR, &pinhole ) );
+		step( stream, pinhole );
+	}
 	// tile / spp sharding across GPUs: rows [y0, y1) of iteration `iteration` (spp = iteration*16 + localSpp, voxKernel.cu:642)
 	void stepTile( hako_stream stream, const hako_camera& pinhole, int iteration, int y0, int y1 )
 	{
 		hako::check( hako_pt_step( m_pt, m_intersectorOctreeGPU.handle(), stream, &pinhole, iteration, y0, y1, m_maxDepth ) );
 	}
 	void resolve( hako_stream stream ) { hako::check( hako_pt_resolve( m_pt, stream ) ); } // :118-127
-	void toImageAsync( hako_stream stream, uint8_t* rgba ) { hako::check( hako_pt_read_rgba8( m_pt, stream, rgba ) ); } // :128-137
+	// :118-129 with the reference's argument list: output->allocate( w, h ), resolve, D2H ENQUEUED into output->data(); the caller
+	// synchronises the stream before reading the image (voxPTGPU.cpp:188-189)
+	template <class Image2DRGBA8>
+	void toImageAsync( hako_stream stream, Image2DRGBA8* output )
+	{
+		output->allocate( m_width, m_height );
+		static_assert( sizeof( *output->data() ) == 4, "image pixels must be 4 bytes (glm::u8vec4)" );
+		hako::check( hako_pt_read_rgba8_async( m_pt, stream, (uint8_t*)output->data() ) );
+	}
+	void toImageAsync( hako_stream stream, uint8_t* rgba ) { hako::check( hako_pt_read_rgba8_async( m_pt, stream, rgba ) ); }
+	void toImage( hako_stream stream, uint8_t* rgba ) { hako::check( hako_pt_read_rgba8( m_pt, stream, rgba ) ); } // returns after the copy has landed
 	void readAccumulators( hako_stream stream, float* rgbw ) { hako::check( hako_pt_read_accum( m_pt, stream, rgbw ) ); }
 
 	hako::Context* m_ctx;

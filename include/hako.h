@@ -41,6 +41,7 @@ typedef struct hako_pt hako_pt;
 typedef struct hako_pairs hako_pairs; /* sorted dumped voxels of one triangle shard, resident on the device */
 typedef struct hako_mesh hako_mesh;
 typedef struct hako_seq hako_seq;
+typedef struct hako_dist hako_dist; /* one NCCL communicator rank bound to a hako_ctx */
 typedef void* hako_stream; /* cudaStream_t */
 
 /* == OctreeNode, voxCommon.hpp:133-138 (68 bytes, align 4).  children[i] = index | mask<<24 after embedMasks
@@ -117,6 +118,9 @@ int hako_ctx_synchronize( hako_ctx* ctx, hako_stream stream );
 int hako_ctx_build_stats( const hako_ctx* ctx, hako_build_stats* out );
 /* number of kernel launches issued through this context since creation (bench.py's gpu_launches claim) */
 uint64_t hako_ctx_launch_count( const hako_ctx* ctx );
+/* measurement: the L2 read roof of the device (traversal is served by L2 while the node array fits it).  Sweeps a
+ * buffer of setBytes (0 = a quarter of the L2) `reps` times; *l2Bytes = cudaDevAttrL2CacheSize, *readGBs = best of three. */
+int hako_ctx_l2_probe( hako_ctx* ctx, hako_stream stream, uint64_t setBytes, int reps, uint64_t* l2Bytes, float* readGBs );
 
 /* ---- build: IntersectorOctreeGPU::build, IntersectorOctreeGPU.hpp:40-241 ----
  * pos/col/emi: 9 floats per triangle (v0,v1,v2), as trianglesFlattened (voxUtil.hpp:8-65) produces.
@@ -225,6 +229,7 @@ int hako_pt_load_hdri( hako_pt* pt, hako_stream stream, const float* rgba, int w
 int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const hako_camera* cam, int iteration, int y0, int y1, int maxDepth );
 int hako_pt_resolve( hako_pt* pt, hako_stream stream );										/* resolve, :118-127 */
 int hako_pt_read_rgba8( hako_pt* pt, hako_stream stream, uint8_t* rgba );					/* toImageAsync, :128-137 (HOST) */
+int hako_pt_read_rgba8_async( hako_pt* pt, hako_stream stream, uint8_t* rgba );			/* the same without the host wait: the caller synchronises the stream (voxPTGPU.cpp:188-189) */
 int hako_pt_read_accum( hako_pt* pt, hako_stream stream, float* rgbw );						/* float4 accumulators (HOST) */
 int hako_pt_accum_device( hako_pt* pt, void** accum_d, uint64_t* bytes );					/* for ncclReduce by the host layer */
 int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, int reset ); /* traversal calls since reset */
@@ -264,6 +269,35 @@ int hako_seq_render_frame( hako_seq* q, const float* pos, const float* col, cons
 						   int gridRes, const hako_camera* cam, int iterations, int maxDepth, const char* pngPath, float* updateMs, float* renderMs );
 int hako_seq_wait( hako_seq* q ); /* taskGroup.waitForAllElementsToFinish, RTCamp.cpp:196 */
 void hako_seq_destroy( hako_seq* q );
+
+/* ---- multi-GPU: one hako_ctx per GPU, NCCL over NVLink / NVSwitch.  No counterpart in the reference (its only
+ * distribution is usecase2_submission/run.py:13-27).  A C++ host written like voxPTGPU.cpp:88-193 / RTCamp.cpp:138-196 drives it
+ * with one process per GPU under any launcher, or one thread per GPU in one process; libnccl.so.2 is loaded at hako_dist_init.
+ *   rank 0:  hako_dist_unique_id( id )  -> ship the 128 bytes to the other ranks  -> every rank: hako_dist_init( ctx, id, rank, world )
+ *   octree:  build on one rank, hako_dist_broadcast_octree          (or hako_dist_build_sharded: every rank builds 1/G of it)
+ *   primary rays: rows / views per rank, no collective (hako_render_primary's y0, y1)
+ *   path tracing: rank r runs hako_pt_step for iterations r, r + G, ... then ONE hako_dist_reduce_accum; resolve on the root. */
+#define HAKO_DIST_ID_BYTES 128
+int hako_dist_unique_id( uint8_t id[HAKO_DIST_ID_BYTES] ); /* ncclGetUniqueId */
+int hako_dist_init( hako_ctx* ctx, const uint8_t id[HAKO_DIST_ID_BYTES], int rank, int world, hako_dist** out ); /* collective; warms the connections up */
+void hako_dist_destroy( hako_dist* d );
+int hako_dist_info( const hako_dist* d, int* rank, int* world, int* ncclVersion );
+int hako_dist_barrier( hako_dist* d, hako_stream stream );					 /* returns when every rank's stream has reached it */
+int hako_dist_max_f32( hako_dist* d, hako_stream stream, float* value );	 /* max over ranks of a host float (device-timed ms) */
+/* Replicate rank root's octree (IntersectorOctreeGPU's two device buffers, IntersectorOctreeGPU.hpp:265-266, + the mask side array).
+ * src: the octree on root, ignored elsewhere.  *out: src on root, elsewhere a new replica (hako_octree_destroy it).  A 64-byte
+ * header broadcast and one host wait size the receivers' arrays; nodes + masks + attributes then travel as ONE NCCL group on
+ * `stream` and the call returns with it enqueued. */
+int hako_dist_broadcast_octree( hako_dist* d, hako_stream stream, int root, hako_octree* src, hako_octree** out );
+/* ncclReduce( sum ) of the float4 accumulators of pt (PathTracer::m_frameBufferF32, PathTracer.hpp:24) onto root, in place. */
+int hako_dist_reduce_accum( hako_dist* d, hako_stream stream, hako_pt* pt, int root );
+int hako_dist_reduce_f32( hako_dist* d, hako_stream stream, float* buf_d, uint64_t count, int root ); /* any DEVICE float buffer */
+int hako_dist_broadcast_bytes( hako_dist* d, hako_stream stream, void* buf_d, uint64_t bytes, int root );
+/* IntersectorOctreeGPU::build (IntersectorOctreeGPU.hpp:40-241) sharded over the ranks: pos / col / emi = THIS rank's triangles
+ * (HOST, scene frame).  Every rank ends with the octree of the whole scene, byte-identical to hako_octree_build on one GPU.
+ * timesMs: NULL or 6 floats (voxelize+sort, splitters, all-to-all, sort+unique, gather, nodes; host clock, synchronised). */
+int hako_dist_build_sharded( hako_dist* d, hako_stream stream, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
+							 const float origin[3], float dps, int gridRes, hako_octree** out, float* timesMs );
 
 /* ---- debug export: saveVoxelsAsMesh, voxMesh.cpp:111-219 ----
  * binary little-endian PLY: 8 corners per voxel, one quad per face without a neighbouring voxel.  HOST pointers. */

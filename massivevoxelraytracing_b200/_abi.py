@@ -60,6 +60,7 @@ SIGNATURES = {
     "hako_ctx_synchronize": (i32, [vp, vp]),
     "hako_ctx_build_stats": (i32, [vp, C.POINTER(BuildStats)]),
     "hako_ctx_launch_count": (u64, [vp]),
+    "hako_ctx_l2_probe": (i32, [vp, vp, u64, i32, pu64, C.POINTER(C.c_float)]),
     "hako_octree_build": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, pp]),
     "hako_octree_build_device": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, pp]),
     "hako_octree_build_from_morton": (i32, [vp, vp, vp, vp, u64, vp, f32, i32, i32, pp]),
@@ -95,6 +96,7 @@ SIGNATURES = {
     "hako_pt_step": (i32, [vp, vp, vp, C.POINTER(Camera), i32, i32, i32, i32]),
     "hako_pt_resolve": (i32, [vp, vp]),
     "hako_pt_read_rgba8": (i32, [vp, vp, vp]),
+    "hako_pt_read_rgba8_async": (i32, [vp, vp, vp]),
     "hako_pt_read_accum": (i32, [vp, vp, vp]),
     "hako_pt_accum_device": (i32, [vp, pp, pu64]),
     "hako_pt_ray_count": (i32, [vp, vp, pu64, i32]),
@@ -116,6 +118,17 @@ SIGNATURES = {
     "hako_seq_wait": (i32, [vp]),
     "hako_seq_destroy": (None, [vp]),
     "hako_voxel_mesh_save_ply": (i32, [C.c_char_p, vp, u64, vp, f32]),
+    "hako_dist_unique_id": (i32, [vp]),
+    "hako_dist_init": (i32, [vp, vp, i32, i32, pp]),
+    "hako_dist_destroy": (None, [vp]),
+    "hako_dist_info": (i32, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "hako_dist_barrier": (i32, [vp, vp]),
+    "hako_dist_max_f32": (i32, [vp, vp, C.POINTER(C.c_float)]),
+    "hako_dist_broadcast_octree": (i32, [vp, vp, i32, vp, pp]),
+    "hako_dist_reduce_accum": (i32, [vp, vp, vp, i32]),
+    "hako_dist_reduce_f32": (i32, [vp, vp, vp, u64, i32]),
+    "hako_dist_broadcast_bytes": (i32, [vp, vp, vp, u64, i32]),
+    "hako_dist_build_sharded": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, pp, C.POINTER(C.c_float)]),
 }
 
 _lib = None

@@ -1,6 +1,7 @@
 // context.cu -- hako_ctx: device selection, the stream-ordered memory pool, error strings, launch accounting.
 // Replaces oroInitialize / oroCtxCreate / the nvrtc `Shader` compile (voxRTGPU.cpp:25-68, hipUtil.hpp:112-157):
 // the kernels are compiled ahead of time for sm_100a, so creating a context is only "pick the device".
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -23,6 +24,26 @@ int cudaFail( cudaError_t e, const char* what, const char* file, int line )
 	const char* base = strrchr( file, '/' );
 	setError( "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString( e ), base ? base + 1 : file, line, what );
 	return HAKO_E_CUDA;
+}
+} // namespace hako
+
+namespace hako
+{
+// resident-set read sweep: every thread streams 16-byte words of a buffer that fits L2, bypassing L1 (ld.global.cg)
+__global__ void __launch_bounds__( 256 ) l2ReadKernel( const uint4* __restrict__ p, uint64_t n16, int reps, uint32_t* __restrict__ sink )
+{
+	uint32_t acc = 0;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for( int r = 0; r < reps; r++ )
+	{
+		// a different starting phase per repetition so that consecutive sweeps do not hit the same slice at the same time
+		for( uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride )
+		{
+			const uint4 v = __ldcg( p + ( ( i + (uint64_t)r * 4099u ) % n16 ) );
+			acc += v.x ^ v.y ^ v.z ^ v.w;
+		}
+	}
+	if( acc == 0x12345678u ) *sink = acc; // never true for the zero-filled buffer's checksum pattern; keeps the loads alive
 }
 } // namespace hako
 
@@ -104,4 +125,53 @@ int hako_ctx_build_stats( const hako_ctx* c, hako_build_stats* out )
 }
 
 uint64_t hako_ctx_launch_count( const hako_ctx* c ) { return c ? c->launches.load() : 0; }
+
+// The L2 roof of this device, measured ("B200 L2 peak is not in MEASURED_PEAKS -- measure once with a resident-set
+// microbenchmark and record"): read bandwidth over a buffer of setBytes (0: a quarter of the L2) that is swept `reps` times.
+int hako_ctx_l2_probe( hako_ctx* c, hako_stream stream, uint64_t setBytes, int reps, uint64_t* l2Bytes, float* readGBs )
+{
+	if( !c || !readGBs ) return HAKO_E_INVALID;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( c->device ) );
+	if( l2Bytes ) *l2Bytes = c->l2Bytes;
+	if( setBytes == 0 ) setBytes = c->l2Bytes / 4;
+	setBytes &= ~(uint64_t)4095;
+	if( setBytes < 4096 || reps < 1 ) return HAKO_E_INVALID;
+	uint4* buf = nullptr;
+	uint32_t* sink = nullptr;
+	HAKO_TRY( hako::dalloc( c, &buf, setBytes / 16, s ) );
+	int r = hako::dalloc( c, &sink, 1, s );
+	float best = 0.0f;
+	do
+	{
+		if( r ) break;
+		cudaError_t e = cudaMemsetAsync( buf, 0, setBytes, s );
+		if( e != cudaSuccess )
+		{
+			r = hako::cudaFail( e, "memset", __FILE__, __LINE__ );
+			break;
+		}
+		const uint32_t grid = (uint32_t)c->smCount * 8u;
+		for( int k = 0; k < 4 && r == 0; k++ ) // first launch warms the set into L2; best of the next three
+		{
+			e = cudaEventRecord( c->ev[6], s );
+			hako::l2ReadKernel<<<grid, 256, 0, s>>>( buf, setBytes / 16, k == 0 ? 1 : reps, sink );
+			c->launches.fetch_add( 1 );
+			if( e == cudaSuccess ) e = cudaGetLastError();
+			if( e == cudaSuccess ) e = cudaEventRecord( c->ev[7], s );
+			if( e == cudaSuccess ) e = cudaEventSynchronize( c->ev[7] );
+			float ms = 0.0f;
+			if( e == cudaSuccess ) e = cudaEventElapsedTime( &ms, c->ev[6], c->ev[7] );
+			if( e != cudaSuccess )
+			{
+				r = hako::cudaFail( e, "l2 probe", __FILE__, __LINE__ );
+				break;
+			}
+			if( k > 0 && ms > 0.0f ) best = std::max( best, (float)( (double)setBytes * reps / ( ms * 1e6 ) ) );
+		}
+	} while( 0 );
+	hako::dfree( buf, s ), hako::dfree( sink, s );
+	*readGBs = best;
+	return r;
+}
 }

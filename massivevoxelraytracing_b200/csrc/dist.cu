@@ -331,7 +331,7 @@ int hako_dist_broadcast_octree( hako_dist* d, hako_stream stream, int root, hako
 	}
 	const uint64_t nodeBytes = (uint64_t)o->numberOfNodes * sizeof( TraceNode ), attrBytes = o->attrs ? (uint64_t)o->numberOfVoxels * 8 : 0;
 	ncclResult_t nr = g_nccl.GroupStart();
-	if( nr == ncclSuccess && nodeBytes ) nr = g_nccl.Broadcast( o->nodes, o->nodes, nodeBytes / 16, ncclUint64 == ncclUint64 ? ncclUint64 : ncclUint64, root, d->comm, s );
+	if( nr == ncclSuccess && nodeBytes ) nr = g_nccl.Broadcast( o->nodes, o->nodes, nodeBytes / 8, ncclUint64, root, d->comm, s );
 	if( nr == ncclSuccess && o->numberOfNodes ) nr = g_nccl.Broadcast( o->masks, o->masks, o->numberOfNodes, ncclUint8, root, d->comm, s );
 	if( nr == ncclSuccess && attrBytes ) nr = g_nccl.Broadcast( o->attrs, o->attrs, attrBytes / 8, ncclUint64, root, d->comm, s );
 	ncclResult_t ge = g_nccl.GroupEnd();
@@ -425,11 +425,9 @@ int hako_dist_build_sharded( hako_dist* d, hako_stream stream, const float* pos,
 	}
 		const uint64_t n = pairs->n;
 		// ---- splitters ----
-		uint64_t* mine = d->dev;					 // [S + 1]
-		uint64_t* gathered = d->dev + ( S + 1 );	 // [world][S + 1]  (d->words covers world + 1 blocks? no: reuse below)
-		// layout of the scratch: [0, (S+1) * world) gathered samples; own samples live in their slot (in-place all-gather)
-		gathered = d->dev;
-		mine = d->dev + (size_t)rank * ( S + 1 );
+		// scratch layout: [0, (S + 1) * world) the gathered samples; a rank's own samples live in its slot (in-place all-gather)
+		uint64_t* gathered = d->dev;
+		uint64_t* mine = d->dev + (size_t)rank * ( S + 1 );
 		sampleKeysKernel<<<divUp( S + 1, 256 ), 256, 0, s>>>( pairs->keys, n, S, mine );
 		ctx->launches.fetch_add( 1 );
 		NK( g_nccl.AllGather( mine, gathered, S + 1, ncclUint64, d->comm, s ) );

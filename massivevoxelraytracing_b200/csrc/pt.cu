@@ -681,9 +681,13 @@ struct TraceWaveParams
 	int refillMin;	 // refill when at least this many lanes of the warp are idle
 	int burst;		 // traversal steps between two refill checks
 };
-template <int MIN_CTAS>
+template <int MIN_CTAS, int TOPK = 0>
 __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const OctreeView tree, const TraceWaveParams tp )
 {
+	// TOPK > 0 (HAKO_SMEM_TOP, A/B variant): the persistent CTA keeps the top TOPK nodes of the tree in shared memory
+	__shared__ uint2 s_top[TOPK > 0 ? TOPK * 8 : 1];
+	TopCache tc{ nullptr, 0xFFFFFFFFu };
+	if( TOPK > 0 ) tc = stageTop<( TOPK > 0 ? TOPK : 1 )>( tree, s_top );
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t nVertices = (uint32_t)*tp.nVertices;
 	const uint32_t stride = (uint32_t)tp.nVertices[-1]; // live paths one vertex earlier: the pitch of the kind-major ray arrays
@@ -742,8 +746,8 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 #pragma unroll 1
 			for( int it = 0; it < tp.burst; it++ )
 			{
-				const int r = tree.wide ? ( tr.ordinary ? tr.template step<true, true>( tree, shadow, stk ) : tr.template step<false, true>( tree, shadow, stk ) )
-										: ( tr.ordinary ? tr.template step<true, false>( tree, shadow, stk ) : tr.template step<false, false>( tree, shadow, stk ) );
+				const int r = tree.wide ? ( tr.ordinary ? tr.template step<true, true, ( TOPK > 0 )>( tree, shadow, stk, tc ) : tr.template step<false, true, ( TOPK > 0 )>( tree, shadow, stk, tc ) )
+										: ( tr.ordinary ? tr.template step<true, false, ( TOPK > 0 )>( tree, shadow, stk, tc ) : tr.template step<false, false, ( TOPK > 0 )>( tree, shadow, stk, tc ) );
 				if( r == TRAV_CONTINUE ) continue;
 				flying = false;
 				if( r == TRAV_HIT )
@@ -1239,6 +1243,8 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 		auto kTrace5 = traceWaveKernel<5>;
 		auto kTrace6 = traceWaveKernel<6>;
 		auto kTrace8 = traceWaveKernel<8>;
+		auto kTrace5Top = traceWaveKernel<5, 512>; // HAKO_SMEM_TOP=512: top 512 nodes in shared memory (A/B)
+		static const int topEnv = getenv( "HAKO_SMEM_TOP" ) ? atoi( getenv( "HAKO_SMEM_TOP" ) ) : 0;
 		const int occ = pt->waveTraceCtas >= 8 ? 8 : ( pt->waveTraceCtas >= 6 ? 6 : 5 );
 		const uint32_t traceGrid = (uint32_t)occ * ctx->smCount;
 		const uint32_t shadeGrid = 8u * ctx->smCount;
@@ -1289,7 +1295,9 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 				tp.shadowFirst = envOn ? 1 : 0;
 				tp.refillMin = std::max( 1, std::min( 32, pt->waveRefillMin ) );
 				tp.burst = std::max( 1, pt->waveBurst );
-				if( occ == 8 )
+				if( topEnv == 512 )
+					HAKO_LAUNCH( ctx, kTrace5Top, traceGrid, 256, 0, ls, q.tree, tp );
+				else if( occ == 8 )
 					HAKO_LAUNCH( ctx, kTrace8, traceGrid, 256, 0, ls, q.tree, tp );
 				else if( occ == 6 )
 					HAKO_LAUNCH( ctx, kTrace6, traceGrid, 256, 0, ls, q.tree, tp );
@@ -1354,6 +1362,16 @@ int hako_pt_read_rgba8( hako_pt* pt, hako_stream stream, uint8_t* rgba )
 	HAKO_TRY( hako_pt_resolve( pt, stream ) ); // toImageAsync = resolve + D2H, PathTracer.hpp:128-137
 	HAKO_CUDA( cudaMemcpyAsync( rgba, pt->rgba8, (size_t)pt->w * pt->h * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
 	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	return HAKO_OK;
+}
+
+// the reference's toImageAsync proper (PathTracer.hpp:118-129): resolve + D2H enqueued, NO host wait -- the caller synchronises the
+// stream (voxPTGPU.cpp:188-189).  rgba should be pinned for the copy to be truly asynchronous.
+int hako_pt_read_rgba8_async( hako_pt* pt, hako_stream stream, uint8_t* rgba )
+{
+	PT_ARG( pt && rgba, "hako_pt_read_rgba8_async: null argument" );
+	HAKO_TRY( hako_pt_resolve( pt, stream ) );
+	HAKO_CUDA( cudaMemcpyAsync( rgba, pt->rgba8, (size_t)pt->w * pt->h * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
 	return HAKO_OK;
 }
 

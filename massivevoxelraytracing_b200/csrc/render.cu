@@ -1,6 +1,8 @@
 // render.cu -- primary-ray casting and batched intersection (the `render` kernel, voxKernel.cu:437-483, and the
 // CPU renderLine loop, voxRT.cpp:307-347), plus conversion between the canonical 68-byte OctreeNode array
 // (voxCommon.hpp:133-138) and the resident 64-byte trace layout.
+#include <cstdlib>
+
 #include "internal.cuh"
 #include "traverse.cuh"
 
@@ -79,10 +81,14 @@ int launchIntersectBatch( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, co
 // Measured alternatives (B200, bench workload, 4096^3 stand-in): persistent warps that refill finished lanes from a tile
 // counter reach 4.1-6.3 Grays/s against 9.3 for this plain launch -- refilled lanes lose coherence with their warp, the
 // resumable state costs 16 more registers, and the hardware CTA scheduler already balances 65 k warps well.
-template <int WARPS_X, int WARPS_Y>
+template <int WARPS_X, int WARPS_Y, int TOPK>
 __global__ void __launch_bounds__( WARPS_X * WARPS_Y * 32 ) renderPrimaryKernel( OctreeView v, hako_camera cam, int w, int h, int y0, int y1, int showVertexColor,
 															  uchar4* __restrict__ rgba, float* __restrict__ tOut, int32_t* __restrict__ nMajorOut, uint32_t* __restrict__ vIndexOut )
 {
+	// TOPK > 0: the top TOPK nodes of the tree are copied to shared memory by every CTA (A/B variant, HAKO_SMEM_TOP)
+	__shared__ uint2 s_top[TOPK > 0 ? TOPK * 8 : 1];
+	TopCache tc{ nullptr, 0xFFFFFFFFu };
+	if( TOPK > 0 ) tc = stageTop<( TOPK > 0 ? TOPK : 1 )>( v, s_top );
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	const int x = blockIdx.x * ( WARPS_X * 8 ) + ( warp % WARPS_X ) * 8 + ( lane & 7u );
 	const int y = y0 + blockIdx.y * ( WARPS_Y * 4 ) + ( warp / WARPS_X ) * 4 + ( lane >> 3 );
@@ -93,7 +99,7 @@ __global__ void __launch_bounds__( WARPS_X * WARPS_Y * 32 ) renderPrimaryKernel(
 	float t = HAKO_MAX_FLOAT;
 	int nMajor = -1;
 	uint32_t vIndex = 0xFFFFFFFFu;
-	const bool hit = octreeTraverse<false>( v, ro, rd, &t, &nMajor, &vIndex );
+	const bool hit = octreeTraverseImpl<( TOPK > 0 )>( v, ro, rd, false, &t, &nMajor, &vIndex, tc );
 
 	const uint64_t p = (uint64_t)( y - y0 ) * w + x;
 	// streaming stores: the outputs are write-once and must not evict octree nodes from L2
@@ -127,7 +133,12 @@ int launchRenderPrimary( hako_ctx* ctx, cudaStream_t s, const OctreeView& v, con
 	if( w <= 0 || y1 <= y0 ) return 0;
 	// block shape: 2x4 warps = 16x16 pixels; 128/64/32-thread blocks measured within 1 % of this (the kernel is issue-bound, not occupancy-bound)
 	dim3 grid( divUp( w, 16 ), divUp( y1 - y0, 16 ) );
-	auto k = renderPrimaryKernel<2, 4>;
+	// HAKO_SMEM_TOP = 64 / 512: stage the top of the tree in shared memory (north_star's design point; measured, not the default:
+	// DESIGN.md section 7a)
+	static const int topEnv = getenv( "HAKO_SMEM_TOP" ) ? atoi( getenv( "HAKO_SMEM_TOP" ) ) : 0;
+	auto k = renderPrimaryKernel<2, 4, 0>;
+	if( topEnv == 64 ) k = renderPrimaryKernel<2, 4, 64>;
+	if( topEnv == 512 ) k = renderPrimaryKernel<2, 4, 512>;
 	HAKO_LAUNCH( ctx, k, grid, 256, 0, s, v, cam, w, h, y0, y1, showVertexColor, (uchar4*)rgba, t, nMajor, vIndex );
 	return 0;
 }

@@ -264,6 +264,290 @@ __global__ void __launch_bounds__( SORT_BLOCK, MIN_CTAS ) onesweepKernel( const 
 		}
 	}
 }
+// ---- one pass, second generation: the tile's keys AND values are fetched by two bulk-async copies (cp.async.bulk, the 1-D TMA
+// path) issued by one thread at kernel entry, each into its own shared buffer and each completing on its own mbarrier.  The value
+// tile therefore arrives while the keys are ranked and the look-back runs -- in the first-generation kernel the value loads could
+// only be issued after the key tile had left the single shared buffer, and 30 % of the warp-stall samples waited for them
+// (profiles/r1q_onesweep_stalls.txt).  Ranking, look-back and the two-step scatter are unchanged, so the result is the same
+// stable order.  Needs 16-byte aligned arrays (the bulk copy's granularity); sortPairsDevice falls back otherwise.
+__device__ __forceinline__ uint32_t smemAddr( const void* p ) { return (uint32_t)__cvta_generic_to_shared( p ); }
+__device__ __forceinline__ void mbarInit( uint64_t* bar, uint32_t count )
+{
+	asm volatile( "mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"( smemAddr( bar ) ), "r"( count ) );
+}
+__device__ __forceinline__ void mbarExpectTx( uint64_t* bar, uint32_t bytes )
+{
+	asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"( smemAddr( bar ) ), "r"( bytes ) : "memory" );
+}
+__device__ __forceinline__ void bulkLoad( void* dstSmem, const void* srcGlobal, uint32_t bytes, uint64_t* bar )
+{
+	asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"( smemAddr( dstSmem ) ), "l"( srcGlobal ), "r"( bytes ),
+				  "r"( smemAddr( bar ) )
+				  : "memory" );
+}
+__device__ __forceinline__ void mbarWait( uint64_t* bar, uint32_t parity )
+{
+	asm volatile(
+		"{\n"
+		".reg .pred p;\n"
+		"WAIT_%=:\n"
+		"mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+		"@p bra DONE_%=;\n"
+		"bra WAIT_%=;\n"
+		"DONE_%=:\n"
+		"}\n" ::"r"( smemAddr( bar ) ),
+		"r"( parity )
+		: "memory" );
+}
+
+template <int RBITS, int BLOCK, int ITEMS>
+struct SortV2Smem
+{
+	static constexpr int RADIX = 1 << RBITS;
+	static constexpr int WARPS = BLOCK / 32;
+	static constexpr int TILE = BLOCK * ITEMS;
+	static constexpr size_t OFF_KEYS = 0;								 // u64[TILE]: key tile, later the sorted staging buffer
+	static constexpr size_t OFF_VALUES = OFF_KEYS + (size_t)TILE * 8;	 // u64[TILE]: value tile in input order
+	static constexpr size_t OFF_GBASE = OFF_VALUES + (size_t)TILE * 8;	 // u64[RADIX]
+	static constexpr size_t OFF_TBASE = OFF_GBASE + (size_t)RADIX * 8;	 // u32[RADIX]
+	static constexpr size_t OFF_WHIST = OFF_TBASE + (size_t)RADIX * 4;	 // u16[WARPS][RADIX]
+	static constexpr size_t OFF_WTOT = OFF_WHIST + (size_t)WARPS * RADIX * 2; // u32[WARPS]
+	static constexpr size_t OFF_BAR = ( OFF_WTOT + (size_t)WARPS * 4 + 15 ) & ~(size_t)15; // 2 mbarriers + the tile index
+	static constexpr size_t BYTES = OFF_BAR + 32;
+};
+
+template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS>
+__global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
+																 uint64_t* __restrict__ keysOut, uint64_t* __restrict__ valuesOut, uint64_t n,
+																 int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [RADIX] exclusive */,
+																 unsigned long long* __restrict__ lookback /* [tiles][RADIX], zeroed */, uint32_t* __restrict__ ticket )
+{
+	using L = SortV2Smem<RBITS, BLOCK, ITEMS>;
+	constexpr int RADIX = L::RADIX, WARPS = L::WARPS, TILE = L::TILE;
+	constexpr int DPT = ( RADIX + BLOCK - 1 ) / BLOCK; // digits per thread in the per-digit phase (threads beyond RADIX / DPT idle there)
+	extern __shared__ __align__( 128 ) unsigned char s_raw[];
+	uint64_t* s_keys = (uint64_t*)( s_raw + L::OFF_KEYS );
+	uint64_t* s_values = (uint64_t*)( s_raw + L::OFF_VALUES );
+	unsigned long long* s_globalBase = (unsigned long long*)( s_raw + L::OFF_GBASE );
+	uint32_t* s_tileBase = (uint32_t*)( s_raw + L::OFF_TBASE );
+	uint16_t* s_warpHist = (uint16_t*)( s_raw + L::OFF_WHIST ); // [WARPS][RADIX]
+	uint32_t* s_warpTotals = (uint32_t*)( s_raw + L::OFF_WTOT );
+	uint64_t* s_bar = (uint64_t*)( s_raw + L::OFF_BAR );
+	uint32_t* s_tile = (uint32_t*)( s_bar + 2 );
+
+	if( threadIdx.x == 0 )
+	{
+		mbarInit( &s_bar[0], 1 );
+		mbarInit( &s_bar[1], 1 );
+		asm volatile( "fence.mbarrier_init.release.cluster;" ::: "memory" );
+		const uint32_t t = atomicAdd( ticket, 1u );
+		*s_tile = t;
+		const uint64_t start = (uint64_t)t * TILE;
+		const uint32_t cnt = (uint32_t)min( (uint64_t)TILE, n - start );
+		const uint32_t bytes = ( cnt * 8u ) & ~15u; // whole 16-byte units; an odd last key is fetched below
+		if( bytes )
+		{
+			mbarExpectTx( &s_bar[0], bytes );
+			bulkLoad( s_keys, keysIn + start, bytes, &s_bar[0] );
+			if( PAIRS )
+			{
+				mbarExpectTx( &s_bar[1], bytes );
+				bulkLoad( s_values, valuesIn + start, bytes, &s_bar[1] );
+			}
+		}
+	}
+	for( int i = threadIdx.x; i < WARPS * RADIX / 2; i += BLOCK ) ( (uint32_t*)s_warpHist )[i] = 0;
+	__syncthreads();
+	const uint32_t tile = *s_tile;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint64_t tileStart = (uint64_t)tile * TILE;
+	const uint32_t tileCount = (uint32_t)min( (uint64_t)TILE, n - tileStart );
+	const bool bulk = ( ( tileCount * 8u ) & ~15u ) != 0;
+	const bool oddTail = ( tileCount & 1u ) != 0; // the last pair of an odd tile does not fill a 16-byte unit
+
+	// warp-striped arrangement: warp w owns items [w * ITEMS * 32, (w + 1) * ITEMS * 32), item i of lane l is w * ITEMS * 32 + i * 32 + l
+	uint64_t key[ITEMS];
+	uint16_t rank[ITEMS];
+	const uint32_t warpBase = warp * ( ITEMS * 32 );
+	if( bulk ) mbarWait( &s_bar[0], 0 );
+#pragma unroll
+	for( int i = 0; i < ITEMS; i++ )
+	{
+		const uint32_t idx = warpBase + i * 32 + lane;
+		uint64_t k = ~0ull;
+		if( idx < tileCount ) k = ( oddTail && idx == tileCount - 1 ) ? keysIn[tileStart + idx] : s_keys[idx];
+		key[i] = k;
+	}
+	uint16_t* myHist = s_warpHist + warp * RADIX;
+#pragma unroll
+	for( int i = 0; i < ITEMS; i++ )
+	{
+		const uint32_t idx = warpBase + i * 32 + lane;
+		const bool valid = idx < tileCount;
+		const uint32_t d = valid ? digitOf( key[i], shift, mask ) : ( RADIX - 1 );
+		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, d | ( valid ? 0u : 0x10000u ) );
+		const uint32_t before = __popc( peers & ( ( 1u << lane ) - 1u ) );
+		uint32_t base = 0;
+		if( valid ) base = myHist[d];
+		__syncwarp();
+		if( valid && before == 0 ) myHist[d] = (uint16_t)( base + __popc( peers ) );
+		__syncwarp();
+		rank[i] = (uint16_t)( base + before );
+	}
+	__syncthreads(); // every key is in registers: s_keys becomes the sorted staging buffer
+
+	{
+		uint32_t total[DPT];
+		unsigned long long excl[DPT];
+		uint32_t mine = 0;
+		const bool owner = threadIdx.x * DPT < RADIX;
+#pragma unroll
+		for( int j = 0; j < DPT; j++ )
+		{
+			const uint32_t d = threadIdx.x * DPT + j;
+			total[j] = 0;
+			excl[j] = 0;
+			if( !owner ) continue;
+			uint32_t tot = 0;
+#pragma unroll
+			for( int w = 0; w < WARPS; w++ )
+			{
+				const uint32_t c = s_warpHist[w * RADIX + d];
+				s_warpHist[w * RADIX + d] = (uint16_t)tot;
+				tot += c;
+			}
+			total[j] = tot;
+			mine += tot;
+			*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + d ) = ( tile == 0 ? LB_FLAG_INC : LB_FLAG_AGG ) | (unsigned long long)tot;
+		}
+#pragma unroll
+		for( int j = 0; j < DPT; j++ )
+		{
+			const uint32_t d = threadIdx.x * DPT + j;
+			if( !owner || tile == 0 ) continue;
+			int64_t t = (int64_t)tile - 1;
+			for( ;; )
+			{
+				unsigned long long v;
+				do
+				{
+					v = *(const volatile unsigned long long*)( lookback + (size_t)t * RADIX + d );
+				} while( ( v >> 62 ) == 0 );
+				excl[j] += v & LB_VALUE_MASK;
+				if( ( v >> 62 ) == 2 ) break;
+				t--;
+			}
+			*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + d ) = LB_FLAG_INC | ( excl[j] + total[j] );
+		}
+		uint32_t inc = mine;
+#pragma unroll
+		for( int o = 1; o < 32; o <<= 1 )
+		{
+			const uint32_t nb = __shfl_up_sync( 0xFFFFFFFFu, inc, o );
+			if( lane >= o ) inc += nb;
+		}
+		if( lane == 31 ) s_warpTotals[warp] = inc;
+		__syncthreads();
+		uint32_t wbase = 0;
+#pragma unroll
+		for( int w = 0; w < WARPS; w++ )
+			if( w < (int)warp ) wbase += s_warpTotals[w];
+		uint32_t tb = wbase + inc - mine;
+		if( owner )
+		{
+#pragma unroll
+			for( int j = 0; j < DPT; j++ )
+			{
+				const uint32_t d = threadIdx.x * DPT + j;
+				s_tileBase[d] = tb;
+				s_globalBase[d] = digitBase[d] + excl[j] - tb;
+				tb += total[j];
+			}
+		}
+	}
+	__syncthreads();
+#pragma unroll
+	for( int i = 0; i < ITEMS; i++ )
+	{
+		const uint32_t idx = warpBase + i * 32 + lane;
+		if( idx < tileCount )
+		{
+			const uint32_t d = digitOf( key[i], shift, mask );
+			const uint32_t p = s_tileBase[d] + myHist[d] + rank[i];
+			rank[i] = (uint16_t)p;
+			s_keys[p] = key[i];
+		}
+	}
+	__syncthreads();
+	uint64_t dst[ITEMS];
+#pragma unroll
+	for( int i = 0; i < ITEMS; i++ )
+	{
+		const uint32_t p = i * BLOCK + threadIdx.x;
+		if( p < tileCount )
+		{
+			const uint64_t k = s_keys[p];
+			dst[i] = s_globalBase[digitOf( k, shift, mask )] + p;
+			keysOut[dst[i]] = k;
+		}
+	}
+	if( PAIRS )
+	{
+		// the value tile has been in flight since kernel entry
+		if( bulk ) mbarWait( &s_bar[1], 0 );
+		__syncthreads(); // the sorted keys have left s_keys
+#pragma unroll
+		for( int i = 0; i < ITEMS; i++ )
+		{
+			const uint32_t idx = warpBase + i * 32 + lane;
+			if( idx < tileCount ) s_keys[rank[i]] = ( oddTail && idx == tileCount - 1 ) ? valuesIn[tileStart + idx] : s_values[idx];
+		}
+		__syncthreads();
+#pragma unroll
+		for( int i = 0; i < ITEMS; i++ )
+		{
+			const uint32_t p = i * BLOCK + threadIdx.x;
+			if( p < tileCount ) valuesOut[dst[i]] = s_keys[p];
+		}
+	}
+}
+
+// variants of the bulk-copy pass: block size x items per thread x resident CTAs per SM (HAKO_SORT_VARIANT)
+//   1: 256 x 15 x 3 (3 840-pair tiles, 71 KB)   2: 512 x 8 x 2 (4 096-pair tiles, 83 KB)   3: 256 x 16 x 2 (4 096, 79 KB)
+int sortVariantTile( int variant ) { return variant == 1 ? 256 * 15 : ( variant == 0 ? SORT_TILE : 4096 ); }
+template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS>
+int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t* kin, const uint64_t* vin, uint64_t* kout, uint64_t* vout, uint64_t n, int shift, uint32_t mask,
+				   const unsigned long long* digitBase, unsigned long long* lookback, uint32_t* ticket )
+{
+	auto k = onesweepBulkKernel<RBITS, PAIRS, BLOCK, ITEMS, MIN_CTAS>;
+	constexpr size_t bytes = SortV2Smem<RBITS, BLOCK, ITEMS>::BYTES;
+	static bool configured[16] = {}; // per device
+	int dev = ctx->device & 15;
+	if( !configured[dev] )
+	{
+		HAKO_CUDA( cudaFuncSetAttribute( k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes ) );
+		configured[dev] = true;
+	}
+	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+	return 0;
+}
+template <int RBITS, bool PAIRS>
+int launchBulkRP( hako_ctx* ctx, cudaStream_t s, int variant, uint32_t tiles, const uint64_t* kin, const uint64_t* vin, uint64_t* kout, uint64_t* vout, uint64_t n, int shift,
+				  uint32_t mask, const unsigned long long* digitBase, unsigned long long* lookback, uint32_t* ticket )
+{
+	if( variant == 1 ) return launchBulkOne<RBITS, PAIRS, 256, 15, 3>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+	if( variant == 3 ) return launchBulkOne<RBITS, PAIRS, 256, 16, 2>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+	return launchBulkOne<RBITS, PAIRS, 512, 8, 2>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+}
+int launchBulkPass( hako_ctx* ctx, cudaStream_t s, int variant, int rbits, bool pairs, uint32_t tiles, const uint64_t* kin, const uint64_t* vin, uint64_t* kout, uint64_t* vout,
+					uint64_t n, int shift, uint32_t mask, const unsigned long long* digitBase, unsigned long long* lookback, uint32_t* ticket )
+{
+	if( rbits == 9 )
+		return pairs ? launchBulkRP<9, true>( ctx, s, variant, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket )
+					 : launchBulkRP<9, false>( ctx, s, variant, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+	return pairs ? launchBulkRP<8, true>( ctx, s, variant, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket )
+				 : launchBulkRP<8, false>( ctx, s, variant, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+}
 } // namespace
 
 // Sorts in place from the caller's point of view unless resultInTmp is given: with an odd number of passes the result
@@ -285,7 +569,13 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 	const int passes = ( window + rbits - 1 ) / rbits;
 	ctx->stats.sortPasses = (uint32_t)passes;
 	if( n == 0 || passes == 0 ) return 0;
-	const uint64_t tiles = ( n + SORT_TILE - 1 ) / SORT_TILE;
+	// bulk-copy passes need 16-byte aligned arrays; a caller's own device pointers (hako_sort_pairs_device) may not be
+	const bool aligned16 = ( ( (uintptr_t)keys | (uintptr_t)keysTmp | (uintptr_t)values | (uintptr_t)valuesTmp ) & 15u ) == 0;
+	const char* varEnv = getenv( "HAKO_SORT_VARIANT" ); // 0: first-generation kernel (plain loads, 4 096-pair tiles)
+	int variant = varEnv ? atoi( varEnv ) : 1; // B200, 72.7 M pairs x 36 bits: variant 0 4.46 ms, 1 4.18, 2 4.62, 3 5.23 (profiles/r2e_sort_variants.log)
+	if( variant < 0 || variant > 3 || !aligned16 ) variant = 0;
+	const uint64_t tileSize = (uint64_t)sortVariantTile( variant );
+	const uint64_t tiles = ( n + tileSize - 1 ) / tileSize;
 	if( tiles >= 0x7FFFFFFFull )
 	{
 		setError( "sort: too many tiles" );
@@ -334,8 +624,12 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 			const int occ = occEnv ? atoi( occEnv ) : 4; // B200: 2 CTAs/SM 5.43 ms, 3: 5.08, 4: 4.50 (72.7 M pairs, 36 bits; profiles/r1g)
 			if( occ == 3 ) k = rbits == 9 ? ( values ? onesweepKernel<9, true, 3> : onesweepKernel<9, false, 3> ) : ( values ? onesweepKernel<8, true, 3> : onesweepKernel<8, false, 3> );
 			if( occ == 4 ) k = rbits == 9 ? ( values ? onesweepKernel<9, true, 4> : onesweepKernel<9, false, 4> ) : ( values ? onesweepKernel<8, true, 4> : onesweepKernel<8, false, 4> );
-			HAKO_LAUNCH( ctx, k, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
-						 lookback + (size_t)p * tiles * RADIX, tickets + p );
+			if( variant == 0 )
+				HAKO_LAUNCH( ctx, k, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
+							 lookback + (size_t)p * tiles * RADIX, tickets + p );
+			else if( ( r = launchBulkPass( ctx, s, variant, rbits, values != nullptr, (uint32_t)tiles, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
+										  lookback + (size_t)p * tiles * RADIX, tickets + p ) ) )
+				break;
 			uint64_t* t = kin;
 			kin = kout, kout = t;
 			t = vin;

@@ -41,6 +41,25 @@ struct TravStack
 	uint4 a[HAKO_STACK_DEPTH]; // node, tx1, ty1, tz1
 	uint2 b[HAKO_STACK_DEPTH]; // childMask | level << 8, nVoxelSkipped
 };
+// Optional shared-memory copy of the LAST `count` nodes of the array = the top of the tree (numbering is bottom-up, the root is
+// last): north_star's "octree top staged in shared memory".  Built per CTA by stageTop(); step<.., TOP = true> reads a node's slot
+// from it when node >= base.  Measured A/B in DESIGN.md section 7a (HAKO_SMEM_TOP); off by default.
+struct TopCache
+{
+	const uint2* slots; // [count][8]
+	uint32_t base;		// numberOfNodes - count
+};
+template <int TOPK>
+__device__ __forceinline__ TopCache stageTop( const OctreeView& v, uint2* s_top )
+{
+	const uint32_t count = v.numberOfNodes < (uint32_t)TOPK ? v.numberOfNodes : (uint32_t)TOPK;
+	const uint32_t base = v.numberOfNodes - count;
+	const uint2* src = &v.nodes[base].slot[0];
+	for( uint32_t i = threadIdx.x; i < count * 8u; i += blockDim.x ) s_top[i] = __ldg( src + i );
+	__syncthreads();
+	return TopCache{ s_top, base };
+}
+
 struct Traversal
 {
 	int sp;
@@ -109,8 +128,8 @@ struct Traversal
 	// 0 < lmax): one FMNMX3 instead of two FSETP + FSEL pairs, ~6 of ~95 instructions per step.  Rays with huge slab distances
 	// (a zero or denormal direction component against the clamped 1/rd) can produce inf - inf = NaN, where the two forms
 	// differ; they take the exact path (tests/test_gpu_traverse.py::test_random_rays_and_shadow has such rays).
-	template <bool FINITE = false, bool WIDE = false>
-	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, TravStack& stk )
+	template <bool FINITE = false, bool WIDE = false, bool TOP = false>
+	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, TravStack& stk, const TopCache tc = TopCache{ nullptr, 0xFFFFFFFFu } )
 	{
 		const float scale = levelScale( level );
 		// :317-319 t0 is recomputed from t1 each visit
@@ -156,7 +175,8 @@ struct Traversal
 					stk.b[sp] = make_uint2( childMask | ( level << 8 ) | ( WIDE ? nmask << 16 : 0u ), skipped );
 					sp++;
 				}
-				const uint2 slot = ldg_u2( &v.nodes[WIDE ? node : ( node & 0xFFFFFFu )].slot[ci] );
+				const uint32_t nidx = WIDE ? node : ( node & 0xFFFFFFu );
+				const uint2 slot = ( TOP && nidx >= tc.base ) ? tc.slots[( nidx - tc.base ) * 8u + ci] : ldg_u2( &v.nodes[nidx].slot[ci] );
 				node = slot.x;
 				if( WIDE ) nmask = ( node != 0xFFFFFFFFu ) ? (uint32_t)__ldg( v.masks + node ) : 0u; // the second dependent load of the wide layout
 				tx1 = x1;
@@ -191,7 +211,9 @@ struct Traversal
 
 // returns true on a hit (and then writes t / nMajor / vIndex); a miss leaves the outputs untouched (voxRT.cpp:313-325).
 // `shadow` may be a compile-time constant (the template wrapper below) or a per-lane runtime value.
-__device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, V3 rd, const bool shadow, float* tOut, int* nMajorOut, uint32_t* vIndexOut )
+template <bool TOP = false>
+__device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, V3 rd, const bool shadow, float* tOut, int* nMajorOut, uint32_t* vIndexOut,
+													const TopCache tc = TopCache{ nullptr, 0xFFFFFFFFu } )
 {
 	Traversal tr;
 	TravStack stk;
@@ -204,14 +226,14 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 		{
 			do
 			{
-				r = tr.template step<true, true>( v, shadow, stk );
+				r = tr.template step<true, true, TOP>( v, shadow, stk, tc );
 			} while( r == TRAV_CONTINUE );
 		}
 		else
 		{
 			do
 			{
-				r = tr.template step<false, true>( v, shadow, stk );
+				r = tr.template step<false, true, TOP>( v, shadow, stk, tc );
 			} while( r == TRAV_CONTINUE );
 		}
 	}
@@ -222,14 +244,14 @@ __device__ __forceinline__ bool octreeTraverseImpl( const OctreeView& v, V3 ro, 
 		{
 			do
 			{
-				r = tr.template step<true, false>( v, shadow, stk );
+				r = tr.template step<true, false, TOP>( v, shadow, stk, tc );
 			} while( r == TRAV_CONTINUE );
 		}
 		else
 		{
 			do
 			{
-				r = tr.template step<false, false>( v, shadow, stk );
+				r = tr.template step<false, false, TOP>( v, shadow, stk, tc );
 			} while( r == TRAV_CONTINUE );
 		}
 	}

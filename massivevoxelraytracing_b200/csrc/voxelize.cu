@@ -14,6 +14,9 @@
 // A column is a pure function of (triangle, x) (voxelization.hpp:230-336), so slicing by x is parity-safe, it bounds
 // the work per thread (a 4096^3 bunny triangle covers ~7k voxels) and the emission order is deterministic: triangle-major,
 // then x, y, z -- exactly the order of the CPU loop.
+#include <algorithm>
+#include <cstdlib>
+
 #include "internal.cuh"
 #include "scan.cuh"
 
@@ -157,13 +160,25 @@ __device__ __forceinline__ uint32_t packRGB255( V3 c )
 }
 } // namespace
 
-// ---- 1. columns per triangle ----
-__global__ void __launch_bounds__( 256 ) triColumnsKernel( const float* __restrict__ pos, uint32_t nTriangles, V3 origin, float dps, int gridRes, uint32_t* __restrict__ nCols )
+// A triangle is "small" when the (x, y) footprint of its clamped box holds at most SMALL_AREA cells: the warp-cooperative kernel
+// (32 triangles per warp, warpVoxelsKernel below) takes those -- the multi-million-triangle regime of the scanned models -- and the
+// per-column kernels take the rest, where one triangle alone is thousands of columns (bunny at 4096^3: ~7 k voxels per triangle).
+constexpr int64_t SMALL_AREA = 4096;
+__device__ __forceinline__ bool isSmallTri( const TriBox& b )
+{
+	const int64_t nx = (int64_t)b.hi_xy.x - b.lo_xy.x + 1, ny = (int64_t)b.hi_xy.y - b.lo_xy.y + 1;
+	return nx <= 0 || ny <= 0 || nx * ny <= SMALL_AREA;
+}
+
+// ---- 1. columns per triangle (largeOnly: small triangles get no column, they belong to warpVoxelsKernel) ----
+__global__ void __launch_bounds__( 256 ) triColumnsKernel( const float* __restrict__ pos, uint32_t nTriangles, V3 origin, float dps, int gridRes, uint32_t* __restrict__ nCols, int largeOnly )
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if( i >= nTriangles ) return;
 	const TriBox b = triBox( loadV3( pos, (uint64_t)i * 3 ), loadV3( pos, (uint64_t)i * 3 + 1 ), loadV3( pos, (uint64_t)i * 3 + 2 ), origin, dps, gridRes );
-	nCols[i] = ( b.hi_xy.x >= b.lo_xy.x ) ? (uint32_t)( b.hi_xy.x - b.lo_xy.x + 1 ) : 0u;
+	uint32_t n = ( b.hi_xy.x >= b.lo_xy.x ) ? (uint32_t)( b.hi_xy.x - b.lo_xy.x + 1 ) : 0u;
+	if( largeOnly && isSmallTri( b ) ) n = 0;
+	nCols[i] = n;
 }
 
 // ---- generic u32 exclusive scan kernel (in place allowed), 256 threads x 8 items ----
@@ -465,64 +480,384 @@ __global__ void __launch_bounds__( 128, EMIT ? HAKO_EMIT_CTAS : HAKO_COUNT_CTAS 
 	}
 }
 
+// ---- warp-cooperative voxelization of small triangles: ONE set-up per triangle, all 32 lanes busy in every phase ----
+// A warp owns 32 consecutive triangles.
+//   set-up   lane = triangle: box, the 9 edge functions of the three projections, plane coefficients (VTContext, voxelization.hpp:
+//            146-224) -- computed ONCE and parked in shared memory (39 words), instead of once per (triangle, x) column and pass;
+//   columns  lane = (triangle, x) of the warp's column list (warp scan + 5-step search): yRangeInclusive (:230-269);
+//   rows     lane = (triangle, x, y) of the chunk's row list: zRangeInclusive (:270-299) + the two 2-D overlap tests (:311-336);
+//   voxels   COUNT: summed.  EMIT: queued in shared memory in (triangle, x, y, z) order -- the CPU loop's order, voxRT.cpp:198-240 --
+//            and shaded by all 32 lanes when the queue is half full (closest-point barycentrics, colour mix, Morton key).
+// Every value is the same fp32 expression as in columnVoxelsKernel, so the voxel set and the attributes are bit-identical.
+constexpr int VW_WARPS = 4;	   // warps per block
+constexpr int VW_CTX = 39;	   // words per triangle context (odd pitch: lanes reading different triangles hit different banks)
+constexpr int VW_QUEUE = 256;  // queue entries per warp; a row chunk adds at most 32 x 4 voxels
+enum
+{
+	VC_FLAGS = 0, // major | flat << 2
+	VC_LOX = 1,
+	VC_LOY = 2,
+	VC_HIY = 3,
+	VC_LOZ = 4,
+	VC_HIZ = 5,
+	VC_EM = 6,	// nx[3], ny[3], dc[3] of the major projection
+	VC_EA = 15, // first minor projection
+	VC_EB = 24, // second minor projection
+	VC_KX = 33,
+	VC_KY = 34,
+	VC_CSIX = 35,
+	VC_CMIN = 36,
+	VC_CMAX = 37,
+	VC_PAD = 38
+};
+__device__ __forceinline__ uint32_t warpInclusiveScan( uint32_t v, uint32_t lane )
+{
+#pragma unroll
+	for( int o = 1; o < 32; o <<= 1 )
+	{
+		const uint32_t n = __shfl_up_sync( 0xFFFFFFFFu, v, o );
+		if( lane >= o ) v += n;
+	}
+	return v;
+}
+// largest i in [0, 31] with pref[i] <= j (pref non-decreasing, pref[0] <= j)
+__device__ __forceinline__ uint32_t lastNotAbove( const uint32_t* pref, uint32_t j )
+{
+	uint32_t lo = 0;
+#pragma unroll
+	for( int step = 16; step >= 1; step >>= 1 )
+		if( pref[lo + step] <= j ) lo += step;
+	return lo;
+}
+
+template <bool EMIT>
+__global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
+																  uint32_t nTriangles, V3 origin, float dps, int gridRes, int sixSeparating,
+																  uint32_t* __restrict__ warpCount, const uint32_t* __restrict__ warpOffset,
+																  uint64_t* __restrict__ keys, uint64_t* __restrict__ values, uint32_t blockBase )
+{
+	__shared__ float s_ctx[VW_WARPS][32][VW_CTX];
+	__shared__ uint32_t s_colPref[VW_WARPS][32];
+	__shared__ uint32_t s_rowPref[VW_WARPS][32];
+	__shared__ float s_tri[EMIT ? VW_WARPS : 1][EMIT ? 32 : 1][27]; // positions, colours, emissions of the warp's triangles
+	__shared__ uint64_t s_q[EMIT ? VW_WARPS : 1][EMIT ? VW_QUEUE : 1];
+	__shared__ uint8_t s_qOwner[EMIT ? VW_WARPS : 1][EMIT ? VW_QUEUE : 1];
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const uint32_t gw = ( blockIdx.x + blockBase ) * VW_WARPS + warp; // global warp = group of 32 triangles
+	const uint32_t tri = gw * 32u + lane;
+	const bool six = sixSeparating != 0;
+	float* ctx = s_ctx[warp][lane];
+	uint32_t* ictx = (uint32_t*)ctx;
+
+	// ---- set-up: lane = triangle ----
+	uint32_t nCols = 0;
+	if( tri < nTriangles )
+	{
+		const V3 v0 = loadV3( pos, (uint64_t)tri * 3 ), v1 = loadV3( pos, (uint64_t)tri * 3 + 1 ), v2 = loadV3( pos, (uint64_t)tri * 3 + 2 );
+		const TriBox b = triBox( v0, v1, v2, origin, dps, gridRes );
+		if( isSmallTri( b ) && b.hi_xy.x >= b.lo_xy.x )
+		{
+			nCols = (uint32_t)( b.hi_xy.x - b.lo_xy.x + 1 );
+			const int major = b.major;
+			const int ax1 = ( major == 0 ) ? 1 : 0;
+			const int ax2 = ( major == 2 ) ? 1 : 2;
+			const Edges EM = edgeSetup( v0, v1, v2, b.n, major, six, dps );
+			const Edges EA = edgeSetup( v0, v1, v2, b.n, ax1, six, dps );
+			const Edges EB = edgeSetup( v0, v1, v2, b.n, ax2, six, dps );
+			// voxelization.hpp:200-223 plane coefficients
+			const V2 v0xy = proj2( v0, major );
+			const float v0z = projR( v0, major );
+			const V2 nxy = proj2( b.n, major );
+			const float nz = projR( b.n, major );
+			const float kx = -nxy.x / nz;
+			const float ky = -nxy.y / nz;
+			const float K = -kx * v0xy.x - ky * v0xy.y + v0z;
+			ictx[VC_FLAGS] = (uint32_t)major | ( b.lo_z == b.hi_z ? 4u : 0u );
+			ictx[VC_LOX] = (uint32_t)b.lo_xy.x;
+			ictx[VC_LOY] = (uint32_t)b.lo_xy.y;
+			ictx[VC_HIY] = (uint32_t)b.hi_xy.y;
+			ictx[VC_LOZ] = (uint32_t)b.lo_z;
+			ictx[VC_HIZ] = (uint32_t)b.hi_z;
+#pragma unroll
+			for( int e = 0; e < 3; e++ )
+			{
+				ctx[VC_EM + e] = EM.nx[e], ctx[VC_EM + 3 + e] = EM.ny[e], ctx[VC_EM + 6 + e] = EM.dc[e];
+				ctx[VC_EA + e] = EA.nx[e], ctx[VC_EA + 3 + e] = EA.ny[e], ctx[VC_EA + 6 + e] = EA.dc[e];
+				ctx[VC_EB + e] = EB.nx[e], ctx[VC_EB + 3 + e] = EB.ny[e], ctx[VC_EB + 6 + e] = EB.dc[e];
+			}
+			ctx[VC_KX] = kx;
+			ctx[VC_KY] = ky;
+			ctx[VC_CSIX] = K + 0.5f * dps * ( kx + ky );
+			ctx[VC_CMIN] = K + dps * ( smin( kx, 0.0f ) + smin( ky, 0.0f ) );
+			ctx[VC_CMAX] = K + dps * ( smax( kx, 0.0f ) + smax( ky, 0.0f ) );
+			if( EMIT )
+			{
+				float* d = s_tri[warp][lane];
+				d[0] = v0.x, d[1] = v0.y, d[2] = v0.z, d[3] = v1.x, d[4] = v1.y, d[5] = v1.z, d[6] = v2.x, d[7] = v2.y, d[8] = v2.z;
+#pragma unroll
+				for( int k = 0; k < 9; k++ )
+				{
+					d[9 + k] = col[(uint64_t)tri * 9 + k];
+					d[18 + k] = emi[(uint64_t)tri * 9 + k];
+				}
+			}
+		}
+	}
+	const uint32_t colIncl = warpInclusiveScan( nCols, lane );
+	const uint32_t colTotal = __shfl_sync( 0xFFFFFFFFu, colIncl, 31 );
+	s_colPref[warp][lane] = colIncl - nCols;
+	__syncwarp();
+	uint32_t total = 0;	  // COUNT: voxels of this lane; EMIT: voxels already written by the warp
+	uint32_t qCount = 0;  // EMIT: voxels waiting in the queue (warp-uniform)
+	const uint32_t outBase = EMIT ? warpOffset[gw] : 0u;
+	// shades queue entries [0, qCount) with all lanes and stores them at outBase + total
+	auto drain = [&]() {
+		__syncwarp();
+		for( uint32_t i = lane; i < qCount; i += 32u )
+		{
+			const uint64_t q = s_q[EMIT ? warp : 0][EMIT ? i : 0];
+			const float* d = s_tri[EMIT ? warp : 0][EMIT ? s_qOwner[warp][i] : 0];
+			const uint32_t cx = (uint32_t)q & 0x1FFFFFu, cy = (uint32_t)( q >> 21 ) & 0x1FFFFFu, cz = (uint32_t)( q >> 42 ) & 0x1FFFFFu;
+			// the voxel's lower corner: origin + dps * index per axis -- the products and sums of the enumeration
+			// ( o = org_xy + dps * {x, y}, r = org_z + (float)z * dps, voxelization.hpp:300-305 )
+			const V3 p = { origin.x + dps * (int)cx, origin.y + dps * (int)cy, origin.z + dps * (int)cz };
+			const V3 bc = closestBary( V3{ d[0], d[1], d[2] }, V3{ d[3], d[4], d[5] }, V3{ d[6], d[7], d[8] }, p );
+			const V3 k0 = { d[9], d[10], d[11] }, k1 = { d[12], d[13], d[14] }, k2 = { d[15], d[16], d[17] };
+			const V3 m0 = { d[18], d[19], d[20] }, m1 = { d[21], d[22], d[23] }, m2 = { d[24], d[25], d[26] };
+			const V3 bcol = bc.x * k1 + bc.y * k2 + bc.z * k0; // voxKernel.cu:148, voxRT.cpp:229
+			const V3 bemi = bc.x * m1 + bc.y * m2 + bc.z * m0;
+			const uint64_t o = (uint64_t)outBase + total + i;
+			keys[o] = mortonEncode( cx, cy, cz );
+			values[o] = (uint64_t)packRGB255( bcol ) | ( (uint64_t)packRGB255( bemi ) << 32 );
+		}
+		total += qCount;
+		qCount = 0;
+		__syncwarp();
+	};
+
+	for( uint32_t cbase = 0; cbase < colTotal; cbase += 32u )
+	{
+		// ---- columns: lane = (triangle, x) ----
+		const uint32_t j = cbase + lane;
+		const bool hasCol = j < colTotal;
+		const uint32_t owner = hasCol ? lastNotAbove( s_colPref[warp], j ) : 0u;
+		const float* oc = s_ctx[warp][owner];
+		const uint32_t* oi = (const uint32_t*)oc;
+		const int major = (int)( oi[VC_FLAGS] & 3u );
+		const V2 org_xy = proj2( origin, major );
+		const int x = (int)oi[VC_LOX] + (int)( j - s_colPref[warp][owner] );
+		int ly = 1, uy = -1;
+		if( hasCol )
+		{
+			// yRangeInclusive( x ), voxelization.hpp:230-269
+			const float xc = org_xy.x + x * dps;
+			float miny = -HAKO_MAX_FLOAT, maxy = HAKO_MAX_FLOAT;
+			bool empty = false;
+#pragma unroll
+			for( int e = 0; e < 3; e++ )
+			{
+				const float ex = oc[VC_EM + e], ey = oc[VC_EM + 3 + e], cc = oc[VC_EM + 6 + e];
+				if( ey == 0.0f )
+				{
+					if( -ex * xc <= cc ) continue;
+					empty = true;
+					break;
+				}
+				const float k = -( xc * ex + cc ) / ey;
+				if( 0.0f < ey )
+					miny = smax( miny, k );
+				else
+					maxy = smin( maxy, k );
+			}
+			if( !empty )
+			{
+				const float minIf = smax( ( miny - org_xy.y ) / dps, -2147483648.0f );
+				const float maxIf = smin( ( maxy - org_xy.y ) / dps, 2147483520.0f );
+				ly = smax( f2i_x86( ceilf( minIf ) ), (int)oi[VC_LOY] );
+				uy = smin( f2i_x86( floorf( maxIf ) ), (int)oi[VC_HIY] );
+			}
+		}
+		const uint32_t rows = ( hasCol && uy >= ly ) ? (uint32_t)( uy - ly + 1 ) : 0u;
+		const uint32_t rowIncl = warpInclusiveScan( rows, lane );
+		const uint32_t rowTotal = __shfl_sync( 0xFFFFFFFFu, rowIncl, 31 );
+		const uint32_t rowExcl = rowIncl - rows;
+		__syncwarp();
+		s_rowPref[warp][lane] = rowExcl;
+		__syncwarp();
+
+		for( uint32_t rbase = 0; rbase < rowTotal; rbase += 32u )
+		{
+			// ---- rows: lane = (triangle, x, y) ----
+			const uint32_t r = rbase + lane;
+			const bool hasRow = r < rowTotal;
+			const uint32_t cl = hasRow ? lastNotAbove( s_rowPref[warp], r ) : 0u;
+			const uint32_t rOwner = __shfl_sync( 0xFFFFFFFFu, owner, cl );
+			const int rx = __shfl_sync( 0xFFFFFFFFu, x, cl );
+			const int rly = __shfl_sync( 0xFFFFFFFFu, ly, cl );
+			const uint32_t rEx = __shfl_sync( 0xFFFFFFFFu, rowExcl, cl );
+			const int y = rly + (int)( r - rEx );
+			const float* rc = s_ctx[warp][rOwner];
+			const uint32_t* ri = (const uint32_t*)rc;
+			const uint32_t flags = ri[VC_FLAGS];
+			const int rMajor = (int)( flags & 3u );
+			const bool flat = ( flags & 4u ) != 0; // voxelization.hpp:313-316: a one-slab box overlaps by construction
+			const V2 rorg = proj2( origin, rMajor );
+			const float org_z = projR( origin, rMajor );
+			const int ax1 = ( rMajor == 0 ) ? 1 : 0;
+			const int ax2 = ( rMajor == 2 ) ? 1 : 2;
+			int zmin = 0, zmax = -1;
+			uint32_t okMask = 0; // bit k: voxel z = zmin + k passes the overlap tests
+			const V2 o = { rorg.x + dps * rx, rorg.y + dps * y };
+			if( hasRow )
+			{
+				// zRangeInclusive( x, y ), voxelization.hpp:270-299 (no pre-clamp before the casts: x86 semantics)
+				const float var = rc[VC_KX] * o.x + rc[VC_KY] * o.y;
+				if( six )
+				{
+					const float idx = ( ( var + rc[VC_CSIX] ) - org_z ) / dps;
+					const float zf = floorf( idx );
+					const int z = f2i_x86( zf );
+					zmin = ( idx == zf ) ? z - 1 : z;
+					zmax = z;
+				}
+				else
+				{
+					zmin = f2i_x86( floorf( ( ( var + rc[VC_CMIN] ) - org_z ) / dps ) );
+					zmax = f2i_x86( floorf( ( ( var + rc[VC_CMAX] ) - org_z ) / dps ) );
+				}
+				zmin = smax( zmin, (int)ri[VC_LOZ] );
+				zmax = smin( zmax, (int)ri[VC_HIZ] );
+				// |kx|, |ky| <= 1 on the major axis, so a row holds at most 4 voxels; 8 keeps a chunk within the queue whatever happens
+				for( int z = zmin, k = 0; z <= zmax && k < 8; z++, k++ )
+				{
+					bool ok = true;
+					if( !flat )
+					{
+						const float rr = org_z + (float)z * dps;
+						const V3 p = unproj( o, rr, rMajor ); // the voxel's lower corner (voxelization.hpp:300-305)
+						const V2 pa = proj2( p, ax1 ), pb = proj2( p, ax2 );
+#pragma unroll
+						for( int e = 0; e < 3; e++ )
+						{
+							if( rc[VC_EA + e] * pa.x + rc[VC_EA + 3 + e] * pa.y + rc[VC_EA + 6 + e] < 0.0f ) ok = false;
+							if( rc[VC_EB + e] * pb.x + rc[VC_EB + 3 + e] * pb.y + rc[VC_EB + 6 + e] < 0.0f ) ok = false;
+						}
+					}
+					if( ok ) okMask |= 1u << k;
+				}
+			}
+			const uint32_t nv = __popc( okMask );
+			if( !EMIT )
+				total += nv;
+			else
+			{
+				const uint32_t vIncl = warpInclusiveScan( nv, lane );
+				const uint32_t vTotal = __shfl_sync( 0xFFFFFFFFu, vIncl, 31 );
+				if( qCount + vTotal > VW_QUEUE ) drain();
+				uint32_t at = qCount + vIncl - nv;
+				for( uint32_t m = okMask; m; m &= m - 1u )
+				{
+					const int z = zmin + ( __ffs( m ) - 1 );
+					const I3 ci = unproji( rx, y, z, rMajor );
+					s_q[EMIT ? warp : 0][EMIT ? at : 0] = (uint64_t)(uint32_t)ci.x | ( (uint64_t)(uint32_t)ci.y << 21 ) | ( (uint64_t)(uint32_t)ci.z << 42 );
+					s_qOwner[EMIT ? warp : 0][EMIT ? at : 0] = (uint8_t)rOwner;
+					at++;
+				}
+				qCount += vTotal;
+				if( qCount >= VW_QUEUE / 2 ) drain();
+			}
+		}
+	}
+	if( EMIT )
+	{
+		if( qCount ) drain();
+	}
+	else
+	{
+#pragma unroll
+		for( int o = 16; o > 0; o >>= 1 ) total += __shfl_xor_sync( 0xFFFFFFFFu, total, o );
+		if( lane == 0 ) warpCount[gw] = total;
+	}
+}
+
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
 					V3 origin, float dps, int gridRes, int sixSeparating, uint64_t** keysOut, uint64_t** valuesOut, uint64_t* D,
 					const std::function<int( int )>& beforeEmit, int emitSlices )
 {
+	// Output layout: the voxels of the small triangles first (warpVoxelsKernel; triangle-major, then x, y, z: the CPU loop's order,
+	// voxRT.cpp:198-240), then those of the large triangles (columnVoxelsKernel, same order among themselves).  The order is
+	// deterministic but unspecified for callers (the reference's is an atomicAdd race, voxKernel.cu:121); sort + unique do not care.
 	bool emitHookRun = false;
 	*D = 0;
 	if( keysOut ) *keysOut = nullptr;
 	if( valuesOut ) *valuesOut = nullptr;
 	if( nTriangles == 0 ) return beforeEmit ? beforeEmit( -1 ) : 0;
+	static const bool columnsOnly = getenv( "HAKO_VOX_COLUMNS_ONLY" ) && atoi( getenv( "HAKO_VOX_COLUMNS_ONLY" ) ) != 0; // A/B knob: the round-1 path
 	uint32_t* colOffset = nullptr;
 	uint32_t* colCount = nullptr;
-	uint64_t* totals = nullptr; // [0] columns, [1] voxels
+	uint32_t* warpCount = nullptr;
+	uint64_t* totals = nullptr; // [0] columns of the large triangles, [1] voxels of the small triangles, [2] voxels of the large ones
 	int r = 0;
 	do
 	{
+		const uint32_t nWarpBlocks = columnsOnly ? 0u : divUp( nTriangles, 32u * VW_WARPS );
+		const uint32_t nWarps = nWarpBlocks * VW_WARPS;
 		if( ( r = dalloc( ctx, &colOffset, (uint64_t)nTriangles + 1, s ) ) ) break;
-		if( ( r = dalloc( ctx, &totals, 2, s ) ) ) break;
-		HAKO_LAUNCH( ctx, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset );
+		if( ( r = dalloc( ctx, &warpCount, (uint64_t)nWarps + 1, s ) ) ) break;
+		if( ( r = dalloc( ctx, &totals, 3, s ) ) ) break;
+		cudaError_t e = cudaMemsetAsync( totals, 0, 24, s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "memset totals", __FILE__, __LINE__ );
+			break;
+		}
+		auto wCount = warpVoxelsKernel<false>;
+		auto wEmit = warpVoxelsKernel<true>;
+		if( nWarps )
+		{
+			HAKO_LAUNCH( ctx, wCount, nWarpBlocks, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, warpCount,
+						 (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
+			if( ( r = scanU32( ctx, s, warpCount, warpCount, nWarps, totals + 1 ) ) ) break;
+		}
+		HAKO_LAUNCH( ctx, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset, columnsOnly ? 0 : 1 );
 		if( ( r = scanU32( ctx, s, colOffset, colOffset, nTriangles, totals ) ) ) break;
-		// Emit slices: slice k covers the triangles [ T_k, T_k+1 ), T_k = nTriangles * k / emitSlices, i.e. the columns
-		// [ colOffset[T_k], colOffset[T_k+1] ); the caller's hook beforeEmit( k ) returns once the attributes of those triangles
-		// are on their way (ordered into `s`), so that an upload of the attribute arrays overlaps the emission of earlier slices.
-		emitSlices = std::max( 1, std::min( { emitSlices, 16, (int)std::max<uint32_t>( 1u, nTriangles / 65536u ) } ) );
-		cudaError_t e = cudaMemcpyAsync( ctx->pinned, totals, 8, cudaMemcpyDeviceToHost, s );
-		for( int k = 1; k < emitSlices && e == cudaSuccess; k++ )
-			e = cudaMemcpyAsync( (uint32_t*)( ctx->pinned + 1 ) + k, colOffset + (uint64_t)nTriangles * k / emitSlices, 4, cudaMemcpyDeviceToHost, s );
+		e = cudaMemcpyAsync( ctx->pinned, totals, 16, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
 		ctx->stats.hostSyncs++;
 		if( e != cudaSuccess )
 		{
-			r = cudaFail( e, "read column total", __FILE__, __LINE__ );
+			r = cudaFail( e, "read column / voxel totals", __FILE__, __LINE__ );
 			break;
 		}
 		const uint64_t nColumns = ctx->pinned[0];
-		uint32_t sliceColumn[17];
-		for( int k = 1; k < emitSlices; k++ ) sliceColumn[k] = ( (const uint32_t*)( ctx->pinned + 1 ) )[k];
+		const uint64_t smallVoxels = ctx->pinned[1];
 		if( nColumns >= 0xFFFFFFFFull )
 		{
 			setError( "voxelize: %llu (triangle, x) columns exceed the 32-bit work index", (unsigned long long)nColumns );
 			r = HAKO_E_LIMIT;
 			break;
 		}
-		if( nColumns == 0 ) break;
-		if( ( r = dalloc( ctx, &colCount, nColumns, s ) ) ) break;
 		auto kCount = columnVoxelsKernel<false>;
 		auto kEmit = columnVoxelsKernel<true>;
-		HAKO_LAUNCH( ctx, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
-					 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, 0u, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
-		if( ( r = scanU32( ctx, s, colCount, colCount, nColumns, totals + 1 ) ) ) break;
-		e = cudaMemcpyAsync( ctx->pinned, totals + 1, 8, cudaMemcpyDeviceToHost, s );
-		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
-		ctx->stats.hostSyncs++;
-		if( e != cudaSuccess )
+		uint64_t largeVoxels = 0;
+		if( nColumns )
 		{
-			r = cudaFail( e, "read voxel total", __FILE__, __LINE__ );
-			break;
+			// the large triangles (none in the scanned-model regime): one more pass and one more host read
+			if( ( r = dalloc( ctx, &colCount, nColumns, s ) ) ) break;
+			HAKO_LAUNCH( ctx, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
+						 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, 0u, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
+			if( ( r = scanU32( ctx, s, colCount, colCount, nColumns, totals + 2 ) ) ) break;
+			e = cudaMemcpyAsync( ctx->pinned, totals + 2, 8, cudaMemcpyDeviceToHost, s );
+			if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
+			ctx->stats.hostSyncs++;
+			if( e != cudaSuccess )
+			{
+				r = cudaFail( e, "read voxel total", __FILE__, __LINE__ );
+				break;
+			}
+			largeVoxels = ctx->pinned[0];
 		}
-		const uint64_t total = ctx->pinned[0];
+		const uint64_t total = smallVoxels + largeVoxels;
 		*D = total;
 		if( total >= 0xFFFFFFFFull )
 		{
@@ -535,27 +870,33 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		if( ( r = dalloc( ctx, keysOut, total, s ) ) ) break;
 		if( ( r = dalloc( ctx, valuesOut, total, s ) ) ) break;
 		emitHookRun = true;
-		// a block belongs to the last slice any of its columns belongs to: slice k launches the blocks that lie entirely below
-		// the first column of slice k+1 and were not launched before
-		const uint32_t nBlocks = (uint32_t)divUp( nColumns, 128 );
+		// Emit slices: slice k covers the triangles [ T_k, T_k+1 ), T_k = nTriangles * k / emitSlices -- the ranges in which the
+		// caller uploads the attribute arrays; beforeEmit( k ) returns once the attributes of slices 0..k are on their way (ordered
+		// into `s`), so the upload overlaps the emission of earlier slices.  A block of 128 triangles belongs to the last slice any
+		// of its triangles belongs to.
+		emitSlices = std::max( 1, std::min( { emitSlices, 16, (int)std::max<uint32_t>( 1u, nTriangles / 65536u ) } ) );
 		uint32_t blockBase = 0;
 		for( int k = 0; k < emitSlices && r == 0; k++ )
 		{
-			const uint32_t blockEnd = k + 1 < emitSlices ? std::min( nBlocks, sliceColumn[k + 1] / 128u ) : nBlocks;
-			if( beforeEmit && ( r = beforeEmit( k + 1 < emitSlices ? k : -1 ) ) ) break; // -1: everything (the last slice)
-			if( blockEnd > blockBase )
-				HAKO_LAUNCH( ctx, kEmit, blockEnd - blockBase, 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
-							 origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr, colCount, (uint32_t)total, *keysOut, *valuesOut, blockBase );
+			const bool last = k + 1 == emitSlices;
+			const uint32_t blockEnd = last ? nWarpBlocks : std::min<uint32_t>( nWarpBlocks, (uint32_t)( (uint64_t)nTriangles * ( k + 1 ) / emitSlices / ( 32u * VW_WARPS ) ) );
+			if( beforeEmit && ( r = beforeEmit( last ? -1 : k ) ) ) break; // -1: everything
+			if( blockEnd > blockBase && smallVoxels )
+				HAKO_LAUNCH( ctx, wEmit, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr,
+							 warpCount, *keysOut, *valuesOut, blockBase );
 			blockBase = std::max( blockBase, blockEnd );
 		}
 		if( r ) break;
+		if( largeVoxels )
+			HAKO_LAUNCH( ctx, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns, origin, dps, gridRes, sixSeparating,
+						 (uint32_t*)nullptr, colCount, (uint32_t)largeVoxels, *keysOut + smallVoxels, *valuesOut + smallVoxels, 0u );
 	} while( 0 );
 	if( beforeEmit && !emitHookRun )
 	{
 		const int rh = beforeEmit( -1 ); // the caller's upload must be joined on every path
 		if( r == 0 ) r = rh;
 	}
-	dfree( colOffset, s ), dfree( colCount, s ), dfree( totals, s );
+	dfree( colOffset, s ), dfree( colCount, s ), dfree( warpCount, s ), dfree( totals, s );
 	if( r && keysOut )
 	{
 		dfree( *keysOut, s ), dfree( *valuesOut, s );

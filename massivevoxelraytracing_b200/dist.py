@@ -75,6 +75,83 @@ def broadcast_octree(ctx, octree_cls, octree, src=0, group=None):
     return octree
 
 
+class NativeDist:
+    """The multi-GPU layer of the C ABI (include/hako.h: hako_dist_*, csrc/dist.cu) -- NCCL called from C++, no torch tensor on
+    the data path.  torch.distributed (any backend, gloo is enough) only ships the 128-byte NCCL id from rank 0 to the others,
+    as any launcher of a C++ host would."""
+
+    def __init__(self, ctx, rank=None, world=None, group=None, unique_id=None):
+        self.ctx = ctx
+        self.lib = ctx.lib
+        self.rank = dist.get_rank(group) if rank is None else int(rank)
+        self.world = dist.get_world_size(group) if world is None else int(world)
+        if unique_id is None:
+            box = [None]
+            if self.rank == 0:
+                buf = (C.c_uint8 * 128)()
+                check(self.lib.hako_dist_unique_id(buf))
+                box[0] = bytes(buf)
+            dist.broadcast_object_list(box, src=0, group=group)
+            unique_id = box[0]
+        assert len(unique_id) == 128
+        self._id = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        h = C.c_void_p()
+        check(self.lib.hako_dist_init(ctx.h, self._id, self.rank, self.world, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.hako_dist_destroy(self.h)
+            self.h = None
+
+    def nccl_version(self):
+        v = C.c_int()
+        check(self.lib.hako_dist_info(self.h, None, None, C.byref(v)))
+        return v.value
+
+    def barrier(self, stream=None):
+        check(self.lib.hako_dist_barrier(self.h, getattr(stream, "cuda_stream", stream)))
+
+    def max_f32(self, value, stream=None):
+        v = C.c_float(float(value))
+        check(self.lib.hako_dist_max_f32(self.h, getattr(stream, "cuda_stream", stream), C.byref(v)))
+        return v.value
+
+    def broadcast_octree(self, octree_cls, octree=None, src=0, stream=None):
+        """replicate the octree of rank `src`; returns an octree object on every rank (the source object itself on src).
+        The broadcast is enqueued on `stream`; synchronise before timing or destroying the source."""
+        out = C.c_void_p()
+        check(self.lib.hako_dist_broadcast_octree(self.h, getattr(stream, "cuda_stream", stream), int(src),
+                                                  octree.h if (self.rank == src and octree is not None) else None, C.byref(out)))
+        if self.rank == src:
+            return octree
+        o = octree_cls(self.ctx)
+        o._adopt(out)
+        return o
+
+    def reduce_accum(self, pt, dst=0, stream=None):
+        """sum the float4 accumulators of PathTracer `pt` onto rank dst, in place (one ncclReduce)"""
+        check(self.lib.hako_dist_reduce_accum(self.h, getattr(stream, "cuda_stream", stream), pt.h, int(dst)))
+
+    def build_sharded(self, octree_cls, tris, col, emi, origin, dps, grid, times=None, stream=None):
+        """every rank passes the SAME float32 [T, 3, 3] host arrays; rank r voxelizes triangles [T r / G, T (r+1) / G)"""
+        T = int(np.asarray(tris).reshape(-1, 9).shape[0])
+        t0, t1 = triangle_shard(T, self.rank, self.world)
+        f = lambda a: np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1, 9)[t0:t1])
+        p, c, e = f(tris), f(col), f(emi)
+        org = np.ascontiguousarray(origin, np.float32)
+        ms = (C.c_float * 6)()
+        out = C.c_void_p()
+        check(self.lib.hako_dist_build_sharded(self.h, getattr(stream, "cuda_stream", stream), p.ctypes.data, c.ctypes.data, e.ctypes.data, t1 - t0,
+                                               org.ctypes.data, float(dps), int(grid), C.byref(out), ms))
+        if times is not None:
+            for k, v in zip(("voxelize_sort_ms", "splitters_ms", "exchange_ms", "sort_unique_ms", "gather_unique_ms", "octree_ms"), ms):
+                times[k] = times.get(k, 0.0) + float(v)
+        o = octree_cls(self.ctx)
+        o._adopt(out)
+        return o
+
+
 def reduce_accum(tensor, dst=0, group=None):
     """sum the per-rank float4 accumulators onto rank dst (in place)"""
     dist.reduce(tensor, dst, op=dist.ReduceOp.SUM, group=group)

@@ -64,6 +64,12 @@ class Context:
     def launch_count(self):
         return int(self.lib.hako_ctx_launch_count(self.h))
 
+    def l2_probe(self, set_bytes=0, reps=20, stream=None):
+        """(L2 size in bytes, measured L2 read bandwidth in GB/s over a resident set) -- the roof the traversal is held against"""
+        l2, gbs = C.c_uint64(), C.c_float()
+        check(self.lib.hako_ctx_l2_probe(self.h, _stream(stream), int(set_bytes), int(reps), C.byref(l2), C.byref(gbs)))
+        return int(l2.value), float(gbs.value)
+
     def build_stats(self):
         s = BuildStats()
         check(self.lib.hako_ctx_build_stats(self.h, C.byref(s)))

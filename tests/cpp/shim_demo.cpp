@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "IntersectorOctreeGPU.hpp"
@@ -36,6 +37,107 @@ static void makeScene( std::vector<vec3>& v, std::vector<vec3>& c, std::vector<v
 			c.push_back( { 0.7f, 0.7f, 0.7f } );
 			e.push_back( { 0, 0, 0 } );
 		}
+}
+
+// stand-ins for pr::Camera3D (libs/prlib/src/pr.hpp:189-198) and pr::Image2DRGBA8, as voxPTGPU.cpp uses them
+struct Camera3D
+{
+	vec3 origin = { 4, 4, 4 };
+	vec3 lookat = { 0, 0, 0 };
+	vec3 up = { 0, 1, 0 };
+	float fovy = 45.0f * 3.14159265f / 180.0f;
+	float zNear = 0.01f;
+	float zFar = 1000.0f;
+	bool zUp = false;
+	float perspective = 1.0f;
+};
+struct Image2DRGBA8
+{
+	struct px
+	{
+		uint8_t x, y, z, w;
+	};
+	void allocate( int w, int h )
+	{
+		m_w = w, m_h = h;
+		m_data.resize( (size_t)w * h );
+	}
+	px* data() { return m_data.data(); }
+	int width() const { return m_w; }
+	int height() const { return m_h; }
+	std::vector<px> m_data;
+	int m_w = 0, m_h = 0;
+};
+
+// One thread per GPU, the north-star partition through the C ABI alone (no Python, no torch): rank 0 builds, the octree is
+// replicated with hako_dist_broadcast_octree, each rank path-traces its spp shard (iterations r, r + G, ...), ONE
+// hako_dist_reduce_accum sums the accumulators on rank 0, which compares them with its own 1-GPU render of all iterations.
+static int multiGpuSection( const std::vector<vec3>& vertices, const std::vector<vec3>& vcolors, const std::vector<vec3>& vemissions, vec3 origin, float dps, int gridRes,
+							const std::vector<float>& env, int ew, int eh, const hako_camera& cam, int W, int H )
+{
+	const int world = 2, iterations = 4;
+	hako_ctx* probe = nullptr;
+	if( hako_ctx_create( 1, &probe ) != HAKO_OK )
+	{
+		printf( "multi-GPU section skipped: %s\n", hako_last_error() );
+		return 0;
+	}
+	hako_ctx_destroy( probe );
+	uint8_t id[HAKO_DIST_ID_BYTES];
+	hako::check( hako_dist_unique_id( id ) );
+	std::vector<float> reduced( (size_t)W * H * 4 ), single( (size_t)W * H * 4 );
+	int status[2] = { 0, 0 };
+	auto rankMain = [&]( int rank ) {
+		try
+		{
+			hako::Context ctx( rank );
+			hako_dist* d = nullptr;
+			hako::check( hako_dist_init( ctx.get(), id, rank, world, &d ) );
+			IntersectorOctreeGPU built( &ctx );
+			if( rank == 0 ) built.build( vertices, vcolors, vemissions, (Shader*)nullptr, nullptr, origin, dps, gridRes );
+			hako_octree* tree = nullptr;
+			hako::check( hako_dist_broadcast_octree( d, nullptr, 0, rank == 0 ? const_cast<hako_octree*>( built.handle() ) : nullptr, &tree ) );
+			hako_pt* pt = nullptr;
+			hako::check( hako_pt_create( ctx.get(), nullptr, &pt ) );
+			hako::check( hako_pt_resize( pt, nullptr, W, H ) );
+			hako::check( hako_pt_load_hdri( pt, nullptr, env.data(), ew, eh, env.data(), ew, eh ) );
+			for( int it = rank; it < iterations; it += world ) hako::check( hako_pt_step( pt, tree, nullptr, &cam, it, 0, H, 4 ) );
+			hako::check( hako_dist_reduce_accum( d, nullptr, pt, 0 ) );
+			if( rank == 0 )
+			{
+				hako::check( hako_pt_read_accum( pt, nullptr, reduced.data() ) );
+				hako::check( hako_pt_clear( pt, nullptr ) );
+				for( int it = 0; it < iterations; it++ ) hako::check( hako_pt_step( pt, tree, nullptr, &cam, it, 0, H, 4 ) );
+				hako::check( hako_pt_read_accum( pt, nullptr, single.data() ) );
+			}
+			hako::check( hako_dist_barrier( d, nullptr ) );
+			hako_pt_destroy( pt );
+			if( rank != 0 ) hako_octree_destroy( tree );
+			hako_dist_destroy( d );
+		}
+		catch( const hako::Error& err )
+		{
+			fprintf( stderr, "rank %d: hako error %d: %s\n", rank, err.code, err.what() );
+			status[rank] = 1;
+		}
+	};
+	std::thread t1( rankMain, 1 );
+	rankMain( 0 );
+	t1.join();
+	if( status[0] || status[1] ) return 5;
+	double worst = 0.0;
+	for( size_t i = 0; i < reduced.size(); i++ )
+	{
+		if( ( i & 3 ) == 3 )
+		{
+			if( reduced[i] != single[i] || reduced[i] != 16.0f * iterations ) return 6; // spp counts add up exactly
+			continue;
+		}
+		const double den = std::fabs( single[i] ) > 1e-3 ? std::fabs( single[i] ) : 1e-3;
+		worst = std::fmax( worst, std::fabs( reduced[i] - single[i] ) / den );
+	}
+	printf( "2 GPUs, spp-sharded + ncclReduce vs 1 GPU: worst relative difference %.3g\n", worst );
+	return worst <= 1e-5 ? 0 : 7;
 }
 
 int main( int argc, char** argv )
@@ -114,7 +216,7 @@ int main( int argc, char** argv )
 		pt.loadHDRI( nullptr, env.data(), ew, eh );
 		pt.updateScene( vertices, vcolors, vemissions, nullptr, origin, dps, gridRes );
 		for( int i = 0; i < 4; i++ ) pt.step( nullptr, cam );
-		pt.toImageAsync( nullptr, image.data() );
+		pt.toImage( nullptr, image.data() );
 		std::vector<float> acc( (size_t)W * H * 4 );
 		pt.readAccumulators( nullptr, acc.data() );
 		double sum = 0;
@@ -130,6 +232,29 @@ int main( int argc, char** argv )
 				for( size_t i = 0; i < (size_t)W * H; i++ ) fwrite( &image[i * 4], 1, 3, f );
 				fclose( f );
 			}
+		}
+		// ---- the same with the reference's own argument lists, as voxPTGPU.cpp:88-91,177-193 is written ----
+		{
+			PathTracer pt2; // default-constructed, voxPTGPU.cpp:88
+			pt2.setup( nullptr, "../voxKernel.cu", "../", true );
+			pt2.resizeFrameBufferIfNeeded( nullptr, W, H );
+			pt2.loadHDRI( nullptr, env.data(), ew, eh );
+			pt2.updateScene( vertices, vcolors, vemissions, nullptr, origin, dps, gridRes );
+			Camera3D camera;
+			static Image2DRGBA8 img;
+			for( int i = 0; i < 4; i++ ) pt2.step( nullptr, camera, 6.0f, 0.02f );
+			pt2.toImageAsync( nullptr, &img );
+			hako::check( hako_ctx_synchronize( pt2.m_ctx->get(), nullptr ) ); // oroStreamSynchronize( stream ), voxPTGPU.cpp:189
+			if( img.width() != W || img.height() != H || memcmp( img.data(), image.data(), image.size() ) != 0 )
+			{
+				printf( "reference-signature PathTracer calls: image differs from the hako_camera path\n" );
+				return 8;
+			}
+			printf( "reference-signature calls ok (%d steps)\n", pt2.getSteps() );
+		}
+		{
+			const int mg = multiGpuSection( vertices, vcolors, vemissions, origin, dps, gridRes, env, ew, eh, cam, W, H );
+			if( mg ) return mg;
 		}
 		// error behaviour: gridRes must be a power of two (IntersectorOctreeGPU.hpp:48-51 abort()) -> hako::Error here
 		try

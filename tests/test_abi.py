@@ -81,7 +81,7 @@ def build_shim_demo(out_dir):
     exe = os.path.join(str(out_dir), "shim_demo")
     pkg = os.path.join(ROOT, "massivevoxelraytracing_b200")
     subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cpp", "shim_demo.cpp"),
-                    "-o", exe, "-L" + pkg, "-lhako_b200", "-Wl,-rpath," + pkg], check=True)
+                    "-o", exe, "-pthread", "-L" + pkg, "-lhako_b200", "-Wl,-rpath," + pkg], check=True)
     return exe
 
 

@@ -35,16 +35,63 @@ def _oracle_stages(oracle, tris, col, emi, grid):
 
 
 # ---------------------------------------------------------------- voxelize
-@pytest.mark.parametrize("grid", [16, 64, 256])
+def _canon(keys, color, emission):
+    """the dumped voxels as a sorted multiset of (key, colour, emission) records: the emission order is unspecified
+    (include/hako.h; the reference's own is an atomicAdd race, voxKernel.cu:121)"""
+    rec = np.empty(keys.size, np.dtype([("k", np.uint64), ("c", np.uint32), ("e", np.uint32)]))
+    rec["k"] = keys
+    rec["c"] = np.ascontiguousarray(color).view(np.uint32).reshape(-1)
+    rec["e"] = np.ascontiguousarray(emission).view(np.uint32).reshape(-1)
+    return np.sort(rec, order=("k", "c", "e"))
+
+
+def _assert_same_voxels(gk, ga, keys, c, e):
+    assert gk.size == keys.size
+    assert np.array_equal(_canon(gk, ga["color"], ga["emission"]), _canon(keys, c, e))
+
+
+@pytest.mark.parametrize("grid", [16, 64, 256, 2048])
 def test_voxelize_matches_oracle(hk, ctx, oracle, bunny, grid):
+    """16..256: every bunny triangle takes the warp-cooperative path (32 triangles per warp); 2048: a mix of that and the
+    per-column path of large triangles"""
     tris, col, emi = bunny
-    origin, dps = scene_params(tris, grid)
+    if grid == 2048:
+        tris, col, emi = tris[:600], col[:600], emi[:600]
+    origin, dps = scene_params(bunny[0], grid)
     keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), grid)
     gk, ga = ctx.voxelize(tris, col, emi, origin, float(dps), grid)
-    # emission order is deterministic here (triangle, x, y, z) == the CPU loop order (voxRT.cpp:198-240)
-    np.testing.assert_array_equal(gk, keys)
-    np.testing.assert_array_equal(ga["color"], c)
-    np.testing.assert_array_equal(ga["emission"], e)
+    _assert_same_voxels(gk, ga, keys, c, e)
+    if grid <= 256:
+        # small triangles only: the emission order is (triangle, x, y, z) == the CPU loop's order (voxRT.cpp:198-240)
+        np.testing.assert_array_equal(gk, keys)
+        np.testing.assert_array_equal(ga["color"], c)
+        np.testing.assert_array_equal(ga["emission"], e)
+
+
+def test_voxelize_paths_agree(hk, oracle, bunny, monkeypatch):
+    """HAKO_VOX_COLUMNS_ONLY=1 (one thread per (triangle, x) column for every triangle, the round-1 kernels) and the default
+    hybrid produce the same dumped voxels; both equal the oracle.  Ragged triangle counts exercise the partial last warp."""
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, 512)
+    out = []
+    for env in ("0", "1"):
+        monkeypatch.setenv("HAKO_VOX_COLUMNS_ONLY", env)
+        import subprocess, sys, os, json
+        code = ("import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+                "import massivevoxelraytracing_b200 as hk\nfrom scenes import bunny_scene, scene_params\n"
+                "t, c, e = bunny_scene(); o, d = scene_params(t, 512); ctx = hk.Context(0)\n"
+                "import hashlib\n"
+                "for n in (1, 31, 33, 1000, t.shape[0]):\n"
+                "    k, a = ctx.voxelize(t[:n], c[:n], e[:n], o, float(d), 512)\n"
+                "    r = np.empty(k.size, np.dtype([('k', np.uint64), ('a', np.uint64)])); r['k'] = k; r['a'] = a.view(np.uint64).reshape(-1)\n"
+                "    print(n, k.size, hashlib.sha1(np.sort(r, order=('k', 'a')).tobytes()).hexdigest())\n") % (
+                    os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=dict(os.environ, HAKO_VOX_COLUMNS_ONLY=env))
+        assert r.returncode == 0, r.stderr
+        out.append(r.stdout)
+    assert out[0] == out[1] and len(out[0].splitlines()) == 5
+    keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), 512)
+    assert int(out[0].splitlines()[-1].split()[1]) == keys.size
 
 
 def test_voxelize_conservative_and_degenerate(hk, ctx, oracle, bunny, small_cases):
@@ -52,8 +99,7 @@ def test_voxelize_conservative_and_degenerate(hk, ctx, oracle, bunny, small_case
     origin, dps = scene_params(tris, 64)
     keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), 64, six=False)
     gk, ga = ctx.voxelize(tris, col, emi, origin, float(dps), 64, sixSeparating=False)
-    np.testing.assert_array_equal(gk, keys)
-    np.testing.assert_array_equal(ga["color"], c)
+    _assert_same_voxels(gk, ga, keys, c, e)
     deg = small_cases["deg_tris"]
     for grid in (8, 32):
         for six in (1, 0):
@@ -72,9 +118,7 @@ def test_voxelize_out_of_range_colours(hk, ctx, oracle):
     emi = (rng.standard_normal((64, 3, 3)) * 1e12).astype(np.float32)
     keys, c, e = oracle.voxelize(tris, col, emi, np.zeros(3, np.float32), 1.0 / 32, 32)
     gk, ga = ctx.voxelize(tris, col, emi, np.zeros(3, np.float32), 1.0 / 32, 32)
-    np.testing.assert_array_equal(gk, keys)
-    np.testing.assert_array_equal(ga["color"], c)
-    np.testing.assert_array_equal(ga["emission"], e)
+    _assert_same_voxels(gk, ga, keys, c, e)
 
 
 # ---------------------------------------------------------------- sort

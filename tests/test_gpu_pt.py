@@ -215,3 +215,38 @@ def test_pt_errors(hk, ctx):
     with pytest.raises(hk.HakoError):
         p.resizeFrameBufferIfNeeded(None, 0, 16)
     p.cleanUp()
+
+
+@pytest.mark.parametrize("max_depth,rows", [(4, (0, 1080)), (8, (300, 780))])
+def test_step_matches_oracle_at_baseline_shape(hk, ctx, oracle, bunny, max_depth, rows):
+    """BASELINE config 3's shape (1920x1080, depth 4; depth 8 = the reference's loop bound) on the bunny at 1024^3 (2.1 M voxels):
+    one 16-spp step of the CUDA path against the threaded CPU restatement, same RMSE bound as the small cases.  (The restatement
+    itself is pinned against the reference's renderPT kernel at this shape in tests/test_gpu_refgpu.py.)"""
+    grid, W, H = 1024, 1920, 1080
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    hw, hh = 512, 256
+    env, envp = procedural_hdri(hw, hh), procedural_hdri(1024, 512, seed=3)
+    p = hk.PathTracer(ctx).setup()
+    p.updateScene(tris, col, emi, None, origin, float(dps), grid)
+    p.loadHDRI(None, env, envp)
+    p.maxDepth = max_depth
+    p.resizeFrameBufferIfNeeded(None, W, H)
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR=0.01)
+    y0, y1 = rows
+    p.ray_count(reset=True)
+    p.step(None, cam, rows=rows, iteration=3)
+    acc = p.accumulators()[y0:y1]
+    rays = p.ray_count()
+    _, mk, at = p.m_intersectorOctreeGPU.export(False, True, True)
+    tree = oracle.build_octree(mk, origin, float(dps), grid)
+    ocam = oracle.camera_lookat((4, 4, 4), (0, 0, 0), (0, 1, 0), None, W, H, focus=6.0, lens_r=0.01)
+    ref = np.zeros(W * H * 4, np.float32)
+    orays = oracle.pt_render(tree, at["color"], at["emission"], int(p.m_intersectorOctreeGPU.hasEmission()), ocam, W, H, 3, oracle.pmj_table(), ref,
+                             env, oracle.hdri_build_sats(env, hw, hh), (hw, hh), primary=envp, primary_wh=(1024, 512), max_depth=max_depth, y0=y0, y1=y1)
+    rel, close, exact = _compare(acc, ref.reshape(H, W, 4)[y0:y1])
+    print("1920x1080 rows %d..%d depth %d, bunny 1024^3: rel RMSE %.3g, close %.4f, bit-exact pixels %.4f, rays %d vs %d" % (y0, y1, max_depth, rel, close, exact, rays, orays))
+    assert rel <= REL_RMSE_TOL
+    assert close >= 0.95
+    assert abs(rays - orays) <= 2e-3 * orays
+    p.cleanUp()

@@ -211,3 +211,17 @@ def test_wide_index_layout_matches_reference_layout(hk, ctx, bunny, small_cases,
     # the same rays against the golden values of the reference
     assert np.array_equal(b[4][0].view(np.uint32), small_cases["rays_t"].view(np.uint32))
     assert np.array_equal(b[4][2], small_cases["rays_vindex"])
+
+
+@pytest.mark.parametrize("grid", [32, 64])
+def test_cuda_traversal_agrees_with_dense_grid_dda(hk, ctx, bunny, grid):
+    """the independent comparator (float64 Amanatides-Woo march over the dense occupancy grid, tests/dda.py) against the CUDA
+    path itself: hako_octree_build + hako_intersect_batch, no oracle involved"""
+    from dda import check_against_dda
+    tris, col, emi = bunny
+    origin, dps = scene_params(tris, grid)
+    g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
+    _, mk, _ = g.export(False, True, False)
+    compared, both = check_against_dda(lambda ro, rd: g.intersect(ro, rd), mk, origin, dps, grid, n=20000 if grid == 32 else 6000)
+    assert both > 1500
+    g.cleanUp()
