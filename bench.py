@@ -222,13 +222,41 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     ctx = hk.Context(local)
+    # the multi-GPU layer of the C ABI (hako_dist_*: NCCL called from C++); torch.distributed only ships the 128-byte id and
+    # synchronises the timed regions
+    nd = hdist.NativeDist(ctx) if world > 1 else None
     views_total = VIEWS * world
     nrays_view = W * H
+    stream = torch.cuda.current_stream()
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def max_over_ranks(x):
+        t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def device_ms(fn, reps=1):
+        """device time of fn() on the current stream, events on that stream, max over ranks"""
+        sync_all()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream)
+        sync_all()
+        return max_over_ranks(a.elapsed_time(b) / reps)
 
     # ---- build (rank 0), host-buffer call = the e2e build; then replicate ----
     build = None
     octree = None
     scene = None
+    multi = {}
     if rank == 0:
         scene = make_scene()
         tris, col, emi, origin, dps, gen_s = scene
@@ -246,78 +274,76 @@ def run_ours(args):
                  "octree_nodes": int(st["numberOfNodes"]), "sort_passes": int(st["sortPasses"]), "host_syncs": int(st["hostSyncs"]),
                  "kernel_launches": int(st["kernelLaunches"]), "mesh_generation_s": round(gen_s, 2)}
     if world > 1:
-        warm = torch.zeros(1, device=dev)
-        dist.broadcast(warm, 0)                 # communicator set-up is not part of the replication time
-        torch.cuda.synchronize(dev)
+        # replicate: hako_dist_broadcast_octree (64-byte header, then nodes + masks + attributes as one NCCL group).  A first call
+        # sizes the receivers' memory pools; the timed one is the second (device time on the stream, max over ranks)
+        src = octree
+        rep = nd.broadcast_octree(hk.IntersectorOctreeGPU, src, 0)
+        sync_all()
+        if rank != 0:
+            rep.cleanUp()
+        sync_all()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
-        octree = hdist.broadcast_octree(ctx, hk.IntersectorOctreeGPU, octree, 0)
-        dist.barrier()
-        if rank == 0:
-            build["nccl_broadcast_ms"] = (time.perf_counter() - t0) * 1e3
-        # the alternative to build-on-rank-0 + broadcast: every rank voxelizes / sorts / merges 1/N of the scene, one all-to-all by
-        # Morton range, unique voxels gathered, DAG built on every rank (massivevoxelraytracing_b200/dist.py: build_sharded).
-        # Reported beside the replicated build; the octree used below is the replicated one (they are the same bytes).
+        a.record(stream)
+        octree = nd.broadcast_octree(hk.IntersectorOctreeGPU, src, 0, stream=stream)
+        b.record(stream)
+        sync_all()
+        wall_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        bc_ms = max_over_ranks(a.elapsed_time(b))
+        bytes_ = sum(nb for _, nb in octree.device_arrays())
+        multi["octree_broadcast"] = {"device_ms": round(bc_ms, 3), "wall_ms": round(wall_ms, 3), "MB": round(bytes_ / 1e6, 1), "GBps": round(bytes_ / bc_ms / 1e6, 1)}
+        # the alternative to build-on-rank-0 + broadcast: hako_dist_build_sharded -- every rank voxelizes / sorts / merges 1/N of the
+        # scene, ONE all-to-all of the voxel pairs by Morton range, unique voxels gathered, DAG built on every rank (same bytes)
         try:
             if os.environ.get("HAKO_BENCH_SHARDED", "1") == "0":
                 raise RuntimeError("skipped (HAKO_BENCH_SHARDED=0)")
             if scene is None:
                 scene = make_scene()            # deterministic generator: every rank derives the same triangles
             tris, col, emi, origin, dps, _ = scene
-            stages = hdist.LibStages(ctx, hk.IntersectorOctreeGPU)
             best = None
             for _ in range(3):
                 times = {}
-                dist.barrier()
-                torch.cuda.synchronize(dev)
+                sync_all()
                 t0 = time.perf_counter()
-                sh = hdist.build_sharded(stages, tris, col, emi, origin, dps, GRID, times=times)
-                torch.cuda.synchronize(dev)
-                dist.barrier()
-                wall_ms = (time.perf_counter() - t0) * 1e3
+                sh = nd.build_sharded(hk.IntersectorOctreeGPU, tris, col, emi, origin, dps, GRID, times=times)
+                sync_all()
+                wall_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
                 same = int(sh.info().numberOfNodes == octree.info().numberOfNodes and sh.info().numberOfVoxels == octree.info().numberOfVoxels)
                 sh.cleanUp()
                 if best is None or wall_ms < best[0]:
                     best = (wall_ms, {k: round(v, 2) for k, v in times.items() if k.endswith("_ms")}, same)
             ok = torch.tensor([best[2]], device=dev)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-            if rank == 0:
-                build["sharded_build"] = {"e2e_ms": best[0], "phases_rank0_ms": best[1], "same_counts_as_replicated_on_every_rank": bool(ok.item()),
-                                          "what": "host triangles in -> identical octree resident on every rank; compare with e2e_host_call_ms + nccl_broadcast_ms"}
-            torch.cuda.empty_cache()
+            multi["sharded_build"] = {"e2e_ms": round(best[0], 2), "phases_rank0_ms": best[1], "same_tree_on_every_rank": bool(ok.item())}
         except Exception as exc:                # the bench line must survive a failure of this optional leg
-            if rank == 0:
-                build["sharded_build"] = {"error": repr(exc)[:300]}
+            multi["sharded_build"] = {"error": repr(exc)[:200]}
     info = octree.info()
 
+    # ---- the timed step: VIEWS full frames per GPU, device-resident ----
     my_views = rank_views(rank, world)
     cams = [hk.camera_lookat(view_eye(k, views_total), (0, 0, 0), width=W, height=H) for k in my_views]
-    # one output set per view: 16 x 24.9 MB = 398 MB per step, larger than the 126 MB L2
-    t_d = torch.empty((VIEWS, nrays_view), dtype=torch.float32, device=dev)
-    nm_d = torch.empty((VIEWS, nrays_view), dtype=torch.int32, device=dev)
-    vi_d = torch.empty((VIEWS, nrays_view), dtype=torch.int32, device=dev)
-    stream = torch.cuda.current_stream()
-    # frames alternate between two streams (what hako_render_primary_views does inside): a frame is one wave of CTAs whose
+    t_d = torch.empty((RING, nrays_view), dtype=torch.float32, device=dev)
+    nm_d = torch.empty((RING, nrays_view), dtype=torch.int32, device=dev)
+    vi_d = torch.empty((RING, nrays_view), dtype=torch.int32, device=dev)
+    # frames alternate between streams (what hako_render_primary_views does inside): a frame is one wave of CTAs whose
     # tail -- the few long rays -- would otherwise idle most SMs before the next frame starts
     n_streams = max(1, int(os.environ.get("HAKO_BENCH_STREAMS", "4")))
     sides = [torch.cuda.Stream(device=dev) for _ in range(n_streams - 1)]
     fork, joins = torch.cuda.Event(), [torch.cuda.Event() for _ in sides]
 
-    def step_device():
+    def cast_views(cam_list):
         fork.record(stream)
         for sd in sides:
             sd.wait_event(fork)
-        for i, cam in enumerate(cams):
+        for i, cam in enumerate(cam_list):
             k = i % n_streams
-            octree.render_device(cam, W, H, t=t_d[i], nMajor=nm_d[i], vIndex=vi_d[i], stream=sides[k - 1] if k else stream)
+            octree.render_device(cam, W, H, t=t_d[i % RING], nMajor=nm_d[i % RING], vIndex=vi_d[i % RING], stream=sides[k - 1] if k else stream)
         for sd, j in zip(sides, joins):
             j.record(sd)
             stream.wait_event(j)
 
-    def sync_all():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize(dev)
+    def step_device():
+        cast_views(cams)
 
     for _ in range(max(args.warmup, 3)):
         step_device()
@@ -332,62 +358,81 @@ def run_ours(args):
     e1.record(stream)
     sync_all()
     launches = ctx.launch_count - l0
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    # one frame launched ALONE (no overlap with its neighbours): the isolated-launch figure beside the overlapped one
+    alone_ms = device_ms(lambda: octree.render_device(cams[0], W, H, t=t_d[0], nMajor=nm_d[0], vIndex=vi_d[0], stream=stream), reps=10) if rank == 0 or world > 1 else None
 
-    # ---- e2e: host-buffer C-ABI call, results into pinned host memory ----
-    # headline e2e = the voxRTGPU frame (voxRTGPU.cpp:191-208): `render` -> RGBA8 image -> D2H, 4 B per ray;
-    # the hit-record variant (t / nMajor / vIndex, 12 B per ray: what the parity checks read) is timed beside it.
-    t_h = torch.empty(nrays_view, dtype=torch.float32).pin_memory().numpy()
-    nm_h = torch.empty(nrays_view, dtype=torch.int32).pin_memory().numpy()
-    vi_h = torch.empty(nrays_view, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
-    rgba_h = torch.empty(nrays_view * 4, dtype=torch.uint8).pin_memory().numpy()
+    # ---- e2e: host-buffer C-ABI calls, results into pinned host memory ----
+    # headline e2e = the voxRTGPU frame loop (voxRTGPU.cpp:150-208): `render` -> RGBA8 image -> D2H, 4 B per ray, the views of a
+    # step in CHUNK-view calls of hako_render_primary_views (frame i+1 traced while frame i is copied out, one host wait per call);
+    # the hit-record variant (t / nMajor / vIndex, 12 B per ray) and the one-synchronous-call-per-frame form are timed beside it
     import ctypes as C
-
-    # the frames of a step land in VIEWS distinct pinned host frames (hako_render_primary_views: frame i+1 is traced while
-    # frame i is copied out); the one-call-per-frame form (hako_render_primary, trace and copy of a frame in sequence) is
-    # timed beside it
-    cam_arr = (hk.Camera * VIEWS)(*cams)
-    rgba_all = torch.empty(VIEWS * nrays_view * 4, dtype=torch.uint8).pin_memory().numpy()
-    t_all = torch.empty(VIEWS * nrays_view, dtype=torch.float32).pin_memory().numpy()
-    nm_all = torch.empty(VIEWS * nrays_view, dtype=torch.int32).pin_memory().numpy()
-    vi_all = torch.empty(VIEWS * nrays_view, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+    n_chunks = (VIEWS + CHUNK - 1) // CHUNK
+    cam_chunks = [(hk.Camera * len(cams[c * CHUNK:(c + 1) * CHUNK]))(*cams[c * CHUNK:(c + 1) * CHUNK]) for c in range(n_chunks)]
+    rgba_all = torch.empty(CHUNK * nrays_view * 4, dtype=torch.uint8).pin_memory().numpy()
+    t_all = torch.empty(CHUNK * nrays_view, dtype=torch.float32).pin_memory().numpy()
+    nm_all = torch.empty(CHUNK * nrays_view, dtype=torch.int32).pin_memory().numpy()
+    vi_all = torch.empty(CHUNK * nrays_view, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+    rgba_h = rgba_all[:nrays_view * 4]
 
     def step_host_rgba():
-        hk._abi.check(ctx.lib.hako_render_primary_views(octree.h, None, cam_arr, VIEWS, W, H, 0, rgba_all.ctypes.data, None, None, None))
+        for cc in cam_chunks:
+            hk._abi.check(ctx.lib.hako_render_primary_views(octree.h, None, cc, len(cc), W, H, 0, rgba_all.ctypes.data, None, None, None))
 
     def step_host_records():
-        hk._abi.check(ctx.lib.hako_render_primary_views(octree.h, None, cam_arr, VIEWS, W, H, 0, None, t_all.ctypes.data, nm_all.ctypes.data, vi_all.ctypes.data))
+        for cc in cam_chunks:
+            hk._abi.check(ctx.lib.hako_render_primary_views(octree.h, None, cc, len(cc), W, H, 0, None, t_all.ctypes.data, nm_all.ctypes.data, vi_all.ctypes.data))
 
     def step_host_rgba_per_frame():
         for cam in cams:
             hk._abi.check(ctx.lib.hako_render_primary(octree.h, None, C.byref(cam), W, H, 0, H, 0, rgba_h.ctypes.data, None, None, None))
 
-    def time_host(fn):
+    def time_host(fn, steps):
         fn()
         sync_all()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             fn()
         sync_all()
-        ms_ = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(ms_, op=dist.ReduceOp.MAX)
-        return float(ms_.item())
+        return max_over_ranks((time.perf_counter() - t0) * 1e3) / steps
 
-    e2e_total = time_host(step_host_rgba)
-    e2e_rec_total = time_host(step_host_records)
-    e2e_frame_total = time_host(step_host_rgba_per_frame)
-    # the frames that came back are the frames the device-resident leg produced
-    e2e_parity = bool(np.array_equal(t_all.view(np.uint32), t_d.cpu().numpy().reshape(-1).view(np.uint32))
-                      and np.array_equal(vi_all, vi_d.cpu().numpy().reshape(-1).view(np.uint32)))
+    e2e_steps = max(2, min(args.steps, 10))
+    e2e_ms = time_host(step_host_rgba, e2e_steps)
+    e2e_rec_ms = time_host(step_host_records, max(2, e2e_steps // 3))
+    e2e_frame_ms = time_host(step_host_rgba_per_frame, max(2, e2e_steps // 3))
+    # the frames that came back are the frames the device-resident leg produces: the last RING views of a step
+    step_device()
+    torch.cuda.synchronize(dev)
+    last = len(cam_chunks[-1])
+    host_t = t_all[(last - RING) * nrays_view:last * nrays_view].view(np.uint32).reshape(RING, nrays_view)
+    host_vi = vi_all[(last - RING) * nrays_view:last * nrays_view].reshape(RING, nrays_view)
+    slots = [(VIEWS - RING + j) % RING for j in range(RING)]
+    e2e_parity = bool(all(np.array_equal(host_t[j], t_d[slots[j]].cpu().numpy().view(np.uint32)) and
+                          np.array_equal(host_vi[j], vi_d[slots[j]].cpu().numpy().view(np.uint32)) for j in range(RING)))
+    hits_last = int((t_d[slots[-1]] != 3.402823466e38).sum().item())
+    # the host link's own ceiling in the same run: every rank copies CHUNK frames' worth of bytes device -> pinned host with plain
+    # cudaMemcpyAsync, all ranks at once (what the e2e leg cannot exceed: the ranks of one box share the host's PCIe / memory)
+    src_d = torch.empty(CHUNK * nrays_view * 4, dtype=torch.uint8, device=dev)
+    dst_h = torch.from_numpy(rgba_all)
+
+    def d2h():
+        dst_h.copy_(src_d, non_blocking=True)
+    d2h()
+    link_ms = device_ms(d2h, reps=4)
+    host_link_gbs = CHUNK * nrays_view * 4 * world / link_ms / 1e6
+    del src_d
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    hits_view0 = int((t_d[0] != 3.402823466e38).sum().item())
 
-    # ---- path tracing leg (BASELINE config[2] shape): same octree, 1920x1080, 4 bounces, procedural 2k environment;
+    # ---- strong scaling (fixed total work split over the ranks): STRONG_VIEWS frames in total ----
+    sviews = [k for k in range(STRONG_VIEWS) if k % world == rank]
+    scams = [hk.camera_lookat(view_eye(k, STRONG_VIEWS), (0, 0, 0), width=W, height=H) for k in sviews]
+    cast_views(scams)
+    strong_ms = device_ms(lambda: cast_views(scams), reps=3)
+    multi["strong_primary"] = {"views_total": STRONG_VIEWS, "ms": round(strong_ms, 3), "mrays_per_s": round(STRONG_VIEWS * nrays_view / strong_ms / 1e3, 1),
+                               "collective": "none: frames stay on the rank that traced them"}
+
+    # ---- path tracing leg (BASELINE config[2] shape): its own octree at 8192^3, 1920x1080, 4 bounces, procedural 2k environment;
     # samples-per-pixel sharded over ranks (rank r renders iterations r, r+G, ...), ONE ncclReduce of the accumulators ----
     pt_octree = None
     pt_build_ms = None
@@ -398,28 +443,36 @@ def run_ours(args):
         t0 = time.perf_counter()
         pt_octree = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, pt_origin, float(pt_dps), PT_GRID)
         pt_build_ms = (time.perf_counter() - t0) * 1e3
-    pt_bcast_ms = None
     if world > 1:
-        dist.barrier()
-        t0 = time.perf_counter()
-        pt_octree = hdist.broadcast_octree(ctx, hk.IntersectorOctreeGPU, pt_octree, 0)
-        dist.barrier()
-        pt_bcast_ms = (time.perf_counter() - t0) * 1e3
-    pt_res = run_pt_leg(hk, hdist, ctx, pt_octree, dev, rank, world, args)
+        sync_all()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        pt_octree = nd.broadcast_octree(hk.IntersectorOctreeGPU, pt_octree, 0, stream=stream)
+        b.record(stream)
+        sync_all()
+        bc_ms = max_over_ranks(a.elapsed_time(b))
+        bytes_ = sum(nb for _, nb in pt_octree.device_arrays())
+        multi["octree_broadcast_8192"] = {"device_ms": round(bc_ms, 3), "MB": round(bytes_ / 1e6, 1), "GBps": round(bytes_ / bc_ms / 1e6, 1)}
+    pt_res = run_pt_leg(hk, hdist, nd, ctx, pt_octree, dev, rank, world, args, multi)
     if rank == 0 and pt_res is not None:
         pt_info = pt_octree.info()
         pt_res["octree"] = {"grid": PT_GRID, "voxels": int(pt_info.numberOfVoxels), "nodes": int(pt_info.numberOfNodes), "build_e2e_ms": pt_build_ms,
-                            "device_bytes": int(pt_info.deviceBytes), "nccl_broadcast_ms": pt_bcast_ms}
+                            "device_bytes": int(pt_info.deviceBytes)}
+    # the reference's own GPU kernels on this GPU, same scenes (the bar the new kernels must beat)
+    ref_gpu = run_reference_gpu(hk, ctx, octree, pt_octree, cams[0], args) if (rank == 0 and not args.no_cpu) else None
     pt_octree.cleanUp()
-    sweep = run_build_sweep(hk, ctx, scene) if (rank == 0 and not args.no_sweep) else None
+    sweep = run_build_sweep(hk, ctx, scene) if (rank == 0 and world == 1 and not args.no_sweep) else None
+    l2_bytes, l2_gbs = ctx.l2_probe(0, 20) if rank == 0 else (0, 0.0)
 
     if rank != 0:
+        if nd is not None:
+            nd.close()
         if world > 1:
             dist.destroy_process_group()
         return
     rays_step_all = nrays_view * VIEWS * world
     value = rays_step_all * args.steps / (ms_total * 1e-3) / 1e6
-    e2e_value = rays_step_all * args.steps / (e2e_total * 1e-3) / 1e6
+    e2e_value = rays_step_all / (e2e_ms * 1e-3) / 1e6
 
     # ---- CPU baseline + descents/ray + parity spot check (rank 0, N=1 only: bounded CPU work) ----
     cpu = None
@@ -430,25 +483,29 @@ def run_ours(args):
         tris, col, emi, origin, dps, _ = scene
         o, tree, mk, cpu_build = cpu_tree(port, ref, tris, col, emi, origin, dps)
         threads = host_threads()
-        cpu_cast(o, tree, views_total, range(2), threads, True)
+        sample_views = rank_views(0, 1)[::VIEWS // 64]   # 64 of the step's views spread over the orbit, row band (k mod 16) of each: 8.3 M rays
+        cpu_cast(o, tree, views_total, sample_views[:2], threads, True)
         rays_c, secs_c = 0, 0.0
         reps = 0
-        while secs_c < 3.0 and reps < 8:
-            r, s = cpu_cast(o, tree, views_total, rank_views(0, views_total // VIEWS), threads, True)
+        while secs_c < 10.0 and reps < 40:
+            r, s = cpu_cast(o, tree, views_total, sample_views, threads, True)
             rays_c += r
             secs_c += s
             reps += 1
-        r1, s1 = cpu_cast(o, tree, views_total, rank_views(0, views_total // VIEWS), 1, True)
+        r1, s1 = cpu_cast(o, tree, views_total, sample_views[:16], 1, True)
         ptree = tree if o is port else port.build_octree(mk, origin, dps, GRID)
         stats = np.zeros(4, np.uint64)
-        rs, _ = cpu_cast(port, ptree, views_total, rank_views(0, views_total // VIEWS), threads, True, stats)
+        rs, _ = cpu_cast(port, ptree, views_total, sample_views, threads, True, stats)
         dbar = float(stats[1]) / rs
         cpu = {"value": rays_c / secs_c / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference" if ref is not None else "port",
-               "sample": "row band k of view k for the %d views of a step (%d rays), repeated %d times; %d host threads over image rows" % (VIEWS, rs, reps, threads),
+               "sample": "row band (k mod %d) of view k for 64 of the step's %d views (%d rays), repeated %d times (%.1f s); %d host threads over image rows" % (
+                   REF_BANDS, VIEWS, rs, reps, secs_c, threads),
                "single_thread_mrays": r1 / s1 / 1e6, "cpu": cpu_model(), "build_ms": {k: (round(v, 1) if isinstance(v, float) else v) for k, v in cpu_build.items()},
                "traversal_stats_per_ray": {"loop_visits": float(stats[0]) / rs, "descents": dbar, "pushes": float(stats[2]) / rs, "max_stack": int(stats[3])}}
-        # parity spot check: view 0 complete, GPU (device buffers of the last step) vs the CPU reference
-        cam0 = o.camera_lookat(view_eye(0, views_total), (0, 0, 0), (0, 1, 0), None, W, H)
+        # parity spot check: view 0 complete, GPU vs the CPU reference
+        octree.render_device(cams[0], W, H, t=t_d[0], nMajor=nm_d[0], vIndex=vi_d[0], stream=stream)
+        torch.cuda.synchronize(dev)
+        cam0 = o.camera_lookat(view_eye(my_views[0], views_total), (0, 0, 0), (0, 1, 0), None, W, H)
         ct, cnm, cvi = tree.render_primary(cam0, W, H, 0, H, threads)
         parity = bool((t_d[0].cpu().numpy().view(np.uint32) == ct.view(np.uint32)).all() and (vi_d[0].cpu().numpy().view(np.uint32) == cvi).all()
                       and (nm_d[0].cpu().numpy() == cnm).all() and mk.size == info.numberOfVoxels and tree.num_nodes == info.numberOfNodes)
@@ -468,36 +525,52 @@ def run_ours(args):
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
                 "traffic": load_profile_value("render_dram_bytes_per_launch", None),
                 "algorithmic_bytes_per_ray": bytes_per_ray, "descents_per_ray": dbar, "rays_per_launch": nrays_view, "avg_launch_ms": launch_ms,
+                "avg_launch_ms_is": "timed region / launches with the frames of a step overlapped on %d streams; a frame launched ALONE is `isolated`" % n_streams,
+                "isolated": {"launch_ms": alone_ms, "achieved": nrays_view * bytes_per_ray / (alone_ms * 1e-3) / 1e9,
+                             "frac": nrays_view * bytes_per_ray / (alone_ms * 1e-3) / 1e9 / peak, "mrays_per_s": nrays_view / alone_ms / 1e3},
+                # the roof that matters while the node array fits L2: measured read bandwidth over a resident set (hako_ctx_l2_probe),
+                # against the sector-granular node traffic of the traversal (one 32-byte sector per descent + the 12-byte record)
+                "l2": {"l2_bytes": l2_bytes, "peak_gbs": l2_gbs, "peak_source": "hako_ctx_l2_probe: ld.global.cg sweep of a %d MB resident set, best of 3" % (l2_bytes // 4 // 1000000),
+                       "achieved_gbs": nrays_view * (12.0 + 32.0 * dbar) / (launch_ms * 1e-3) / 1e9,
+                       "frac": (nrays_view * (12.0 + 32.0 * dbar) / (launch_ms * 1e-3) / 1e9 / l2_gbs) if l2_gbs else None,
+                       "ncu_lts_throughput_pct": load_profile_value("render_l2_throughput_pct_of_peak", None)},
                 "ncu": {k: load_profile_value(k, None) for k in ("render_issue_active_pct", "render_lanes_active_per_instruction", "render_l2_throughput_pct_of_peak",
                                                                   "render_l1_hit_pct", "render_l2_hit_pct", "render_warp_instructions_per_launch", "source")},
                 "note": "pointer-chasing traversal with the %.0f MB octree L2-resident: the binding limit is the warp-instruction issue rate, not HBM (issue_bound below); a launch "
-                        "timed ALONE is bound by its longest rays (a ray is a serial chain of dependent node fetches; ~29 %% of such a launch the average SM idles), which is why "
-                        "the frames of a step are overlapped on several streams" % (info.numberOfNodes * 64 / 1e6)}
+                        "timed ALONE is bound by its longest rays (a ray is a serial chain of dependent node fetches), which is why the frames of a step are overlapped on several streams"
+                        % (info.numberOfNodes * 64 / 1e6)}
     winst = load_profile_value("render_warp_instructions_per_launch", None)
+    clocks = sampler.summary()
     if winst:
         # issue roofline: every SM has 4 warp schedulers issuing at most 1 warp instruction per clock
         sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
-        clocks = sampler.summary()
         mhz = float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)
         floor_ms = float(winst) / (sm_count * 4 * mhz * 1e6) * 1e3
         roofline["issue_bound"] = {"warp_instructions_per_launch": winst, "schedulers": sm_count * 4, "sm_mhz": mhz, "floor_ms_per_launch": floor_ms,
-                                   "frac": floor_ms / launch_ms, "source": "instruction count from the ncu capture named in roofline.ncu.source"}
+                                   "frac": floor_ms / launch_ms, "frac_isolated": floor_ms / alone_ms,
+                                   "source": "instruction count of view 0 from the ncu capture named in roofline.ncu.source (this round)"}
     cfg = base_config(world)
+    e2e_bytes = 4 * nrays_view * VIEWS
     line = {"metric": "Mrays/s (octree traversal, primary rays)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": cfg, "clocks": sampler.summary(),
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 60 * VIEWS, "d2h_bytes_per_step": 4 * nrays_view * VIEWS,
-                    "ms_per_step": e2e_total / args.steps,
-                    "call": "hako_render_primary_views (pinned host frames): the 16 views of a step in one call, RGBA8 frames out = the voxRTGPU frame loop (render kernel + D2H of the image, voxRTGPU.cpp:150-208), frame i+1 traced while frame i is copied",
-                    "per_frame_call": {"value": rays_step_all * args.steps / (e2e_frame_total * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_frame_total / args.steps,
-                                       "call": "hako_render_primary, one synchronous call per frame"},
+            "config": cfg, "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 60 * VIEWS, "d2h_bytes_per_step": e2e_bytes,
+                    "ms_per_step": e2e_ms, "steps_timed": e2e_steps,
+                    "host_link_gbs": host_link_gbs, "d2h_gbs": e2e_bytes * world / e2e_ms / 1e6, "frac_of_host_link": e2e_bytes * world / e2e_ms / 1e6 / host_link_gbs,
+                    "host_link_is": "all %d rank(s) copying %d MB device -> pinned host with plain cudaMemcpyAsync at the same time: the ceiling of this leg" % (world, CHUNK * nrays_view * 4 // 1000000),
+                    "call": "hako_render_primary_views (pinned host frames): the %d views of a step in %d-view calls, RGBA8 frames out = the voxRTGPU frame loop (voxRTGPU.cpp:150-208), frame i+1 traced while frame i is copied" % (VIEWS, CHUNK),
+                    "per_frame_call": {"value": rays_step_all / (e2e_frame_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_frame_ms, "call": "hako_render_primary, one synchronous call per frame"},
                     "frames_equal_device_leg": e2e_parity,
-                    "hit_records": {"value": rays_step_all * args.steps / (e2e_rec_total * 1e-3) / 1e6, "unit": "Mrays/s", "d2h_bytes_per_step": 12 * nrays_view * VIEWS,
-                                    "ms_per_step": e2e_rec_total / args.steps, "call": "same call returning t / nMajor / vIndex (12 B per ray) instead of the images"}},
-            "gpu_launches": int(launches), "roofline": roofline, "path_tracing": pt_res, "cpu_baseline": cpu, "build": build, "build_sweep": sweep,
-            "hits_view0": hits_view0,
-            "parity_vs_cpu_reference_view0": parity, "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware"}
+                    "hit_records": {"value": rays_step_all / (e2e_rec_ms * 1e-3) / 1e6, "unit": "Mrays/s", "d2h_bytes_per_step": 12 * nrays_view * VIEWS,
+                                    "ms_per_step": e2e_rec_ms, "call": "same call returning t / nMajor / vIndex (12 B per ray) instead of the images"}},
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "build": build, "build_sweep": sweep,
+            "hits_last_view": hits_last, "parity_vs_cpu_reference_view0": parity,
+            "published_reference": "1.04 Grays/s @ 8192^3 dragon on RTX 3090 Ti / RX 7900 XTX (seminar slide 66), not this metric/hardware",
+            # short blocks LAST, so that they survive a log tail: the reference's own GPU kernels on this box, path tracing, multi-GPU
+            "reference_gpu": ref_gpu, "path_tracing": pt_res, "multi_gpu": multi}
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
+    if nd is not None:
+        nd.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -508,7 +581,7 @@ PT_GRID = 8192          # BASELINE config[2]: the dragon at 8192^3
 SWEEP_GRIDS = (1024, 2048, 4096, 8192, 16384)   # BASELINE config[3]: voxelize + sort + octree build, 2^10 .. 2^14
 
 
-def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
+def run_pt_leg(hk, hdist, nd, ctx, octree, dev, rank, world, args, multi):
     import torch
     import torch.distributed as dist
     from scenes import procedural_hdri
@@ -517,19 +590,10 @@ def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
     pt.m_intersectorOctreeGPU = octree          # share the resident octree (no rebuild)
     pt.maxDepth = PT_DEPTH
     pt.resizeFrameBufferIfNeeded(None, W, H)
-    pt.loadHDRI(None, procedural_hdri(2048, 1024))
+    env = procedural_hdri(2048, 1024)
+    pt.loadHDRI(None, env, env)
     cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR=0.0)
-    ptr, nbytes = pt.accum_device()
-    acc = hdist.as_tensor(ptr, nbytes, dev).view(torch.float32)
     stream = torch.cuda.current_stream()
-    iters = hdist.spp_shard(PT_STEPS * world, rank, world)
-
-    def frame():
-        pt.clearFrameBuffer()
-        for it in iters:
-            pt.step(None, cam, iteration=it)
-        if world > 1:
-            hdist.reduce_accum(acc, 0)
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -537,50 +601,110 @@ def run_pt_leg(hk, hdist, ctx, octree, dev, rank, world, args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
-    frame()
-    sync_all()
-    pt.ray_count(reset=True)
-    l0 = ctx.launch_count
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    def mx(x, op=None):
+        t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=op or dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def frame(iters):
+        pt.clearFrameBuffer()
+        for it in iters:
+            pt.step(None, cam, iteration=it)
+        if world > 1:
+            nd.reduce_accum(pt, 0)              # hako_dist_reduce_accum: the ONE collective of the path
+
+    def timed(iters, reps):
+        frame(iters)
+        sync_all()
+        pt.ray_count(reset=True)
+        l0 = ctx.launch_count
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            frame(iters)
+        e1.record(stream)
+        sync_all()
+        return mx(e0.elapsed_time(e1) / reps), mx(pt.ray_count() / reps, dist.ReduceOp.SUM if world > 1 else None), (ctx.launch_count - l0) // reps
+
+    # weak scaling: PT_STEPS steps per rank, whatever N
+    iters = hdist.spp_shard(PT_STEPS * world, rank, world)
     reps = 3
-    e0.record(stream)
-    for _ in range(reps):
-        frame()
-    e1.record(stream)
-    sync_all()
-    ms = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
-    rays = torch.tensor([pt.ray_count() / reps], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(rays, op=dist.ReduceOp.SUM)
-    launches = (ctx.launch_count - l0) // reps
+    ms, rays, launches = timed(iters, reps)
+    spp = 16 * PT_STEPS * world
+    a = pt.accumulators() if rank == 0 else None
     # e2e: the PathTracer calls a voxPTGPU frame makes (clear, steps, reduce, toImageAsync = resolve + D2H of the RGBA8 frame)
     t0 = time.perf_counter()
     for _ in range(reps):
-        frame()
+        frame(iters)
         if rank == 0:
-            img = pt.toImageAsync()
+            pt.toImageAsync()
     sync_all()
-    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / reps], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_ms = mx((time.perf_counter() - t0) * 1e3 / reps)
+    # strong scaling: ONE 512-spp frame (STRONG_SPP_STEPS steps in total) split over the ranks, reduce included
+    s_iters = hdist.spp_shard(STRONG_SPP_STEPS, rank, world)
+    s_ms, _, _ = timed(s_iters, 2)
+    s_ok = bool((pt.accumulators()[..., 3] == 16 * STRONG_SPP_STEPS).all()) if rank == 0 else None
+    multi["strong_path_tracing"] = {"spp": 16 * STRONG_SPP_STEPS, "ms_per_frame": round(s_ms, 2), "mpaths_per_s": round(W * H * 16 * STRONG_SPP_STEPS / s_ms / 1e3, 1),
+                                    "spp_count_ok": s_ok, "collective": "ncclReduce(sum) of the 33 MB float4 accumulators (hako_dist_reduce_accum)" if world > 1 else "none (1 GPU)"}
     res = None
     if rank == 0:
-        spp = 16 * PT_STEPS * world
-        a = pt.accumulators()
         ok = bool((a[..., 3] == spp).all())
         paths = W * H * spp
         res = {"workload": "config[2]: stand-in dragon %d^3, %dx%d, maxDepth %d, procedural 2048x1024 environment (monks_forest_2k.hdr is missing), %d spp per frame = %d steps x 16 spp per GPU"
                            % (PT_GRID, W, H, PT_DEPTH, spp, PT_STEPS),
-               "ms_per_frame": float(ms.item()), "ms_per_spp_per_gpu": float(ms.item()) / (16 * PT_STEPS), "mpaths_per_s": paths / (float(ms.item()) * 1e-3) / 1e6,
-               "mrays_per_s": float(rays.item()) / (float(ms.item()) * 1e-3) / 1e6, "rays_per_path": float(rays.item()) / paths,
-               "e2e_ms_per_frame": float(e2e_ms.item()), "e2e_mpaths_per_s": paths / (float(e2e_ms.item()) * 1e-3) / 1e6, "d2h_bytes_per_frame": W * H * 4,
+               "ms_per_frame": ms, "ms_per_spp_per_gpu": ms / (16 * PT_STEPS), "mpaths_per_s": paths / (ms * 1e-3) / 1e6,
+               "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_path": rays / paths,
+               "e2e_ms_per_frame": e2e_ms, "e2e_mpaths_per_s": paths / (e2e_ms * 1e-3) / 1e6, "d2h_bytes_per_frame": W * H * 4,
                "launches_per_frame_per_gpu": int(launches), "spp_count_ok": ok, "mean_radiance": float(a[..., :3].mean() / spp),
                "collective": "ncclReduce(sum) of %d MB float4 accumulators" % (W * H * 16 // 1000000) if world > 1 else "none (1 GPU)",
                "published_reference": "12.5 ms/spp at 1920x1080, 8 bounces, 4096^3 scene, RX 7900 XTX (seminar slide 67); different scene and hardware"}
     pt.m_intersectorOctreeGPU = own
     pt.cleanUp()
     return res
+
+
+def run_reference_gpu(hk, ctx, octree, pt_octree, cam0, args):
+    """The reference's OWN kernels (voxKernel.cu compiled ahead of time for sm_100a by oracle/Makefile, launched by
+    oracle/librefgpu.so) on this GPU and these scenes, beside ours: `render` on the bench octree (view 0) and `renderPT` at depth 4
+    on the 8192^3 octree.  Test infrastructure used as a reported baseline, after the timed regions -- like cpu_baseline."""
+    try:
+        from oracle import refgpu
+        from scenes import procedural_hdri
+        if not refgpu.available():
+            return {"unavailable": "oracle/_ref/voxKernel.sm_100a.cubin not built (needs /root/reference at build time)"}
+        out = {"what": "reference voxKernel.cu kernels, nvcc -arch=sm_100a (fmad on, as the reference's nvrtc build), same octree bytes (68-byte nodes) and cameras"}
+        info = octree.info()
+        if info.wideIndex:
+            return {"unavailable": "the bench octree exceeds the reference's 24-bit node index"}
+        nodes, _, attrs = octree.export(True, False, True)
+        r = refgpu.RefGpu("default")
+        r.set_octree(nodes, attrs.view(np.uint8).reshape(-1, 8), np.array(info.lower, np.float32), np.array(info.upper, np.float32), float(info.dps), bool(info.hasEmission))
+        _, best, mean = r.render(cam0, W, H, False, reps=10)
+        ours_rgba, _, _, _ = octree.render(cam0, W, H, ids=False)
+        img, _, _ = r.render(cam0, W, H, False, reps=1)
+        out["render"] = {"ms_best": best, "ms_mean": mean, "mrays_per_s": W * H / best / 1e3, "pixels_differing_from_ours": float((img != ours_rgba).any(-1).mean())}
+        r.close()
+        del nodes, attrs
+        pinfo = pt_octree.info()
+        if not pinfo.wideIndex and refgpu.available("d4"):
+            nodes, _, attrs = pt_octree.export(True, False, True)
+            r = refgpu.RefGpu("d4")
+            r.set_octree(nodes, attrs.view(np.uint8).reshape(-1, 8), np.array(pinfo.lower, np.float32), np.array(pinfo.upper, np.float32), float(pinfo.dps), bool(pinfo.hasEmission))
+            env = procedural_hdri(2048, 1024)
+            r.load_hdri(env, env)
+            pt = hk.PathTracer(ctx).setup()
+            r.set_pmj(pt.pmj_table())
+            pt.cleanUp()
+            r.pt_resize(W, H)
+            cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR=0.0)
+            ms = [r.pt_step(cam, it) for it in range(3)]
+            acc = r.pt_accum()
+            out["renderPT"] = {"depth": PT_DEPTH, "grid": PT_GRID, "ms_per_16spp_step": min(ms), "ms_per_spp": min(ms) / 16.0, "mean_radiance": float(acc[..., :3].mean() / 48.0)}
+            r.close()
+        return out
+    except Exception as exc:
+        return {"error": repr(exc)[:300]}
 
 
 def run_build_sweep(hk, ctx, scene):

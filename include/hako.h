@@ -143,6 +143,8 @@ int hako_octree_info_get( const hako_octree* o, hako_octree_info* out );
 int hako_octree_export( const hako_octree* o, hako_stream stream, hako_node68* nodes, uint64_t* mortons, hako_voxel_attrib* attrs );
 /* IntersectorOctreeGPU::cleanUp, IntersectorOctreeGPU.hpp:26-38 */
 void hako_octree_destroy( hako_octree* o );
+/* the same without the device-wide wait: the arrays are released behind the work already queued on `stream` (frame loops) */
+void hako_octree_destroy_async( hako_octree* o, hako_stream stream );
 /* device addresses of the resident arrays (for NCCL broadcast by the host layer); sizes in bytes */
 int hako_octree_device_arrays( const hako_octree* o, void** nodes_d, uint64_t* nodeBytes, void** masks_d, uint64_t* maskBytes,
 							   void** attrs_d, uint64_t* attrBytes );

@@ -68,6 +68,7 @@ SIGNATURES = {
     "hako_octree_info_get": (i32, [vp, C.POINTER(OctreeInfo)]),
     "hako_octree_export": (i32, [vp, vp, vp, vp, vp]),
     "hako_octree_destroy": (None, [vp]),
+    "hako_octree_destroy_async": (None, [vp, vp]),
     "hako_octree_device_arrays": (i32, [vp, pp, pu64, pp, pu64, pp, pu64]),
     "hako_octree_create_replica": (i32, [vp, C.POINTER(OctreeInfo), pp]),
     "hako_voxelize": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, i32, vp, vp, u64, pu64]),

@@ -419,6 +419,7 @@ int hako_sort_unique_device( hako_ctx* ctx, hako_stream stream, uint64_t* keys_d
 	CHECK_ARG( ctx && U && ( n == 0 || ( keys_d && values_d ) ), "hako_sort_unique_device: null argument" );
 	CHECK_ARG( isPow2( gridRes ) && gridRes <= ( 1 << 21 ), "hako_sort_unique_device: bad grid" );
 	CHECK_ARG( n < 0xFFFFFFFFull, "hako_sort_unique_device: more than 2^32 - 1 pairs" );
+	CHECK_ARG( ( ( (uintptr_t)keys_d | (uintptr_t)values_d ) & 15u ) == 0, "hako_sort_unique_device: keys_d / values_d must be 16-byte aligned (the merge kernel reads pairs of keys)" );
 	*U = 0;
 	if( hasEmission ) *hasEmission = 0;
 	if( n == 0 ) return HAKO_OK;

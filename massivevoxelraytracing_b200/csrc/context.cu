@@ -36,10 +36,22 @@ __global__ void __launch_bounds__( 256 ) l2ReadKernel( const uint4* __restrict__
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
 	for( int r = 0; r < reps; r++ )
 	{
-		// a different starting phase per repetition so that consecutive sweeps do not hit the same slice at the same time
-		for( uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride )
+		// a different starting phase per repetition so that consecutive sweeps do not hit the same slice at the same time; four
+		// independent 16-byte loads in flight per thread and iteration, no integer division in the loop
+		const uint64_t off = ( (uint64_t)r * 4099u * 64u ) % n16;
+		uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+		for( ; i + 3 * stride < n16; i += 4 * stride )
 		{
-			const uint4 v = __ldcg( p + ( ( i + (uint64_t)r * 4099u ) % n16 ) );
+			uint64_t a0 = i + off, a1 = a0 + stride, a2 = a1 + stride, a3 = a2 + stride;
+			a0 -= a0 >= n16 ? n16 : 0, a1 -= a1 >= n16 ? n16 : 0, a2 -= a2 >= n16 ? n16 : 0, a3 -= a3 >= n16 ? n16 : 0;
+			const uint4 v0 = __ldcg( p + a0 ), v1 = __ldcg( p + a1 ), v2 = __ldcg( p + a2 ), v3 = __ldcg( p + a3 );
+			acc += ( v0.x ^ v0.y ^ v0.z ^ v0.w ) + ( v1.x ^ v1.y ^ v1.z ^ v1.w ) + ( v2.x ^ v2.y ^ v2.z ^ v2.w ) + ( v3.x ^ v3.y ^ v3.z ^ v3.w );
+		}
+		for( ; i < n16; i += stride )
+		{
+			uint64_t a0 = i + off;
+			a0 -= a0 >= n16 ? n16 : 0;
+			const uint4 v = __ldcg( p + a0 );
 			acc += v.x ^ v.y ^ v.z ^ v.w;
 		}
 	}
@@ -80,14 +92,32 @@ int hako_ctx_create( int device, hako_ctx** out )
 	c->device = device;
 	c->smCount = prop.multiProcessorCount;
 	c->l2Bytes = (size_t)prop.l2CacheSize;
-	HAKO_CUDA( cudaDeviceGetDefaultMemPool( &c->pool, device ) );
-	uint64_t keep = ~0ull; // never trim: steady-state rebuilds reuse the same blocks
-	HAKO_CUDA( cudaMemPoolSetAttribute( c->pool, cudaMemPoolAttrReleaseThreshold, &keep ) );
-	for( int i = 0; i < 8; i++ ) HAKO_CUDA( cudaEventCreate( &c->ev[i] ) );
-	HAKO_CUDA( cudaMallocHost( (void**)&c->pinned, 64 * sizeof( uint64_t ) ) );
-	HAKO_CUDA( cudaStreamCreateWithFlags( &c->copyStream, cudaStreamNonBlocking ) );
-	for( int i = 0; i < 2; i++ ) HAKO_CUDA( cudaStreamCreateWithFlags( &c->bandStream[i], cudaStreamNonBlocking ) );
-	for( int i = 0; i < 17; i++ ) HAKO_CUDA( cudaEventCreateWithFlags( &c->bandEv[i], cudaEventDisableTiming ) );
+	// A PRIVATE stream-ordered pool: steady-state rebuilds reuse its blocks (it is never trimmed while the context lives), the
+	// memory goes back to the driver with the context, and the process's default pool -- which torch's or anybody else's
+	// cudaMallocAsync uses -- is left alone.  One host thread per context: stats, the pinned words and the internal streams are
+	// not synchronised between threads (use one hako_ctx per thread, as tests/cpp/shim_demo.cpp does per GPU).
+	cudaError_t e2 = cudaSuccess;
+	{
+		cudaMemPoolProps props = {};
+		props.allocType = cudaMemAllocationTypePinned;
+		props.handleTypes = cudaMemHandleTypeNone;
+		props.location.type = cudaMemLocationTypeDevice;
+		props.location.id = device;
+		e2 = cudaMemPoolCreate( &c->pool, &props );
+		uint64_t keep = ~0ull;
+		if( e2 == cudaSuccess ) e2 = cudaMemPoolSetAttribute( c->pool, cudaMemPoolAttrReleaseThreshold, &keep );
+	}
+	for( int i = 0; i < 8 && e2 == cudaSuccess; i++ ) e2 = cudaEventCreate( &c->ev[i] );
+	if( e2 == cudaSuccess ) e2 = cudaMallocHost( (void**)&c->pinned, 64 * sizeof( uint64_t ) );
+	if( e2 == cudaSuccess ) e2 = cudaStreamCreateWithFlags( &c->copyStream, cudaStreamNonBlocking );
+	for( int i = 0; i < 2 && e2 == cudaSuccess; i++ ) e2 = cudaStreamCreateWithFlags( &c->bandStream[i], cudaStreamNonBlocking );
+	for( int i = 0; i < 17 && e2 == cudaSuccess; i++ ) e2 = cudaEventCreateWithFlags( &c->bandEv[i], cudaEventDisableTiming );
+	if( e2 != cudaSuccess )
+	{
+		const int r = hako::cudaFail( e2, "hako_ctx_create", __FILE__, __LINE__ );
+		hako_ctx_destroy( c ); // releases whatever was created
+		return r;
+	}
 	*out = c;
 	return HAKO_OK;
 }
@@ -106,6 +136,7 @@ void hako_ctx_destroy( hako_ctx* c )
 	if( c->copyStream ) cudaStreamDestroy( c->copyStream );
 	for( int i = 0; i < 2; i++ )
 		if( c->bandStream[i] ) cudaStreamDestroy( c->bandStream[i] );
+	if( c->pool ) cudaMemPoolDestroy( c->pool );
 	delete c;
 }
 

@@ -104,6 +104,19 @@ inline void dfree( T* p, cudaStream_t s )
 		if( le__ != cudaSuccess ) return hako::cudaFail( le__, #kernel, __FILE__, __LINE__ ); \
 	} while( 0 )
 
+// the same inside a `do { ... } while( 0 )` body (or a loop guarded by r == 0) whose owner releases resources afterwards: a launch
+// error sets r and leaves the body instead of returning past the clean-up.  One statement, safe as an unbraced if / else arm.
+#define HAKO_LAUNCH_R( ctx, r, kernel, grid, block, smem, stream, ... )                             \
+	if( ( r = [&]() -> int {                                                                        \
+			kernel<<<( grid ), ( block ), ( smem ), ( stream )>>>( __VA_ARGS__ );                   \
+			( ctx )->launches.fetch_add( 1, std::memory_order_relaxed );                            \
+			const cudaError_t le__ = cudaGetLastError();                                            \
+			return le__ == cudaSuccess ? 0 : hako::cudaFail( le__, #kernel, __FILE__, __LINE__ );   \
+		}() ) != 0 )                                                                                \
+		break;                                                                                      \
+	else                                                                                            \
+		( (void)0 )
+
 // ---- stage entry points (defined in the per-stage .cu files; all stream-ordered, device pointers) ----
 int traceImportNodes( hako_ctx* ctx, cudaStream_t s, const hako_node68* nodes68_d, uint32_t n, TraceNode* out, uint8_t* masks );
 int traceExportNodes( hako_ctx* ctx, cudaStream_t s, const TraceNode* nodes, const uint8_t* masks, uint32_t n, hako_node68* out68_d );

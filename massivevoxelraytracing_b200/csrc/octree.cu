@@ -367,7 +367,14 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 	HAKO_CUDA( cudaMemsetAsync( hist, 0, 22 * 8, s ) );
 	{
 		const uint32_t blocks = (uint32_t)min( (uint64_t)ctx->smCount * 8, ( n + 255 ) / 256 );
-		HAKO_LAUNCH( ctx, levelHistKernel, blocks, 256, 0, s, mortons, n, hist );
+		levelHistKernel<<<blocks, 256, 0, s>>>( mortons, n, hist );
+		ctx->launches.fetch_add( 1, std::memory_order_relaxed );
+		const cudaError_t le = cudaGetLastError();
+		if( le != cudaSuccess )
+		{
+			dfree( hist, s );
+			return cudaFail( le, "levelHistKernel", __FILE__, __LINE__ );
+		}
 	}
 	HAKO_CUDA( cudaMemcpyAsync( ctx->pinned, hist, 22 * 8, cudaMemcpyDeviceToHost, s ) );
 	HAKO_CUDA( cudaStreamSynchronize( s ) );
@@ -463,35 +470,35 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 				if( l == 0 )
 				{
 					CK( cudaMemsetAsync( leafTables, 0xFF, 512 * 4, s ) );
-					HAKO_LAUNCH( ctx, kLeafDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
+					HAKO_LAUNCH_R( ctx, r, kLeafDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
 								 leafTables, nodes, masks, 0u, wide );
-					HAKO_LAUNCH( ctx, leafRankKernel, 1, 256, 0, s, leafTables, leafTables + 256, nodes, masks, ls );
-					HAKO_LAUNCH( ctx, leafAssignKernel, divUp( Gl, 256 ), 256, 0, s, groupMask, Gl, leafTables + 256, nC, wide );
+					HAKO_LAUNCH_R( ctx, r, leafRankKernel, 1, 256, 0, s, leafTables, leafTables + 256, nodes, masks, ls );
+					HAKO_LAUNCH_R( ctx, r, leafAssignKernel, divUp( Gl, 256 ), 256, 0, s, groupMask, Gl, leafTables + 256, nC, wide );
 				}
 				else
 				{
-					HAKO_LAUNCH( ctx, kUpperDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
+					HAKO_LAUNCH_R( ctx, r, kUpperDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
 								 (uint32_t*)nullptr, nodes, masks, 0u, wide );
 					uint32_t tsz = 1;
 					while( tsz < 2 * (uint64_t)Gl ) tsz <<= 1;
 					CK( cudaMemsetAsync( table, 0xFF, (size_t)tsz * 4, s ) );
-					HAKO_LAUNCH( ctx, dagInsertKernel, divUp( Gl, 256 ), 256, 0, s, groupNode, Gl, table, tsz - 1 );
+					HAKO_LAUNCH_R( ctx, r, dagInsertKernel, divUp( Gl, 256 ), 256, 0, s, groupNode, Gl, table, tsz - 1 );
 					cudaFreeAsync( scanMem, s );
 					scanMem = nullptr;
 					const uint64_t tiles2 = ( (uint64_t)Gl + OB_BLOCK - 1 ) / OB_BLOCK;
 					ScanState st2;
 					if( ( r = zeroedScanState( ctx, s, tiles2, &scanMem, &st2 ) ) ) break;
-					HAKO_LAUNCH( ctx, dagLookupKernel, (uint32_t)tiles2, OB_BLOCK, 0, s, groupNode, groupMask, Gl, table, tsz - 1, st2, rep, rankOf, nodes, masks, ls, l );
-					HAKO_LAUNCH( ctx, dagAssignKernel, divUp( Gl, 256 ), 256, 0, s, rep, rankOf, groupMask, Gl, ls, l, nC, wide );
+					HAKO_LAUNCH_R( ctx, r, dagLookupKernel, (uint32_t)tiles2, OB_BLOCK, 0, s, groupNode, groupMask, Gl, table, tsz - 1, st2, rep, rankOf, nodes, masks, ls, l );
+					HAKO_LAUNCH_R( ctx, r, dagAssignKernel, divUp( Gl, 256 ), 256, 0, s, rep, rankOf, groupMask, Gl, ls, l, nC, wide );
 				}
 			}
 			else
 			{
 				if( l == 0 )
-					HAKO_LAUNCH( ctx, kLeafNaive, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
+					HAKO_LAUNCH_R( ctx, r, kLeafNaive, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
 								 (uint32_t*)nullptr, nodes, masks, naiveBase, wide );
 				else
-					HAKO_LAUNCH( ctx, kUpperNaive, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
+					HAKO_LAUNCH_R( ctx, r, kUpperNaive, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
 								 (uint32_t*)nullptr, nodes, masks, naiveBase, wide );
 				naiveBase += Gl;
 			}
@@ -519,7 +526,7 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 		if( wide )
 		{
 			if( nNodes < 0xFFFFFFu && !forceWide )
-				HAKO_LAUNCH( ctx, embedMasksKernel, divUp( (uint64_t)nNodes * 8, 256 ), 256, 0, s, nodes, masks, nNodes );
+				HAKO_LAUNCH_R( ctx, r, embedMasksKernel, divUp( (uint64_t)nNodes * 8, 256 ), 256, 0, s, nodes, masks, nNodes );
 			else
 				stayWide = 1;
 		}

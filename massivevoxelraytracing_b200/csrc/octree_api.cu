@@ -2,6 +2,7 @@
 // (IntersectorOctreeGPU.hpp:21-275 and IntersectorOctree.hpp:214-266 are the reference surfaces.)
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "internal.cuh"
 
@@ -30,12 +31,55 @@ int hako_octree_import( hako_ctx* ctx, hako_stream stream, const hako_node68* no
 		hako::setError( "hako_octree_import: %u nodes exceed the 24-bit node index (voxCommon.hpp:183-195)", nNodes );
 		return HAKO_E_LIMIT;
 	}
+	// The traversal indexes nodes[child & 0xFFFFFF] and pushes one stack entry per level without bounds checks, so a tree from
+	// outside is validated before it is uploaded: every child index is smaller than its parent's (the bottom-up numbering of
+	// IntersectorOctree.hpp:11-123; it also rules out cycles), the mask embedded in a child pointer is the child's own mask byte
+	// (voxCommon.hpp:183-195), a present child has its bit in the parent's mask, and the tree is at most 21 levels deep.
+	int depthOfRoot = 0;
+	{
+		std::vector<uint8_t> depth( nNodes, 1 );
+		for( uint32_t i = 0; i < nNodes; i++ )
+		{
+			uint32_t dmax = 0;
+			for( int c = 0; c < 8; c++ )
+			{
+				const uint32_t ch = nodes[i].children[c];
+				if( ch == 0xFFFFFFFFu ) continue;
+				const uint32_t idx = ch & 0xFFFFFFu;
+				if( idx >= i )
+				{
+					hako::setError( "hako_octree_import: node %u child %d points at node %u (children must precede their parent)", i, c, idx );
+					return HAKO_E_INVALID;
+				}
+				if( ( ch >> 24 ) != nodes[idx].mask )
+				{
+					hako::setError( "hako_octree_import: node %u child %d carries mask 0x%02x but node %u has mask 0x%02x (embedMasks, voxCommon.hpp:183-195)", i, c, ch >> 24, idx,
+									nodes[idx].mask );
+					return HAKO_E_INVALID;
+				}
+				if( !( ( nodes[i].mask >> c ) & 1u ) )
+				{
+					hako::setError( "hako_octree_import: node %u has child %d but its mask 0x%02x does not", i, c, nodes[i].mask );
+					return HAKO_E_INVALID;
+				}
+				dmax = depth[idx] > dmax ? depth[idx] : dmax;
+			}
+			if( dmax + 1 > 21 )
+			{
+				hako::setError( "hako_octree_import: the tree is deeper than 21 levels at node %u (morton.hpp:73: 21 bits per axis)", i );
+				return HAKO_E_INVALID;
+			}
+			depth[i] = (uint8_t)( dmax + 1 );
+		}
+		if( nNodes ) depthOfRoot = depth[nNodes - 1];
+	}
 	cudaStream_t s = (cudaStream_t)stream;
 	HAKO_CUDA( cudaSetDevice( ctx->device ) );
 	hako_octree* o = new hako_octree();
 	o->ctx = ctx;
 	o->numberOfNodes = nNodes;
 	o->numberOfVoxels = nVoxels;
+	o->gridRes = depthOfRoot ? ( 1 << depthOfRoot ) : 0; // levels below the root = log2( gridRes )
 	o->lower = { lower[0], lower[1], lower[2] };
 	o->upper = { upper[0], upper[1], upper[2] };
 	o->dps = dps;
@@ -156,6 +200,16 @@ void hako_octree_destroy( hako_octree* o )
 	if( o->masks ) cudaFree( o->masks );
 	if( o->attrs ) cudaFree( o->attrs );
 	if( o->mortons ) cudaFree( o->mortons );
+	delete o;
+}
+
+// the same, stream-ordered: the arrays go back to the pool behind the work already queued on `stream` (no device-wide wait)
+void hako_octree_destroy_async( hako_octree* o, hako_stream stream )
+{
+	if( !o ) return;
+	cudaSetDevice( o->ctx->device );
+	cudaStream_t s = (cudaStream_t)stream;
+	dfree( o->nodes, s ), dfree( o->masks, s ), dfree( o->attrs, s ), dfree( o->mortons, s );
 	delete o;
 }
 

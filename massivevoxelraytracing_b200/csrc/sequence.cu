@@ -7,6 +7,7 @@
 //                                            frame and writes NNN.png while the next frame is already building / rendering.
 //                                            Headless: there is no window to present to.
 #include <condition_variable>
+#include <cstdlib>
 #include <deque>
 #include <mutex>
 #include <string>
@@ -73,7 +74,12 @@ struct hako_seq
 	hako_pt* pt = nullptr;
 	hako_ctx* ctx = nullptr;
 	int w = 0, h = 0;
-	cudaStream_t stream = nullptr; // build + render
+	// Two streams (RTCamp.cpp:138-196 runs everything on one): frame f's clear / steps / resolve / download are only ENQUEUED on
+	// `stream`, so the host returns at once and updateScene( f + 1 ) -- voxelize, sort, unique, octree on `buildStream`, with its
+	// host waits -- runs on the GPU beside the rendering of frame f.  HAKO_SEQ_OVERLAP=0: one stream, the A/B reference.
+	cudaStream_t stream = nullptr;		// render
+	cudaStream_t buildStream = nullptr; // build (== stream when overlap is off)
+	bool overlap = true;
 	hako_octree* octree = nullptr; // the scene of the frame in flight
 	struct Slot
 	{
@@ -96,7 +102,7 @@ struct hako_seq
 	bool quit = false;
 	int writeErrors = 0;
 	std::vector<std::thread> writers;
-	cudaEvent_t ev[3] = {};
+	cudaEvent_t ev[4] = {};
 };
 
 static void writerLoop( hako_seq* q )
@@ -209,8 +215,12 @@ int hako_seq_create( hako_pt* pt, int nBuffers, int nWriters, hako_seq** out )
 	cudaSetDevice( q->ctx->device );
 	nBuffers = std::max( 1, std::min( nBuffers > 0 ? nBuffers : 4, 16 ) ); // RTCamp.cpp:127-131 pools 4
 	nWriters = std::max( 1, std::min( nWriters > 0 ? nWriters : 2, 16 ) );
+	const char* ov = getenv( "HAKO_SEQ_OVERLAP" );
+	q->overlap = !( ov && atoi( ov ) == 0 );
 	cudaError_t e = cudaStreamCreateWithFlags( &q->stream, cudaStreamNonBlocking );
-	for( int i = 0; i < 3 && e == cudaSuccess; i++ ) e = cudaEventCreate( &q->ev[i] );
+	if( e == cudaSuccess && q->overlap ) e = cudaStreamCreateWithFlags( &q->buildStream, cudaStreamNonBlocking );
+	if( !q->overlap ) q->buildStream = q->stream;
+	for( int i = 0; i < 4 && e == cudaSuccess; i++ ) e = cudaEventCreate( &q->ev[i] );
 	q->slots.resize( nBuffers );
 	for( int i = 0; i < nBuffers && e == cudaSuccess; i++ )
 	{
@@ -248,13 +258,15 @@ int hako_seq_render_frame( hako_seq* q, const float* pos, const float* col, cons
 		return HAKO_E_INVALID;
 	}
 	HAKO_CUDA( cudaSetDevice( q->ctx->device ) );
-	cudaStream_t s = q->stream;
-	HAKO_CUDA( cudaEventRecord( q->ev[0], s ) );
+	cudaStream_t s = q->stream, bs = q->buildStream;
+	HAKO_CUDA( cudaEventRecord( q->ev[0], bs ) );
 	hako_octree* next = nullptr;
-	HAKO_TRY( hako_octree_build( q->ctx, s, pos, col, emi, nTriangles, origin, dps, gridRes, &next ) ); // PathTracer::updateScene
-	if( q->octree ) hako_octree_destroy( q->octree ); // frees are stream-ordered behind the previous frame's kernels
+	HAKO_TRY( hako_octree_build( q->ctx, bs, pos, col, emi, nTriangles, origin, dps, gridRes, &next ) ); // PathTracer::updateScene; the previous frame may still be rendering
+	HAKO_CUDA( cudaEventRecord( q->ev[1], bs ) );
+	HAKO_CUDA( cudaStreamWaitEvent( s, q->ev[1], 0 ) );
+	if( q->octree ) hako_octree_destroy_async( q->octree, s ); // stream-ordered behind the previous frame's kernels: no device-wide wait
 	q->octree = next;
-	HAKO_CUDA( cudaEventRecord( q->ev[1], s ) );
+	HAKO_CUDA( cudaEventRecord( q->ev[3], s ) );
 	HAKO_TRY( hako_pt_clear( q->pt, s ) );
 	for( int it = 0; it < iterations; it++ ) HAKO_TRY( hako_pt_step( q->pt, q->octree, s, cam, it, 0, q->h, maxDepth ) );
 	HAKO_TRY( hako_pt_resolve( q->pt, s ) );
@@ -289,7 +301,7 @@ int hako_seq_render_frame( hako_seq* q, const float* pos, const float* col, cons
 	{
 		HAKO_CUDA( cudaEventSynchronize( q->ev[2] ) );
 		if( updateMs ) cudaEventElapsedTime( updateMs, q->ev[0], q->ev[1] );
-		if( renderMs ) cudaEventElapsedTime( renderMs, q->ev[1], q->ev[2] );
+		if( renderMs ) cudaEventElapsedTime( renderMs, q->ev[3], q->ev[2] );
 	}
 	return HAKO_OK;
 }
@@ -329,8 +341,9 @@ void hako_seq_destroy( hako_seq* q )
 		cudaFreeHost( s.host );
 		cudaEventDestroy( s.ready );
 	}
-	for( int i = 0; i < 3; i++ ) cudaEventDestroy( q->ev[i] );
+	for( int i = 0; i < 4; i++ ) cudaEventDestroy( q->ev[i] );
 	cudaStreamSynchronize( q->stream );
+	if( q->overlap && q->buildStream ) cudaStreamDestroy( q->buildStream );
 	cudaStreamDestroy( q->stream );
 	delete q;
 }

@@ -601,13 +601,13 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 		const uint32_t histBlocks = (uint32_t)min( (uint64_t)ctx->smCount * 8, ( n + SORT_BLOCK * 8 - 1 ) / ( SORT_BLOCK * 8 ) );
 		if( rbits == 9 )
 		{
-			HAKO_LAUNCH( ctx, sortHistogramKernel<9>, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
-			HAKO_LAUNCH( ctx, sortScanHistogramKernel<9>, passes, RADIX, 0, s, hist );
+			HAKO_LAUNCH_R( ctx, r, sortHistogramKernel<9>, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
+			HAKO_LAUNCH_R( ctx, r, sortScanHistogramKernel<9>, passes, RADIX, 0, s, hist );
 		}
 		else
 		{
-			HAKO_LAUNCH( ctx, sortHistogramKernel<8>, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
-			HAKO_LAUNCH( ctx, sortScanHistogramKernel<8>, passes, RADIX, 0, s, hist );
+			HAKO_LAUNCH_R( ctx, r, sortHistogramKernel<8>, histBlocks, SORT_BLOCK, 0, s, keys, n, beginBit, endBit, passes, hist );
+			HAKO_LAUNCH_R( ctx, r, sortScanHistogramKernel<8>, passes, RADIX, 0, s, hist );
 		}
 		uint64_t *kin = keys, *vin = values, *kout = keysTmp, *vout = valuesTmp;
 		for( int p = 0; p < passes; p++ )
@@ -625,7 +625,7 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 			if( occ == 3 ) k = rbits == 9 ? ( values ? onesweepKernel<9, true, 3> : onesweepKernel<9, false, 3> ) : ( values ? onesweepKernel<8, true, 3> : onesweepKernel<8, false, 3> );
 			if( occ == 4 ) k = rbits == 9 ? ( values ? onesweepKernel<9, true, 4> : onesweepKernel<9, false, 4> ) : ( values ? onesweepKernel<8, true, 4> : onesweepKernel<8, false, 4> );
 			if( variant == 0 )
-				HAKO_LAUNCH( ctx, k, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
+				HAKO_LAUNCH_R( ctx, r, k, (uint32_t)tiles, SORT_BLOCK, 0, s, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
 							 lookback + (size_t)p * tiles * RADIX, tickets + p );
 			else if( ( r = launchBulkPass( ctx, s, variant, rbits, values != nullptr, (uint32_t)tiles, kin, vin, kout, vout, n, shift, mask, hist + (size_t)p * RADIX,
 										  lookback + (size_t)p * tiles * RADIX, tickets + p ) ) )
@@ -635,6 +635,7 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 			t = vin;
 			vin = vout, vout = t;
 		}
+		if( r ) break;
 		if( kin != keys )
 		{
 			if( resultInTmp )

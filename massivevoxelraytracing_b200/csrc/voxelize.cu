@@ -815,11 +815,11 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		auto wEmit = warpVoxelsKernel<true>;
 		if( nWarps )
 		{
-			HAKO_LAUNCH( ctx, wCount, nWarpBlocks, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, warpCount,
+			HAKO_LAUNCH_R( ctx, r, wCount, nWarpBlocks, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, warpCount,
 						 (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
 			if( ( r = scanU32( ctx, s, warpCount, warpCount, nWarps, totals + 1 ) ) ) break;
 		}
-		HAKO_LAUNCH( ctx, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset, columnsOnly ? 0 : 1 );
+		HAKO_LAUNCH_R( ctx, r, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset, columnsOnly ? 0 : 1 );
 		if( ( r = scanU32( ctx, s, colOffset, colOffset, nTriangles, totals ) ) ) break;
 		e = cudaMemcpyAsync( ctx->pinned, totals, 16, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
@@ -844,7 +844,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		{
 			// the large triangles (none in the scanned-model regime): one more pass and one more host read
 			if( ( r = dalloc( ctx, &colCount, nColumns, s ) ) ) break;
-			HAKO_LAUNCH( ctx, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
+			HAKO_LAUNCH_R( ctx, r, kCount, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns,
 						 origin, dps, gridRes, sixSeparating, colCount, (const uint32_t*)nullptr, 0u, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
 			if( ( r = scanU32( ctx, s, colCount, colCount, nColumns, totals + 2 ) ) ) break;
 			e = cudaMemcpyAsync( ctx->pinned, totals + 2, 8, cudaMemcpyDeviceToHost, s );
@@ -882,13 +882,13 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 			const uint32_t blockEnd = last ? nWarpBlocks : std::min<uint32_t>( nWarpBlocks, (uint32_t)( (uint64_t)nTriangles * ( k + 1 ) / emitSlices / ( 32u * VW_WARPS ) ) );
 			if( beforeEmit && ( r = beforeEmit( last ? -1 : k ) ) ) break; // -1: everything
 			if( blockEnd > blockBase && smallVoxels )
-				HAKO_LAUNCH( ctx, wEmit, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr,
+				HAKO_LAUNCH_R( ctx, r, wEmit, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr,
 							 warpCount, *keysOut, *valuesOut, blockBase );
 			blockBase = std::max( blockBase, blockEnd );
 		}
 		if( r ) break;
 		if( largeVoxels )
-			HAKO_LAUNCH( ctx, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns, origin, dps, gridRes, sixSeparating,
+			HAKO_LAUNCH_R( ctx, r, kEmit, divUp( nColumns, 128 ), 128, 0, s, pos, col, emi, nTriangles, colOffset, (uint32_t)nColumns, origin, dps, gridRes, sixSeparating,
 						 (uint32_t*)nullptr, colCount, (uint32_t)largeVoxels, *keysOut + smallVoxels, *valuesOut + smallVoxels, 0u );
 	} while( 0 );
 	if( beforeEmit && !emitHookRun )

@@ -109,6 +109,39 @@ def test_export_roundtrip(hk, ctx, oracle, bunny):
     assert g.hasEmission() == bool(me[:, :3].any())
 
 
+def test_import_validates_and_accepts_any_float_sequence(hk, ctx, oracle, bunny):
+    """hako_octree_import rejects trees the traversal could not walk safely (child index not below its parent, embedded mask that
+    is not the child's mask, a child without its mask bit), and lower / upper may be tuples or float64 arrays (the binding keeps
+    the converted arrays alive across the call)"""
+    tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 32)
+    lo, up = tree.bounds()
+    nodes = tree.nodes()
+    g = hk.IntersectorOctreeGPU(ctx)
+    g.import_nodes(nodes, tuple(float(x) for x in lo), np.asarray(up, np.float64), float(dps))
+    i = g.info()
+    assert np.array_equal(np.array(i.lower, np.float32), lo) and np.array_equal(np.array(i.upper, np.float32), up)
+    assert i.gridRes == 32
+    ro = np.array([[4.0, 4.0, 4.0]], np.float32)
+    rd = np.array([[-1.0, -1.0, -1.0]], np.float32)
+    t, nm, vi = g.intersect(ro, rd)
+    ot, onm, ovi = tree.intersect(ro, rd)
+    assert t.view(np.uint32)[0] == ot.view(np.uint32)[0] and vi[0] == ovi[0]
+    g.cleanUp()
+    root = nodes.size - 1
+    c = int(np.nonzero(nodes["children"][root] != 0xFFFFFFFF)[0][0])
+    for kind in ("forward", "mask", "bit"):
+        bad = nodes.copy()
+        if kind == "forward":
+            bad["children"][5][0] = np.uint32(root | (int(nodes["mask"][root]) << 24))       # a cycle / forward reference
+            bad["mask"][5] |= 1
+        elif kind == "mask":
+            bad["children"][root][c] ^= np.uint32(1 << 24)                                   # embedded mask != the child's mask
+        else:
+            bad["mask"][root] &= np.uint8(~(1 << c) & 0xFF)                                  # child present, mask bit clear
+        with pytest.raises(hk.HakoError):
+            hk.IntersectorOctreeGPU(ctx).import_nodes(bad, lo, up, float(dps))
+
+
 def test_random_rays_and_shadow(hk, ctx, oracle, bunny, small_cases):
     s = small_cases
     tree, mk, mc, me, origin, dps = _oracle_tree(oracle, bunny, 64)
