@@ -461,6 +461,15 @@ def run_ours(args):
     # the reference's own GPU kernels on this GPU, same scenes (the bar the new kernels must beat)
     ref_gpu = run_reference_gpu(hk, ctx, octree, pt_octree, cams[0], args) if (rank == 0 and not args.no_cpu) else None
     pt_octree.cleanUp()
+    # BASELINE config[4] (the massive scene, 8 GPUs): on by default when the job has 8 ranks, HAKO_BENCH_MASSIVE=1 / 0 overrides
+    want_massive = os.environ.get("HAKO_BENCH_MASSIVE", "1" if world == 8 else "0") == "1"
+    if want_massive:
+        octree_keep = octree
+        try:
+            multi["massive_32768"] = run_massive_leg(hk, hdist, nd, ctx, dev, rank, world, scene)
+        except Exception as exc:
+            multi["massive_32768"] = {"error": repr(exc)[:200]}
+        octree = octree_keep
     sweep = run_build_sweep(hk, ctx, scene) if (rank == 0 and world == 1 and not args.no_sweep) else None
     l2_bytes, l2_gbs = ctx.l2_probe(0, 20) if rank == 0 else (0, 0.0)
 
@@ -662,6 +671,96 @@ def run_pt_leg(hk, hdist, nd, ctx, octree, dev, rank, world, args, multi):
     pt.m_intersectorOctreeGPU = own
     pt.cleanUp()
     return res
+
+
+def run_massive_leg(hk, hdist, nd, ctx, dev, rank, world, scene):
+    """BASELINE config[4], scaled to the 32-bit voxel counters of the reference format: the stand-in dragon at 32768^3 -- billions of
+    surface voxels, a wide-index octree of ~47 GB -- built on rank 0, replicated to every GPU over NVLink (hako_dist_broadcast_octree),
+    then a 3840x2160 primary frame per GPU and 4K path tracing with the spp sharded over the ranks and one ncclReduce."""
+    import torch
+    import torch.distributed as dist
+    from scenes import procedural_hdri, scene_params
+    MW, MH, MG = 3840, 2160, 32768
+    stream = torch.cuda.current_stream()
+    out = {"grid": MG, "image": [MW, MH]}
+
+    def mx(x):
+        t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    g = None
+    if rank == 0:
+        tris, col, emi, _, _, _ = scene
+        origin, dps = scene_params(tris, MG)
+        t0 = time.perf_counter()
+        g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), MG)
+        out["build_host_call_ms"] = round((time.perf_counter() - t0) * 1e3, 1)
+        st = ctx.build_stats()
+        info = g.info()
+        out["voxels"], out["nodes"], out["wide_index"], out["device_GB"] = int(info.numberOfVoxels), int(info.numberOfNodes), int(info.wideIndex), round(info.deviceBytes / 1e9, 2)
+        out["build_device_ms"] = {k: round(st[k], 1) for k in ("ms_voxelize", "ms_sort", "ms_unique", "ms_octree", "ms_total")}
+    if world > 1:
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        g = nd.broadcast_octree(hk.IntersectorOctreeGPU, g, 0, stream=stream)
+        b.record(stream)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        ms = mx(a.elapsed_time(b))
+        nbytes = sum(nb for _, nb in g.device_arrays())
+        out["broadcast"] = {"device_ms": round(ms, 1), "GB": round(nbytes / 1e9, 2), "GBps": round(nbytes / ms / 1e6, 1)}
+    cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=MW, height=MH, focus=6.0, lensR=0.0)
+    t_d = torch.empty(MW * MH, dtype=torch.float32, device=dev)
+    nm_d = torch.empty(MW * MH, dtype=torch.int32, device=dev)
+    vi_d = torch.empty(MW * MH, dtype=torch.int32, device=dev)
+    for _ in range(3):
+        g.render_device(cam, MW, MH, t=t_d, nMajor=nm_d, vIndex=vi_d, stream=stream)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(10):
+        g.render_device(cam, MW, MH, t=t_d, nMajor=nm_d, vIndex=vi_d, stream=stream)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = mx(e0.elapsed_time(e1) / 10)
+    out["primary_4k"] = {"ms_per_frame_per_gpu": round(ms, 3), "mrays_per_s_all_gpus": round(MW * MH * world / ms / 1e3, 1), "hits": int((t_d != 3.402823466e38).sum().item())}
+    pt = hk.PathTracer(ctx).setup()
+    own = pt.m_intersectorOctreeGPU
+    pt.m_intersectorOctreeGPU = g
+    pt.maxDepth = 4
+    pt.resizeFrameBufferIfNeeded(None, MW, MH)
+    env = procedural_hdri(2048, 1024)
+    pt.loadHDRI(None, env, env)
+    iters = hdist.spp_shard(4 * world, rank, world)
+
+    def frame():
+        pt.clearFrameBuffer()
+        for it in iters:
+            pt.step(None, cam, iteration=it)
+        if world > 1:
+            nd.reduce_accum(pt, 0)
+    frame()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    e0.record(stream)
+    frame()
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = mx(e0.elapsed_time(e1))
+    spp = 64 * world
+    out["pt_4k"] = {"spp": spp, "ms_per_frame": round(ms, 1), "mpaths_per_s": round(MW * MH * spp / ms / 1e3, 1)}
+    if rank == 0:
+        acc = pt.accumulators()
+        out["pt_4k"]["spp_count_ok"] = bool((acc[..., 3] == spp).all())
+        out["pt_4k"]["mean_radiance"] = round(float(acc[..., :3].mean() / spp), 4)
+    pt.m_intersectorOctreeGPU = own
+    pt.cleanUp()
+    g.cleanUp()
+    del t_d, nm_d, vi_d
+    return out
 
 
 def run_reference_gpu(hk, ctx, octree, pt_octree, cam0, args):

@@ -62,6 +62,8 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 	initOctree( o, ctx, origin, dps, gridRes );
 	uint64_t *keys = nullptr, *values = nullptr, *keysTmp = nullptr, *valuesTmp = nullptr;
 	bool mergeCountersPending = false;
+	uint64_t levelBoundaries[22] = {};
+	bool haveLevels = false;
 	int r = 0;
 	do
 	{
@@ -97,7 +99,8 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 			else
 				keysTmp = valuesTmp = nullptr;
 			uint64_t runs = 0;
-			if( ( r = countRunsDevice( ctx, s, sk, D, &runs ) ) ) break;
+			if( ( r = countRunsDevice( ctx, s, sk, D, &runs, levelBoundaries ) ) ) break;
+			haveLevels = true;
 			if( ( r = dalloc( ctx, &o->mortons, runs, s ) ) ) break;
 			if( ( r = dalloc( ctx, &o->attrs, runs, s ) ) ) break;
 			// the merge's own counters (U again, hasEmission) are read with the end-of-build synchronisation: no host wait here  (pinned slots 32 / 33: the octree stage uses 0..21)
@@ -129,7 +132,7 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 		}
 		o->numberOfVoxels = (uint32_t)U;
 		CK( cudaEventRecord( ctx->ev[4], s ) );
-		if( ( r = buildOctreeDevice( ctx, s, o->mortons, U, gridRes, 1, &o->nodes, &o->masks, &o->numberOfNodes, nullptr, &o->wide ) ) ) break;
+		if( ( r = buildOctreeDevice( ctx, s, o->mortons, U, gridRes, 1, &o->nodes, &o->masks, &o->numberOfNodes, nullptr, &o->wide, haveLevels ? levelBoundaries : nullptr ) ) ) break;
 		st.numberOfNodes = o->numberOfNodes;
 		CK( cudaEventRecord( ctx->ev[5], s ) );
 		CK( cudaStreamSynchronize( s ) );

@@ -151,10 +151,11 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 // unique.cu
 int uniqueMergeLaunch( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
 					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, unsigned long long* counters_d ); // stream-ordered, no host wait
-int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64_t n, uint64_t* U ); // distinct keys of a sorted array (synchronises)
+int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64_t n, uint64_t* U, uint64_t* levelBoundaries = nullptr ); // distinct keys + per-level boundary counts of a sorted array (synchronises)
 int uniqueMergeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,
 					   uint64_t* keysOut, hako_voxel_attrib* attrsOut, uint64_t* U, uint32_t* hasEmission );
 // octree.cu
+// levelBoundaries: null, or the 22 per-level boundary counts of the key list (countRunsDevice) -- then the stage needs no host read of its own
 int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, uint64_t n, int gridRes, int dag,
-					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodes, uint32_t* launchesOut, int* wideOut );
+					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodes, uint32_t* launchesOut, int* wideOut, const uint64_t* levelBoundaries = nullptr );
 } // namespace hako

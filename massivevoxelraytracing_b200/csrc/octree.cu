@@ -345,7 +345,7 @@ int zeroedScanState( hako_ctx* ctx, cudaStream_t s, uint64_t tiles, void** mem, 
 } // namespace
 
 int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, uint64_t n, int gridRes, int dag,
-					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodesOut, uint32_t* launchesOut, int* wideOut )
+					   TraceNode** nodesOut, uint8_t** masksOut, uint32_t* nNodesOut, uint32_t* launchesOut, int* wideOut, const uint64_t* levelBoundaries )
 {
 	if( wideOut ) *wideOut = 0;
 	*nodesOut = nullptr;
@@ -361,11 +361,15 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 	}
 	const uint64_t launches0 = ctx->launches.load();
 
-	// 1. group counts per level (the one host read needed to size the pools)
-	unsigned long long* hist = nullptr;
-	HAKO_TRY( dalloc( ctx, &hist, 22, s ) );
-	HAKO_CUDA( cudaMemsetAsync( hist, 0, 22 * 8, s ) );
+	// 1. group counts per level: from the caller (the merge stage counted them in its own read of the keys), else one pass + host read
+	uint64_t bounds[22];
+	if( levelBoundaries )
+		for( int j = 0; j < 22; j++ ) bounds[j] = levelBoundaries[j];
+	else
 	{
+		unsigned long long* hist = nullptr;
+		HAKO_TRY( dalloc( ctx, &hist, 22, s ) );
+		HAKO_CUDA( cudaMemsetAsync( hist, 0, 22 * 8, s ) );
 		const uint32_t blocks = (uint32_t)min( (uint64_t)ctx->smCount * 8, ( n + 255 ) / 256 );
 		levelHistKernel<<<blocks, 256, 0, s>>>( mortons, n, hist );
 		ctx->launches.fetch_add( 1, std::memory_order_relaxed );
@@ -375,11 +379,12 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 			dfree( hist, s );
 			return cudaFail( le, "levelHistKernel", __FILE__, __LINE__ );
 		}
+		HAKO_CUDA( cudaMemcpyAsync( ctx->pinned, hist, 22 * 8, cudaMemcpyDeviceToHost, s ) );
+		HAKO_CUDA( cudaStreamSynchronize( s ) );
+		ctx->stats.hostSyncs++;
+		dfree( hist, s );
+		for( int j = 0; j < 22; j++ ) bounds[j] = ctx->pinned[j];
 	}
-	HAKO_CUDA( cudaMemcpyAsync( ctx->pinned, hist, 22 * 8, cudaMemcpyDeviceToHost, s ) );
-	HAKO_CUDA( cudaStreamSynchronize( s ) );
-	ctx->stats.hostSyncs++;
-	dfree( hist, s );
 	uint64_t G[MAX_LEVELS + 1]; // G[l] = groups (= nodes before dedupe) at level l
 	{
 		uint64_t above = 0; // boundaries with top/3 > l
@@ -387,7 +392,7 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 		{
 			// a boundary between i-1 and i exists at level l iff top/3 >= l + 1
 			uint64_t b = 0;
-			for( int j = l + 1; j < 22; j++ ) b += ctx->pinned[j];
+			for( int j = l + 1; j < 22; j++ ) b += bounds[j];
 			G[l] = 1 + b;
 			(void)above;
 		}

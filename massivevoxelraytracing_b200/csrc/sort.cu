@@ -379,20 +379,25 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 		key[i] = k;
 	}
 	uint16_t* myHist = s_warpHist + warp * RADIX;
+	uint32_t* myHist32 = (uint32_t*)myHist; // two 16-bit counters per word (a warp holds at most ITEMS * 32 <= 512 keys of a digit)
 #pragma unroll
 	for( int i = 0; i < ITEMS; i++ )
 	{
 		const uint32_t idx = warpBase + i * 32 + lane;
 		const bool valid = idx < tileCount;
+		// invalid (padding) items sit behind the tile's last key; they get their own match class and are never written
 		const uint32_t d = valid ? digitOf( key[i], shift, mask ) : ( RADIX - 1 );
 		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, d | ( valid ? 0u : 0x10000u ) );
 		const uint32_t before = __popc( peers & ( ( 1u << lane ) - 1u ) );
-		uint32_t base = 0;
-		if( valid ) base = myHist[d];
+		const int leader = __ffs( peers ) - 1;
+		// the class leader reserves the class's ranks with ONE shared-memory atomic that returns the running count: no
+		// load -> add -> store chain through shared memory per item, so the 15 / 16 items of a thread pipeline
+		const uint32_t sh = ( d & 1u ) * 16u;
+		uint32_t old = 0;
+		if( valid && (int)lane == leader ) old = atomicAdd( &myHist32[d >> 1], (uint32_t)__popc( peers ) << sh );
 		__syncwarp();
-		if( valid && before == 0 ) myHist[d] = (uint16_t)( base + __popc( peers ) );
-		__syncwarp();
-		rank[i] = (uint16_t)( base + before );
+		old = __shfl_sync( 0xFFFFFFFFu, old, leader );
+		rank[i] = (uint16_t)( ( ( old >> sh ) & 0xFFFFu ) + before );
 	}
 	__syncthreads(); // every key is in registers: s_keys becomes the sorted staging buffer
 

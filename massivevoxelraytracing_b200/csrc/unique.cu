@@ -66,70 +66,109 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 	uint32_t total;
 	const uint32_t excl = blockExclusiveScan<UQ_BLOCK>( nHeads, &total );
 	const uint64_t prefix = scanTilePrefix( st, tile, total );
-	uint64_t out = prefix + excl;
+	// The merged voxels of the tile are staged in shared memory in output order and written out as one contiguous, coalesced
+	// block (a thread's own outputs are a strided dribble of up to 8 entries).
+	__shared__ uint64_t s_outK[UQ_TILE];
+	__shared__ uint64_t s_outA[UQ_TILE];
+	uint32_t slot = excl;
 	uint32_t anyEmission = 0;
+	// One pass over the thread's items with running sums: a head closes the run before it (if this thread owns it) and opens
+	// the next; items in front of the thread's first head belong to a run of an earlier thread, which walks into them below.
+	uint32_t c0 = 0, c1 = 0, c2 = 0, e0 = 0, e1 = 0, e2 = 0, cnt = 0;
+	uint64_t kcur = 0;
+	bool open = false;
+	auto add = [&]( const uint64_t x ) {
+		c0 += (uint32_t)( x ) & 0xFFu;
+		c1 += (uint32_t)( x >> 8 ) & 0xFFu;
+		c2 += (uint32_t)( x >> 16 ) & 0xFFu;
+		e0 += (uint32_t)( x >> 32 ) & 0xFFu;
+		e1 += (uint32_t)( x >> 40 ) & 0xFFu;
+		e2 += (uint32_t)( x >> 48 ) & 0xFFu;
+		cnt++;
+	};
+	auto emit = [&]() {
+		// integer means (voxRT.cpp:38-47); a run of one voxel -- the common case -- needs no division
+		uint32_t q0 = c0, q1 = c1, q2 = c2, r0 = e0, r1 = e1, r2 = e2;
+		if( cnt > 1 )
+		{
+			q0 /= cnt, q1 /= cnt, q2 /= cnt, r0 /= cnt, r1 /= cnt, r2 /= cnt;
+		}
+		anyEmission |= r0 | r1 | r2;
+		s_outK[slot] = kcur;
+		s_outA[slot] = (uint64_t)q0 | ( (uint64_t)q1 << 8 ) | ( (uint64_t)q2 << 16 ) | ( 1ull << 24 ) | ( (uint64_t)r0 << 32 ) | ( (uint64_t)r1 << 40 ) | ( (uint64_t)r2 << 48 ) | ( 1ull << 56 );
+		slot++;
+	};
 #pragma unroll
 	for( int i = 0; i < UQ_ITEMS; i++ )
 	{
-		if( !( heads & ( 1u << i ) ) ) continue;
-		// walk the run (voxKernel.cu:203-226 does the same serial walk from the first element)
-		uint32_t c[3] = { 0, 0, 0 }, e[3] = { 0, 0, 0 }, cnt = 0;
-		auto add = [&]( const uint64_t x ) {
-			c[0] += (uint32_t)( x ) & 0xFFu;
-			c[1] += (uint32_t)( x >> 8 ) & 0xFFu;
-			c[2] += (uint32_t)( x >> 16 ) & 0xFFu;
-			e[0] += (uint32_t)( x >> 32 ) & 0xFFu;
-			e[1] += (uint32_t)( x >> 40 ) & 0xFFu;
-			e[2] += (uint32_t)( x >> 48 ) & 0xFFu;
-			cnt++;
-		};
-		// the part of the run inside this thread's items: registers
-		bool open = true;
-#pragma unroll
-		for( int j = 0; j < UQ_ITEMS; j++ )
+		if( ( heads >> i ) & 1u )
 		{
-			if( j < i || !open ) continue;
-			if( j > i && ( ( heads >> j ) & 1u || base + j >= n ) )
-				open = false;
-			else
-				add( v[j] );
+			if( open ) emit();
+			kcur = k[i];
+			c0 = c1 = c2 = e0 = e1 = e2 = cnt = 0;
+			open = true;
+			add( v[i] );
 		}
-		// ... and whatever continues in the items of the following threads (voxKernel.cu:203-226 walks the whole run this way)
-		if( open )
-			for( uint64_t j = base + UQ_ITEMS; j < n; j++ )
-			{
-				if( keys[j] != k[i] ) break;
-				add( values[j] );
-			}
-		const uint32_t er = e[0] / cnt, eg = e[1] / cnt, eb = e[2] / cnt;
-		const uint64_t a = (uint64_t)( c[0] / cnt ) | ( (uint64_t)( c[1] / cnt ) << 8 ) | ( (uint64_t)( c[2] / cnt ) << 16 ) | ( 1ull << 24 ) |
-						   ( (uint64_t)er << 32 ) | ( (uint64_t)eg << 40 ) | ( (uint64_t)eb << 48 ) | ( 1ull << 56 );
-		anyEmission |= er | eg | eb;
-		keysOut[out] = k[i];
-		attrsOut[out] = a;
-		out++;
+		else if( open && base + i < n )
+			add( v[i] );
+	}
+	if( open )
+	{
+		// the thread's last run may continue in the items of the following threads (voxKernel.cu:203-226 walks the whole run this way)
+		for( uint64_t j = base + UQ_ITEMS; j < n; j++ )
+		{
+			if( keys[j] != kcur ) break;
+			add( values[j] );
+		}
+		emit();
+	}
+	__syncthreads();
+	for( uint32_t i = threadIdx.x; i < total; i += UQ_BLOCK )
+	{
+		keysOut[prefix + i] = s_outK[i];
+		attrsOut[prefix + i] = s_outA[i];
 	}
 	// hasEmission (voxKernel.cu:228-231 atomicExch): one atomic per warp at most
 	if( __any_sync( 0xFFFFFFFFu, anyEmission != 0 ) && ( threadIdx.x & 31u ) == 0 ) atomicOr( &counters[1], 1ull );
 	if( tile == gridDim.x - 1 && threadIdx.x == 0 ) counters[0] = prefix + total;
 }
 
-// number of distinct keys of a sorted array (one read of the keys): lets the caller allocate the exact-size outputs of the merge
-__global__ void __launch_bounds__( 256 ) countRunsKernel( const uint64_t* __restrict__ keys, uint64_t n, unsigned long long* __restrict__ count )
+// One read of the SORTED dumped keys (duplicates still in) gives everything the host must know before the rest of the build can be
+// sized: the number of distinct keys U = 1 + #{ i : keys[i] != keys[i-1] } (exact-size outputs of the merge), and for every octree
+// level the number of boundaries between neighbouring distinct keys whose highest differing bit lies in that level's digit -- the
+// per-level group counts that octreeTaskInit (voxKernel.cu:245-267) gets with one atomicInc per boundary.  Duplicates contribute
+// nothing to either, so the histogram is that of the unique list.  counters: [0] = U - 1, [1 + l] = boundaries with top bit in digit l.
+__global__ void __launch_bounds__( 256 ) countRunsKernel( const uint64_t* __restrict__ keys, uint64_t n, unsigned long long* __restrict__ counters )
 {
+	__shared__ uint32_t s_hist[22];
+	if( threadIdx.x < 22 ) s_hist[threadIdx.x] = 0;
+	__syncthreads();
 	uint32_t mine = 0;
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-	for( uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride ) mine += ( i == 0 || keys[i] != keys[i - 1] ) ? 1u : 0u;
+	for( uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x + 1; i < n; i += stride )
+	{
+		const uint64_t x = keys[i] ^ keys[i - 1];
+		if( x )
+		{
+			mine++;
+			atomicAdd( &s_hist[( 63 - __clzll( (long long)x ) ) / 3], 1u );
+		}
+	}
 	for( int o = 16; o; o >>= 1 ) mine += __shfl_down_sync( 0xFFFFFFFFu, mine, o );
-	if( ( threadIdx.x & 31u ) == 0 && mine ) atomicAdd( count, (unsigned long long)mine );
+	if( ( threadIdx.x & 31u ) == 0 && mine ) atomicAdd( &counters[0], (unsigned long long)mine );
+	__syncthreads();
+	if( threadIdx.x < 22 && s_hist[threadIdx.x] ) atomicAdd( &counters[1 + threadIdx.x], (unsigned long long)s_hist[threadIdx.x] );
 }
-int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64_t n, uint64_t* U )
+// *U = distinct keys; levelBoundaries (may be null): 22 counts for buildOctreeDevice.  Synchronises (the one host read of this stage).
+int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64_t n, uint64_t* U, uint64_t* levelBoundaries )
 {
 	*U = 0;
+	if( levelBoundaries )
+		for( int i = 0; i < 22; i++ ) levelBoundaries[i] = 0;
 	if( n == 0 ) return 0;
 	unsigned long long* counter = nullptr;
-	HAKO_TRY( dalloc( ctx, &counter, 1, s ) );
-	cudaError_t e = cudaMemsetAsync( counter, 0, 8, s );
+	HAKO_TRY( dalloc( ctx, &counter, 23, s ) );
+	cudaError_t e = cudaMemsetAsync( counter, 0, 23 * 8, s );
 	if( e == cudaSuccess )
 	{
 		const uint32_t blocks = (uint32_t)std::min<uint64_t>( (uint64_t)ctx->smCount * 8, ( n + 255 ) / 256 );
@@ -137,12 +176,14 @@ int countRunsDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, uint64
 		ctx->launches.fetch_add( 1, std::memory_order_relaxed );
 		e = cudaGetLastError();
 	}
-	if( e == cudaSuccess ) e = cudaMemcpyAsync( ctx->pinned, counter, 8, cudaMemcpyDeviceToHost, s );
+	if( e == cudaSuccess ) e = cudaMemcpyAsync( ctx->pinned, counter, 23 * 8, cudaMemcpyDeviceToHost, s );
 	if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
 	ctx->stats.hostSyncs++;
 	dfree( counter, s );
 	if( e != cudaSuccess ) return cudaFail( e, "countRunsDevice", __FILE__, __LINE__ );
-	*U = ctx->pinned[0];
+	*U = ctx->pinned[0] + 1;
+	if( levelBoundaries )
+		for( int i = 0; i < 22; i++ ) levelBoundaries[i] = ctx->pinned[1 + i];
 	return 0;
 }
 

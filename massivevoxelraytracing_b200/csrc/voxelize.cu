@@ -153,6 +153,70 @@ __device__ __forceinline__ V3 closestBary( V3 v0, V3 v1, V3 v2, V3 P )
 	return { bc.x / s, bc.y / s, bc.z / s };
 }
 
+// the same with the per-triangle part ( e0, e1, e2, Ng ) computed once per triangle: identical expressions, so identical bits
+struct BaryTri
+{
+	V3 e0, e1, e2, Ng;
+};
+__device__ __forceinline__ BaryTri baryTri( V3 v0, V3 v1, V3 v2 )
+{
+	BaryTri t;
+	t.e0 = v2 - v0, t.e1 = v0 - v1, t.e2 = v1 - v2;
+	t.Ng = cross( t.e2, t.e0 );
+	return t;
+}
+__device__ __forceinline__ V3 closestBaryPre( V3 v0, V3 v1, V3 v2, const BaryTri& t, V3 P )
+{
+	const V3 d0 = v0 - P, d1 = v1 - P, d2 = v2 - P;
+	float U = dot( cross( d2, d0 ), t.Ng );
+	float V = dot( cross( d0, d1 ), t.Ng );
+	float W = dot( cross( d1, d2 ), t.Ng );
+	if( U < 0.0f )
+	{
+		V = dot( -d0, t.e0 );
+		W = dot( d2, t.e0 );
+	}
+	else if( V < 0.0f )
+	{
+		W = dot( -d1, t.e1 );
+		U = dot( d0, t.e1 );
+	}
+	else if( W < 0.0f )
+	{
+		U = dot( -d2, t.e2 );
+		V = dot( d1, t.e2 );
+	}
+	const V3 bc = { smax( 0.0f, U ), smax( 0.0f, V ), smax( 0.0f, W ) };
+	const float s = bc.x + bc.y + bc.z;
+	return { bc.x / s, bc.y / s, bc.z / s };
+}
+
+// (uint8_t)( v ) with x86 semantics, cheaper than f2u8_x86: cvt.rzi saturates, so its low byte differs from cvttss2si's only for
+// v >= 2^31 (0x7FFFFFFF -> 0xFF against the indefinite value 0x80000000 -> 0x00); NaN gives 0 either way, v < -2^31 gives 0x80000000
+__device__ __forceinline__ uint32_t f2u8_fast( float v ) { return v < 2147483648.0f ? ( (uint32_t)__float2int_rz( v ) & 0xFFu ) : 0u; }
+__device__ __forceinline__ uint32_t packRGB255fast( V3 c )
+{
+	return f2u8_fast( c.x * 255.0f + 0.5f ) | ( f2u8_fast( c.y * 255.0f + 0.5f ) << 8 ) | ( f2u8_fast( c.z * 255.0f + 0.5f ) << 16 ) | 0xFF000000u;
+}
+// Morton code from a 256-entry table of 8 bits spread to every third position (24 bits): three look-ups per axis instead of the
+// five 64-bit shift / or / and rounds of splitBy3 (== encode2mortonCode_LUT, morton.hpp; all variants agree, unittest.cpp:183-216)
+__device__ __forceinline__ uint32_t spread8( uint32_t b )
+{
+	uint32_t x = b & 0xFFu;
+	x = ( x | x << 8 ) & 0x00F00Fu;
+	x = ( x | x << 4 ) & 0x0C30C3u;
+	x = ( x | x << 2 ) & 0x249249u;
+	return x;
+}
+__device__ __forceinline__ uint64_t mortonAxisLut( const uint32_t* lut, uint32_t v )
+{
+	return (uint64_t)lut[v & 0xFFu] | ( (uint64_t)lut[( v >> 8 ) & 0xFFu] << 24 ) | ( (uint64_t)lut[( v >> 16 ) & 0x1Fu] << 48 );
+}
+__device__ __forceinline__ uint64_t mortonEncodeLut( const uint32_t* lut, uint32_t x, uint32_t y, uint32_t z )
+{
+	return mortonAxisLut( lut, x ) | ( mortonAxisLut( lut, y ) << 1 ) | ( mortonAxisLut( lut, z ) << 2 );
+}
+
 __device__ __forceinline__ uint32_t packRGB255( V3 c )
 {
 	// (uint8_t)( v * 255.0f + 0.5f ) with x86 cast semantics; alpha = 255 (voxRT.cpp:230-234, voxKernel.cu:151-158)
@@ -490,25 +554,26 @@ __global__ void __launch_bounds__( 128, EMIT ? HAKO_EMIT_CTAS : HAKO_COUNT_CTAS 
 //            and shaded by all 32 lanes when the queue is half full (closest-point barycentrics, colour mix, Morton key).
 // Every value is the same fp32 expression as in columnVoxelsKernel, so the voxel set and the attributes are bit-identical.
 constexpr int VW_WARPS = 4;	   // warps per block
-constexpr int VW_CTX = 39;	   // words per triangle context (odd pitch: lanes reading different triangles hit different banks)
+constexpr int VW_CTX = 40;	   // words per triangle context (16-byte aligned rows)
 constexpr int VW_QUEUE = 256;  // queue entries per warp; a row chunk adds at most 32 x 4 voxels
 enum
 {
+	// 40 words per triangle, grouped so that each phase fetches what it needs with 16-byte shared loads (the lanes of a chunk mostly
+	// read the same few triangles, i.e. broadcasts): [0..3] header, [4..7] z box + plane slopes, [8..11] plane constants, [12..38] edges
 	VC_FLAGS = 0, // major | flat << 2
 	VC_LOX = 1,
 	VC_LOY = 2,
 	VC_HIY = 3,
 	VC_LOZ = 4,
 	VC_HIZ = 5,
-	VC_EM = 6,	// nx[3], ny[3], dc[3] of the major projection
-	VC_EA = 15, // first minor projection
-	VC_EB = 24, // second minor projection
-	VC_KX = 33,
-	VC_KY = 34,
-	VC_CSIX = 35,
-	VC_CMIN = 36,
-	VC_CMAX = 37,
-	VC_PAD = 38
+	VC_KX = 6,
+	VC_KY = 7,
+	VC_CSIX = 8,
+	VC_CMIN = 9,
+	VC_CMAX = 10,
+	VC_EM = 12, // nx[3], ny[3], dc[3] of the major projection
+	VC_EA = 21, // first minor projection
+	VC_EB = 30	// second minor projection
 };
 __device__ __forceinline__ uint32_t warpInclusiveScan( uint32_t v, uint32_t lane )
 {
@@ -536,10 +601,12 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 																  uint32_t* __restrict__ warpCount, const uint32_t* __restrict__ warpOffset,
 																  uint64_t* __restrict__ keys, uint64_t* __restrict__ values, uint32_t blockBase )
 {
-	__shared__ float s_ctx[VW_WARPS][32][VW_CTX];
+	__shared__ __align__( 16 ) float s_ctx[VW_WARPS][32][VW_CTX];
 	__shared__ uint32_t s_colPref[VW_WARPS][32];
 	__shared__ uint32_t s_rowPref[VW_WARPS][32];
-	__shared__ float s_tri[EMIT ? VW_WARPS : 1][EMIT ? 32 : 1][27]; // positions, colours, emissions of the warp's triangles
+	// positions, colours, emissions of the warp's triangles + Ng of closestBary: 32-word rows read with eight 16-byte loads per
+	// voxel (the drain is bound by shared-memory load issue: 27 scalar loads per voxel cost more than the arithmetic they feed)
+	__shared__ __align__( 16 ) float s_tri[EMIT ? VW_WARPS : 1][EMIT ? 32 : 1][32];
 	__shared__ uint64_t s_q[EMIT ? VW_WARPS : 1][EMIT ? VW_QUEUE : 1];
 	__shared__ uint8_t s_qOwner[EMIT ? VW_WARPS : 1][EMIT ? VW_QUEUE : 1];
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
@@ -600,6 +667,8 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 					d[9 + k] = col[(uint64_t)tri * 9 + k];
 					d[18 + k] = emi[(uint64_t)tri * 9 + k];
 				}
+				const BaryTri bt = baryTri( v0, v1, v2 );
+				d[27] = bt.Ng.x, d[28] = bt.Ng.y, d[29] = bt.Ng.z; // the edges are only needed when the corner projects outside the triangle
 			}
 		}
 	}
@@ -616,19 +685,28 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 		for( uint32_t i = lane; i < qCount; i += 32u )
 		{
 			const uint64_t q = s_q[EMIT ? warp : 0][EMIT ? i : 0];
-			const float* d = s_tri[EMIT ? warp : 0][EMIT ? s_qOwner[warp][i] : 0];
+			const float4* dv = (const float4*)s_tri[EMIT ? warp : 0][EMIT ? s_qOwner[warp][i] : 0];
+			float d[32];
+#pragma unroll
+			for( int k = 0; k < 8; k++ )
+			{
+				const float4 f = dv[k];
+				d[4 * k] = f.x, d[4 * k + 1] = f.y, d[4 * k + 2] = f.z, d[4 * k + 3] = f.w;
+			}
 			const uint32_t cx = (uint32_t)q & 0x1FFFFFu, cy = (uint32_t)( q >> 21 ) & 0x1FFFFFu, cz = (uint32_t)( q >> 42 ) & 0x1FFFFFu;
 			// the voxel's lower corner: origin + dps * index per axis -- the products and sums of the enumeration
 			// ( o = org_xy + dps * {x, y}, r = org_z + (float)z * dps, voxelization.hpp:300-305 )
 			const V3 p = { origin.x + dps * (int)cx, origin.y + dps * (int)cy, origin.z + dps * (int)cz };
-			const V3 bc = closestBary( V3{ d[0], d[1], d[2] }, V3{ d[3], d[4], d[5] }, V3{ d[6], d[7], d[8] }, p );
+			const V3 q0 = { d[0], d[1], d[2] }, q1 = { d[3], d[4], d[5] }, q2 = { d[6], d[7], d[8] };
+			const BaryTri bt = { q2 - q0, q0 - q1, q1 - q2, V3{ d[27], d[28], d[29] } };
+			const V3 bc = closestBaryPre( q0, q1, q2, bt, p );
 			const V3 k0 = { d[9], d[10], d[11] }, k1 = { d[12], d[13], d[14] }, k2 = { d[15], d[16], d[17] };
 			const V3 m0 = { d[18], d[19], d[20] }, m1 = { d[21], d[22], d[23] }, m2 = { d[24], d[25], d[26] };
 			const V3 bcol = bc.x * k1 + bc.y * k2 + bc.z * k0; // voxKernel.cu:148, voxRT.cpp:229
 			const V3 bemi = bc.x * m1 + bc.y * m2 + bc.z * m0;
 			const uint64_t o = (uint64_t)outBase + total + i;
 			keys[o] = mortonEncode( cx, cy, cz );
-			values[o] = (uint64_t)packRGB255( bcol ) | ( (uint64_t)packRGB255( bemi ) << 32 );
+			values[o] = (uint64_t)packRGB255fast( bcol ) | ( (uint64_t)packRGB255fast( bemi ) << 32 );
 		}
 		total += qCount;
 		qCount = 0;
@@ -641,11 +719,18 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 		const uint32_t j = cbase + lane;
 		const bool hasCol = j < colTotal;
 		const uint32_t owner = hasCol ? lastNotAbove( s_colPref[warp], j ) : 0u;
-		const float* oc = s_ctx[warp][owner];
-		const uint32_t* oi = (const uint32_t*)oc;
-		const int major = (int)( oi[VC_FLAGS] & 3u );
+		const float4* ocv = (const float4*)s_ctx[warp][owner];
+		const float4 oh = ocv[0]; // flags, lo_x, lo_y, hi_y
+		float em[12];			  // edges of the major projection: words 12..20
+#pragma unroll
+		for( int k = 0; k < 3; k++ )
+		{
+			const float4 f = ocv[3 + k];
+			em[4 * k] = f.x, em[4 * k + 1] = f.y, em[4 * k + 2] = f.z, em[4 * k + 3] = f.w;
+		}
+		const int major = (int)( __float_as_uint( oh.x ) & 3u );
 		const V2 org_xy = proj2( origin, major );
-		const int x = (int)oi[VC_LOX] + (int)( j - s_colPref[warp][owner] );
+		const int x = (int)__float_as_uint( oh.y ) + (int)( j - s_colPref[warp][owner] );
 		int ly = 1, uy = -1;
 		if( hasCol )
 		{
@@ -656,7 +741,7 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 #pragma unroll
 			for( int e = 0; e < 3; e++ )
 			{
-				const float ex = oc[VC_EM + e], ey = oc[VC_EM + 3 + e], cc = oc[VC_EM + 6 + e];
+				const float ex = em[e], ey = em[3 + e], cc = em[6 + e];
 				if( ey == 0.0f )
 				{
 					if( -ex * xc <= cc ) continue;
@@ -673,8 +758,8 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 			{
 				const float minIf = smax( ( miny - org_xy.y ) / dps, -2147483648.0f );
 				const float maxIf = smin( ( maxy - org_xy.y ) / dps, 2147483520.0f );
-				ly = smax( f2i_x86( ceilf( minIf ) ), (int)oi[VC_LOY] );
-				uy = smin( f2i_x86( floorf( maxIf ) ), (int)oi[VC_HIY] );
+				ly = smax( f2i_x86( ceilf( minIf ) ), (int)__float_as_uint( oh.z ) );
+				uy = smin( f2i_x86( floorf( maxIf ) ), (int)__float_as_uint( oh.w ) );
 			}
 		}
 		const uint32_t rows = ( hasCol && uy >= ly ) ? (uint32_t)( uy - ly + 1 ) : 0u;
@@ -696,9 +781,16 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 			const int rly = __shfl_sync( 0xFFFFFFFFu, ly, cl );
 			const uint32_t rEx = __shfl_sync( 0xFFFFFFFFu, rowExcl, cl );
 			const int y = rly + (int)( r - rEx );
-			const float* rc = s_ctx[warp][rOwner];
-			const uint32_t* ri = (const uint32_t*)rc;
-			const uint32_t flags = ri[VC_FLAGS];
+			const float4* rcv = (const float4*)s_ctx[warp][rOwner];
+			const float4 rh = rcv[0], rz = rcv[1], rk = rcv[2]; // header | lo_z, hi_z, kx, ky | csix, cmin, cmax
+			float ed[20];										 // words 20..39: EA at ed[1..9], EB at ed[10..18]
+#pragma unroll
+			for( int k = 0; k < 5; k++ )
+			{
+				const float4 f = rcv[5 + k];
+				ed[4 * k] = f.x, ed[4 * k + 1] = f.y, ed[4 * k + 2] = f.z, ed[4 * k + 3] = f.w;
+			}
+			const uint32_t flags = __float_as_uint( rh.x );
 			const int rMajor = (int)( flags & 3u );
 			const bool flat = ( flags & 4u ) != 0; // voxelization.hpp:313-316: a one-slab box overlaps by construction
 			const V2 rorg = proj2( origin, rMajor );
@@ -711,10 +803,10 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 			if( hasRow )
 			{
 				// zRangeInclusive( x, y ), voxelization.hpp:270-299 (no pre-clamp before the casts: x86 semantics)
-				const float var = rc[VC_KX] * o.x + rc[VC_KY] * o.y;
+				const float var = rz.z * o.x + rz.w * o.y;
 				if( six )
 				{
-					const float idx = ( ( var + rc[VC_CSIX] ) - org_z ) / dps;
+					const float idx = ( ( var + rk.x ) - org_z ) / dps;
 					const float zf = floorf( idx );
 					const int z = f2i_x86( zf );
 					zmin = ( idx == zf ) ? z - 1 : z;
@@ -722,11 +814,11 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 				}
 				else
 				{
-					zmin = f2i_x86( floorf( ( ( var + rc[VC_CMIN] ) - org_z ) / dps ) );
-					zmax = f2i_x86( floorf( ( ( var + rc[VC_CMAX] ) - org_z ) / dps ) );
+					zmin = f2i_x86( floorf( ( ( var + rk.y ) - org_z ) / dps ) );
+					zmax = f2i_x86( floorf( ( ( var + rk.z ) - org_z ) / dps ) );
 				}
-				zmin = smax( zmin, (int)ri[VC_LOZ] );
-				zmax = smin( zmax, (int)ri[VC_HIZ] );
+				zmin = smax( zmin, (int)__float_as_uint( rz.x ) );
+				zmax = smin( zmax, (int)__float_as_uint( rz.y ) );
 				// |kx|, |ky| <= 1 on the major axis, so a row holds at most 4 voxels; 8 keeps a chunk within the queue whatever happens
 				for( int z = zmin, k = 0; z <= zmax && k < 8; z++, k++ )
 				{
@@ -739,8 +831,8 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 #pragma unroll
 						for( int e = 0; e < 3; e++ )
 						{
-							if( rc[VC_EA + e] * pa.x + rc[VC_EA + 3 + e] * pa.y + rc[VC_EA + 6 + e] < 0.0f ) ok = false;
-							if( rc[VC_EB + e] * pb.x + rc[VC_EB + 3 + e] * pb.y + rc[VC_EB + 6 + e] < 0.0f ) ok = false;
+							if( ed[1 + e] * pa.x + ed[4 + e] * pa.y + ed[7 + e] < 0.0f ) ok = false;
+							if( ed[10 + e] * pb.x + ed[13 + e] * pb.y + ed[16 + e] < 0.0f ) ok = false;
 						}
 					}
 					if( ok ) okMask |= 1u << k;
