@@ -595,12 +595,20 @@ __device__ __forceinline__ uint32_t lastNotAbove( const uint32_t* pref, uint32_t
 	return lo;
 }
 
-template <bool EMIT>
-__global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
-																  uint32_t nTriangles, V3 origin, float dps, int gridRes, int sixSeparating,
-																  uint32_t* __restrict__ warpCount, const uint32_t* __restrict__ warpOffset,
-																  uint64_t* __restrict__ keys, uint64_t* __restrict__ values, uint32_t blockBase )
+// MODE 0: count.  MODE 1: emit (enumerate again, queue, shade).  MODE 2: count AND record: every voxel found is written as one
+// 8-byte record ( owner lane | x | y | z ) into the warp's slab of `slabCap` records, so that the emit pass is pure shading
+// (shadeRecordsKernel) instead of a second enumeration; a warp that finds more voxels than its slab holds keeps counting and is
+// emitted by MODE 1 (`onlyAbove` = slabCap makes MODE 1 skip the warps whose records fit).
+constexpr int VR_COORD_BITS = 19; // record = lane (5 bits) | x, y, z (19 bits each): grids up to 524288^3
+template <int MODE>
+__global__ void __launch_bounds__( VW_WARPS * 32, MODE == 1 ? 4 : 8 ) warpVoxelsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi,
+																	   uint32_t nTriangles, V3 origin, float dps, int gridRes, int sixSeparating,
+																	   uint32_t* __restrict__ warpCount, const uint32_t* __restrict__ warpOffset,
+																	   uint64_t* __restrict__ keys, uint64_t* __restrict__ values, uint32_t blockBase,
+																	   uint64_t* __restrict__ slab, uint32_t slabCap, uint32_t onlyAbove )
 {
+	constexpr bool EMIT = MODE == 1;
+	constexpr bool RECORD = MODE == 2;
 	__shared__ __align__( 16 ) float s_ctx[VW_WARPS][32][VW_CTX];
 	__shared__ uint32_t s_colPref[VW_WARPS][32];
 	__shared__ uint32_t s_rowPref[VW_WARPS][32];
@@ -612,6 +620,11 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 	const uint32_t gw = ( blockIdx.x + blockBase ) * VW_WARPS + warp; // global warp = group of 32 triangles
 	const uint32_t tri = gw * 32u + lane;
+	if( EMIT && onlyAbove )
+	{
+		// hybrid: this launch only serves the warps whose voxels did not fit their record slab (warp-uniform test)
+		if( gw * 32u >= nTriangles || warpOffset[gw + 1] - warpOffset[gw] <= onlyAbove ) return;
+	}
 	const bool six = sixSeparating != 0;
 	float* ctx = s_ctx[warp][lane];
 	uint32_t* ictx = (uint32_t*)ctx;
@@ -839,7 +852,24 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 				}
 			}
 			const uint32_t nv = __popc( okMask );
-			if( !EMIT )
+			if( RECORD )
+			{
+				// `total` is warp-uniform here: the voxels found so far; records beyond the slab are dropped (the count goes on)
+				const uint32_t vIncl = warpInclusiveScan( nv, lane );
+				const uint32_t vTotal = __shfl_sync( 0xFFFFFFFFu, vIncl, 31 );
+				uint32_t at = total + vIncl - nv;
+				for( uint32_t m = okMask; m; m &= m - 1u )
+				{
+					const int z = zmin + ( __ffs( m ) - 1 );
+					const I3 ci = unproji( rx, y, z, rMajor );
+					if( at < slabCap )
+						slab[(uint64_t)gw * slabCap + at] = (uint64_t)rOwner | ( (uint64_t)(uint32_t)ci.x << 5 ) | ( (uint64_t)(uint32_t)ci.y << ( 5 + VR_COORD_BITS ) ) |
+															( (uint64_t)(uint32_t)ci.z << ( 5 + 2 * VR_COORD_BITS ) );
+					at++;
+				}
+				total += vTotal;
+			}
+			else if( !EMIT )
 				total += nv;
 			else
 			{
@@ -866,10 +896,80 @@ __global__ void __launch_bounds__( VW_WARPS * 32, EMIT ? 4 : 8 ) warpVoxelsKerne
 	}
 	else
 	{
+		if( !RECORD )
+		{
 #pragma unroll
-		for( int o = 16; o > 0; o >>= 1 ) total += __shfl_xor_sync( 0xFFFFFFFFu, total, o );
+			for( int o = 16; o > 0; o >>= 1 ) total += __shfl_xor_sync( 0xFFFFFFFFu, total, o );
+		}
 		if( lane == 0 ) warpCount[gw] = total;
 	}
+}
+
+// ---- the emit pass of the record path: pure shading.  A warp loads its 32 triangles' positions, colours, emissions (+ Ng) into
+// shared memory, then walks its slab: one record = one voxel -> closest-point barycentrics, colour mix, Morton key, two stores. ----
+__global__ void __launch_bounds__( VW_WARPS * 32, 8 ) shadeRecordsKernel( const float* __restrict__ pos, const float* __restrict__ col, const float* __restrict__ emi, uint32_t nTriangles,
+														 V3 origin, float dps, const uint32_t* __restrict__ warpOffset, const uint64_t* __restrict__ slab, uint32_t slabCap,
+														 uint64_t* __restrict__ keys, uint64_t* __restrict__ values, uint32_t blockBase )
+{
+	__shared__ __align__( 16 ) float s_tri[VW_WARPS][32][32];
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const uint32_t gw = ( blockIdx.x + blockBase ) * VW_WARPS + warp;
+	if( gw * 32u >= nTriangles ) return;
+	const uint32_t outBase = warpOffset[gw];
+	const uint32_t count = warpOffset[gw + 1] - outBase;
+	if( count == 0 || count > slabCap ) return; // nothing to do, or the warp overflowed its slab and is emitted by warpVoxelsKernel<1>
+	const uint32_t tri = gw * 32u + lane;
+	if( tri < nTriangles )
+	{
+		const V3 v0 = loadV3( pos, (uint64_t)tri * 3 ), v1 = loadV3( pos, (uint64_t)tri * 3 + 1 ), v2 = loadV3( pos, (uint64_t)tri * 3 + 2 );
+		float* d = s_tri[warp][lane];
+		d[0] = v0.x, d[1] = v0.y, d[2] = v0.z, d[3] = v1.x, d[4] = v1.y, d[5] = v1.z, d[6] = v2.x, d[7] = v2.y, d[8] = v2.z;
+#pragma unroll
+		for( int k = 0; k < 9; k++ )
+		{
+			d[9 + k] = col[(uint64_t)tri * 9 + k];
+			d[18 + k] = emi[(uint64_t)tri * 9 + k];
+		}
+		const BaryTri bt = baryTri( v0, v1, v2 );
+		d[27] = bt.Ng.x, d[28] = bt.Ng.y, d[29] = bt.Ng.z;
+	}
+	__syncwarp();
+	const uint64_t* rec = slab + (uint64_t)gw * slabCap;
+	constexpr uint32_t CM = ( 1u << VR_COORD_BITS ) - 1u;
+	for( uint32_t i = lane; i < count; i += 32u )
+	{
+		const uint64_t q = __ldcs( rec + i );
+		const float4* dv = (const float4*)s_tri[warp][(uint32_t)q & 31u];
+		float d[32];
+#pragma unroll
+		for( int k = 0; k < 8; k++ )
+		{
+			const float4 f = dv[k];
+			d[4 * k] = f.x, d[4 * k + 1] = f.y, d[4 * k + 2] = f.z, d[4 * k + 3] = f.w;
+		}
+		const uint32_t cx = (uint32_t)( q >> 5 ) & CM, cy = (uint32_t)( q >> ( 5 + VR_COORD_BITS ) ) & CM, cz = (uint32_t)( q >> ( 5 + 2 * VR_COORD_BITS ) ) & CM;
+		// the voxel's lower corner: origin + dps * index per axis -- the products and sums of the enumeration (voxelization.hpp:300-305)
+		const V3 p = { origin.x + dps * (int)cx, origin.y + dps * (int)cy, origin.z + dps * (int)cz };
+		const V3 q0 = { d[0], d[1], d[2] }, q1 = { d[3], d[4], d[5] }, q2 = { d[6], d[7], d[8] };
+		const BaryTri bt = { q2 - q0, q0 - q1, q1 - q2, V3{ d[27], d[28], d[29] } };
+		const V3 bc = closestBaryPre( q0, q1, q2, bt, p );
+		const V3 k0 = { d[9], d[10], d[11] }, k1 = { d[12], d[13], d[14] }, k2 = { d[15], d[16], d[17] };
+		const V3 m0 = { d[18], d[19], d[20] }, m1 = { d[21], d[22], d[23] }, m2 = { d[24], d[25], d[26] };
+		const V3 bcol = bc.x * k1 + bc.y * k2 + bc.z * k0; // voxKernel.cu:148, voxRT.cpp:229
+		const V3 bemi = bc.x * m1 + bc.y * m2 + bc.z * m0;
+		const uint64_t o = (uint64_t)outBase + i;
+		keys[o] = mortonEncode( cx, cy, cz );
+		values[o] = (uint64_t)packRGB255fast( bcol ) | ( (uint64_t)packRGB255fast( bemi ) << 32 );
+	}
+}
+
+// warps whose voxel count (difference of neighbouring offsets) exceeds the slab capacity
+__global__ void __launch_bounds__( 256 ) countAboveKernel( const uint32_t* __restrict__ offsets, uint32_t n, uint32_t cap, unsigned long long* __restrict__ out )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const bool above = i < n && offsets[i + 1] - offsets[i] > cap;
+	const uint32_t m = __ballot_sync( 0xFFFFFFFFu, above );
+	if( ( threadIdx.x & 31u ) == 0 && m ) atomicAdd( out, (unsigned long long)__popc( m ) );
 }
 
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
@@ -888,7 +988,8 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 	uint32_t* colOffset = nullptr;
 	uint32_t* colCount = nullptr;
 	uint32_t* warpCount = nullptr;
-	uint64_t* totals = nullptr; // [0] columns of the large triangles, [1] voxels of the small triangles, [2] voxels of the large ones
+	uint64_t* slab = nullptr;	// voxel records of the small triangles (record path)
+	uint64_t* totals = nullptr; // [0] columns of the large triangles, [1] voxels of the small triangles, [2] voxels of the large ones, [3] warps beyond their slab
 	int r = 0;
 	do
 	{
@@ -896,24 +997,54 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		const uint32_t nWarps = nWarpBlocks * VW_WARPS;
 		if( ( r = dalloc( ctx, &colOffset, (uint64_t)nTriangles + 1, s ) ) ) break;
 		if( ( r = dalloc( ctx, &warpCount, (uint64_t)nWarps + 1, s ) ) ) break;
-		if( ( r = dalloc( ctx, &totals, 3, s ) ) ) break;
-		cudaError_t e = cudaMemsetAsync( totals, 0, 24, s );
+		if( ( r = dalloc( ctx, &totals, 4, s ) ) ) break;
+		// Record path: the counting pass keeps every voxel it finds (8 bytes) in a per-warp slab, and the emit pass only shades.
+		// The slab capacity is what a temporary of at most 4 GiB (and an eighth of the free memory) gives every warp, capped at
+		// 4096 records; scenes too dense for that (capacity < 256: e.g. 32768^3, ~18 k voxels per warp) enumerate twice as before,
+		// and so does any single warp that overflows its slab.  HAKO_VOX_RECORD=0: always enumerate twice (A/B reference).
+		static const bool recordOff = getenv( "HAKO_VOX_RECORD" ) && atoi( getenv( "HAKO_VOX_RECORD" ) ) == 0;
+		uint32_t slabCap = 0;
+		if( nWarps && keysOut && !recordOff && gridRes <= ( 1 << VR_COORD_BITS ) )
+		{
+			size_t freeB = 0, totalB = 0;
+			cudaMemGetInfo( &freeB, &totalB );
+			const uint64_t budget = std::min<uint64_t>( 4ull << 30, (uint64_t)freeB / 8 );
+			const uint64_t cap = std::min<uint64_t>( 4096, budget / ( 8ull * nWarps ) ) & ~31ull;
+			if( cap >= 256 ) slabCap = (uint32_t)cap;
+			static const int capEnv = getenv( "HAKO_VOX_SLAB_CAP" ) ? atoi( getenv( "HAKO_VOX_SLAB_CAP" ) ) : 0; // tests: force overflowing warps
+			if( capEnv > 0 ) slabCap = (uint32_t)capEnv;
+		}
+		if( slabCap && ( r = dalloc( ctx, &slab, (uint64_t)nWarps * slabCap, s ) ) ) break;
+		cudaError_t e = cudaMemsetAsync( totals, 0, 32, s );
 		if( e != cudaSuccess )
 		{
 			r = cudaFail( e, "memset totals", __FILE__, __LINE__ );
 			break;
 		}
-		auto wCount = warpVoxelsKernel<false>;
-		auto wEmit = warpVoxelsKernel<true>;
+		auto wCount = warpVoxelsKernel<0>;
+		auto wEmit = warpVoxelsKernel<1>;
+		auto wRecord = warpVoxelsKernel<2>;
 		if( nWarps )
 		{
-			HAKO_LAUNCH_R( ctx, r, wCount, nWarpBlocks, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, warpCount,
-						 (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u );
+			if( slabCap )
+				HAKO_LAUNCH_R( ctx, r, wRecord, nWarpBlocks, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, warpCount,
+							   (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u, slab, slabCap, 0u );
+			else
+				HAKO_LAUNCH_R( ctx, r, wCount, nWarpBlocks, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, warpCount,
+							   (const uint32_t*)nullptr, (uint64_t*)nullptr, (uint64_t*)nullptr, 0u, (uint64_t*)nullptr, 0u, 0u );
 			if( ( r = scanU32( ctx, s, warpCount, warpCount, nWarps, totals + 1 ) ) ) break;
+			// warpCount[nWarps] = total, so that a warp's count is warpCount[w + 1] - warpCount[w]; then the warps beyond their slab
+			e = cudaMemcpyAsync( warpCount + nWarps, totals + 1, 4, cudaMemcpyDeviceToDevice, s );
+			if( e != cudaSuccess )
+			{
+				r = cudaFail( e, "copy total", __FILE__, __LINE__ );
+				break;
+			}
+			if( slabCap ) HAKO_LAUNCH_R( ctx, r, countAboveKernel, divUp( nWarps, 256 ), 256, 0, s, warpCount, nWarps, slabCap, (unsigned long long*)( totals + 3 ) );
 		}
 		HAKO_LAUNCH_R( ctx, r, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset, columnsOnly ? 0 : 1 );
 		if( ( r = scanU32( ctx, s, colOffset, colOffset, nTriangles, totals ) ) ) break;
-		e = cudaMemcpyAsync( ctx->pinned, totals, 16, cudaMemcpyDeviceToHost, s );
+		e = cudaMemcpyAsync( ctx->pinned, totals, 32, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
 		ctx->stats.hostSyncs++;
 		if( e != cudaSuccess )
@@ -923,6 +1054,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		}
 		const uint64_t nColumns = ctx->pinned[0];
 		const uint64_t smallVoxels = ctx->pinned[1];
+		const uint64_t overflowWarps = ctx->pinned[3];
 		if( nColumns >= 0xFFFFFFFFull )
 		{
 			setError( "voxelize: %llu (triangle, x) columns exceed the 32-bit work index", (unsigned long long)nColumns );
@@ -974,8 +1106,19 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 			const uint32_t blockEnd = last ? nWarpBlocks : std::min<uint32_t>( nWarpBlocks, (uint32_t)( (uint64_t)nTriangles * ( k + 1 ) / emitSlices / ( 32u * VW_WARPS ) ) );
 			if( beforeEmit && ( r = beforeEmit( last ? -1 : k ) ) ) break; // -1: everything
 			if( blockEnd > blockBase && smallVoxels )
-				HAKO_LAUNCH_R( ctx, r, wEmit, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr,
-							 warpCount, *keysOut, *valuesOut, blockBase );
+			{
+				if( slabCap )
+				{
+					HAKO_LAUNCH_R( ctx, r, shadeRecordsKernel, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, warpCount, slab, slabCap,
+								   *keysOut, *valuesOut, blockBase );
+					if( overflowWarps ) // the few warps whose voxels did not fit their slab: enumerate again (the others return at once)
+						HAKO_LAUNCH_R( ctx, r, wEmit, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating,
+									   (uint32_t*)nullptr, warpCount, *keysOut, *valuesOut, blockBase, (uint64_t*)nullptr, 0u, slabCap );
+				}
+				else
+					HAKO_LAUNCH_R( ctx, r, wEmit, blockEnd - blockBase, VW_WARPS * 32, 0, s, pos, col, emi, nTriangles, origin, dps, gridRes, sixSeparating, (uint32_t*)nullptr,
+								   warpCount, *keysOut, *valuesOut, blockBase, (uint64_t*)nullptr, 0u, 0u );
+			}
 			blockBase = std::max( blockBase, blockEnd );
 		}
 		if( r ) break;
@@ -988,7 +1131,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		const int rh = beforeEmit( -1 ); // the caller's upload must be joined on every path
 		if( r == 0 ) r = rh;
 	}
-	dfree( colOffset, s ), dfree( colCount, s ), dfree( warpCount, s ), dfree( totals, s );
+	dfree( colOffset, s ), dfree( colCount, s ), dfree( warpCount, s ), dfree( totals, s ), dfree( slab, s );
 	if( r && keysOut )
 	{
 		dfree( *keysOut, s ), dfree( *valuesOut, s );

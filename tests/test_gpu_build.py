@@ -69,13 +69,14 @@ def test_voxelize_matches_oracle(hk, ctx, oracle, bunny, grid):
 
 
 def test_voxelize_paths_agree(hk, oracle, bunny, monkeypatch):
-    """HAKO_VOX_COLUMNS_ONLY=1 (one thread per (triangle, x) column for every triangle, the round-1 kernels) and the default
-    hybrid produce the same dumped voxels; both equal the oracle.  Ragged triangle counts exercise the partial last warp."""
+    """every execution path of the voxelizer produces the same dumped voxels, and they equal the oracle's.  Ragged triangle
+    counts exercise the partial last warp."""
     tris, col, emi = bunny
     origin, dps = scene_params(tris, 512)
     out = []
-    for env in ("0", "1"):
-        monkeypatch.setenv("HAKO_VOX_COLUMNS_ONLY", env)
+    # default (record path: the counting pass keeps the voxels, the emit pass only shades) | per-column kernels only | two
+    # enumerations (no records) | record slabs of 32 voxels per warp, so that most warps overflow and take the hybrid path
+    for extra in ({}, {"HAKO_VOX_COLUMNS_ONLY": "1"}, {"HAKO_VOX_RECORD": "0"}, {"HAKO_VOX_SLAB_CAP": "32"}):
         import subprocess, sys, os, json
         code = ("import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
                 "import massivevoxelraytracing_b200 as hk\nfrom scenes import bunny_scene, scene_params\n"
@@ -86,10 +87,10 @@ def test_voxelize_paths_agree(hk, oracle, bunny, monkeypatch):
                 "    r = np.empty(k.size, np.dtype([('k', np.uint64), ('a', np.uint64)])); r['k'] = k; r['a'] = a.view(np.uint64).reshape(-1)\n"
                 "    print(n, k.size, hashlib.sha1(np.sort(r, order=('k', 'a')).tobytes()).hexdigest())\n") % (
                     os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
-        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=dict(os.environ, HAKO_VOX_COLUMNS_ONLY=env))
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=dict(os.environ, **extra))
         assert r.returncode == 0, r.stderr
         out.append(r.stdout)
-    assert out[0] == out[1] and len(out[0].splitlines()) == 5
+    assert out[0] == out[1] == out[2] == out[3] and len(out[0].splitlines()) == 5
     keys, c, e = oracle.voxelize(tris, col, emi, origin, float(dps), 512)
     assert int(out[0].splitlines()[-1].split()[1]) == keys.size
 
