@@ -124,7 +124,9 @@ int hako_ctx_l2_probe( hako_ctx* ctx, hako_stream stream, uint64_t setBytes, int
 
 /* ---- build: IntersectorOctreeGPU::build, IntersectorOctreeGPU.hpp:40-241 ----
  * pos/col/emi: 9 floats per triangle (v0,v1,v2), as trianglesFlattened (voxUtil.hpp:8-65) produces.
- * HOST pointers; the H2D copy is part of the call, as in the reference (:68-70). */
+ * HOST pointers; the H2D copy is part of the call, as in the reference (:68-70).  On return the host arrays are free to reuse
+ * and every count is final; the last device copy of the node array may still be in flight on `stream` (the reference returns
+ * with its embedMasks launch in flight, :230-238): use the octree on the same stream, or synchronise the stream first. */
 int hako_octree_build( hako_ctx* ctx, hako_stream stream, const float* pos, const float* col, const float* emi,
 					   uint32_t nTriangles, const float origin[3], float dps, int gridRes, hako_octree** out );
 /* same with DEVICE-resident vertex data (per-frame rebuilds skip the H2D) */

@@ -135,8 +135,15 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 		if( ( r = buildOctreeDevice( ctx, s, o->mortons, U, gridRes, 1, &o->nodes, &o->masks, &o->numberOfNodes, nullptr, &o->wide, haveLevels ? levelBoundaries : nullptr ) ) ) break;
 		st.numberOfNodes = o->numberOfNodes;
 		CK( cudaEventRecord( ctx->ev[5], s ) );
-		CK( cudaStreamSynchronize( s ) );
-		st.hostSyncs++;
+		// No host wait here: the octree stage's own read of the final node count (its last host wait) has drained everything the
+		// host looks at -- the merge's counters below included; what may still be in flight on `s` is the copy of the nodes into
+		// their exact-size arrays, stream-ordered like the reference's final embedMasks launch (IntersectorOctreeGPU.hpp:230-238).
+		// The per-stage times are read from the events when hako_ctx_build_stats asks for them.
+		if( U && o->numberOfNodes == 0 )
+		{
+			CK( cudaStreamSynchronize( s ) ); // a tree without nodes (gridRes 1): nothing waited yet
+			st.hostSyncs++;
+		}
 		if( mergeCountersPending )
 		{
 			if( ctx->pinned[32] != U )
@@ -147,12 +154,7 @@ static int buildFromDeviceTriangles( hako_ctx* ctx, cudaStream_t s, const float*
 			}
 			o->hasEmission = ctx->pinned[33] ? 1u : 0u;
 		}
-		cudaEventElapsedTime( &st.ms_voxelize, ctx->ev[1], ctx->ev[2] );
-		cudaEventElapsedTime( &st.ms_sort, ctx->ev[2], ctx->ev[3] );
-		cudaEventElapsedTime( &st.ms_unique, ctx->ev[3], ctx->ev[4] );
-		cudaEventElapsedTime( &st.ms_octree, ctx->ev[4], ctx->ev[5] );
-		cudaEventElapsedTime( &st.ms_h2d, ctx->ev[0], ctx->ev[1] );
-		cudaEventElapsedTime( &st.ms_total, ctx->ev[0], ctx->ev[5] );
+		ctx->statsPending = true;
 #undef CK
 	} while( 0 );
 	dfree( keys, s ), dfree( values, s ), dfree( keysTmp, s ), dfree( valuesTmp, s );

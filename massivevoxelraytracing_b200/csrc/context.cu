@@ -148,9 +148,24 @@ int hako_ctx_synchronize( hako_ctx* c, hako_stream stream )
 	return HAKO_OK;
 }
 
-int hako_ctx_build_stats( const hako_ctx* c, hako_build_stats* out )
+int hako_ctx_build_stats( const hako_ctx* cc, hako_build_stats* out )
 {
-	if( !c || !out ) return HAKO_E_INVALID;
+	if( !cc || !out ) return HAKO_E_INVALID;
+	hako_ctx* c = const_cast<hako_ctx*>( cc );
+	if( c->statsPending )
+	{
+		// the build returned without a final host wait: its last event may still be in flight
+		HAKO_CUDA( cudaSetDevice( c->device ) );
+		HAKO_CUDA( cudaEventSynchronize( c->ev[5] ) );
+		hako_build_stats& st = c->stats;
+		cudaEventElapsedTime( &st.ms_h2d, c->ev[0], c->ev[1] );
+		cudaEventElapsedTime( &st.ms_voxelize, c->ev[1], c->ev[2] );
+		cudaEventElapsedTime( &st.ms_sort, c->ev[2], c->ev[3] );
+		cudaEventElapsedTime( &st.ms_unique, c->ev[3], c->ev[4] );
+		cudaEventElapsedTime( &st.ms_octree, c->ev[4], c->ev[5] );
+		cudaEventElapsedTime( &st.ms_total, c->ev[0], c->ev[5] );
+		c->statsPending = false;
+	}
 	*out = c->stats;
 	return HAKO_OK;
 }

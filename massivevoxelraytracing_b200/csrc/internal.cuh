@@ -20,6 +20,7 @@ struct hako_ctx
 	cudaMemPool_t pool = nullptr;
 	std::atomic<uint64_t> launches{ 0 };
 	hako_build_stats stats{};
+	bool statsPending = false; // the stage times of the last build are still in the events ev[0..5]
 	cudaEvent_t ev[8] = {};
 	// pinned staging word(s) for the few device->host counter reads a build needs
 	uint64_t* pinned = nullptr; // 64 x u64
