@@ -21,6 +21,10 @@ struct hako_ctx
 	std::atomic<uint64_t> launches{ 0 };
 	hako_build_stats stats{};
 	bool statsPending = false; // the stage times of the last build are still in the events ev[0..5]
+	// voxelizer: voxels per 32-triangle warp of the last build of an equally large mesh (sizes the next build's record slabs)
+	uint32_t lastVoxTriangles = 0;
+	int lastVoxGrid = 0;
+	double lastVoxPerWarp = 0.0;
 	cudaEvent_t ev[8] = {};
 	// pinned staging word(s) for the few device->host counter reads a build needs
 	uint64_t* pinned = nullptr; // 64 x u64

@@ -999,17 +999,25 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		if( ( r = dalloc( ctx, &warpCount, (uint64_t)nWarps + 1, s ) ) ) break;
 		if( ( r = dalloc( ctx, &totals, 4, s ) ) ) break;
 		// Record path: the counting pass keeps every voxel it finds (8 bytes) in a per-warp slab, and the emit pass only shades.
-		// The slab capacity is what a temporary of at most 4 GiB (and an eighth of the free memory) gives every warp, capped at
-		// 4096 records; scenes too dense for that (capacity < 256: e.g. 32768^3, ~18 k voxels per warp) enumerate twice as before,
-		// and so does any single warp that overflows its slab.  HAKO_VOX_RECORD=0: always enumerate twice (A/B reference).
+		// Slab capacity: three times the voxels per warp of the previous build of this mesh on this context, scaled by the change
+		// of resolution (RTCamp rebuilds the same mesh every frame) -- else what a 2 GiB temporary gives every warp; at most 4 096
+		// records and a 4 GiB temporary (an eighth of the free memory).  Scenes too dense for 256 records per warp (32768^3:
+		// ~18 k voxels per warp) enumerate twice as before, and so does any single warp that overflows its slab.
+		// HAKO_VOX_RECORD=0: always enumerate twice (A/B reference).
 		static const bool recordOff = getenv( "HAKO_VOX_RECORD" ) && atoi( getenv( "HAKO_VOX_RECORD" ) ) == 0;
 		uint32_t slabCap = 0;
 		if( nWarps && keysOut && !recordOff && gridRes <= ( 1 << VR_COORD_BITS ) )
 		{
 			size_t freeB = 0, totalB = 0;
 			cudaMemGetInfo( &freeB, &totalB );
-			const uint64_t budget = std::min<uint64_t>( 4ull << 30, (uint64_t)freeB / 8 );
-			const uint64_t cap = std::min<uint64_t>( 4096, budget / ( 8ull * nWarps ) ) & ~31ull;
+			const uint64_t hardBudget = std::min<uint64_t>( 4ull << 30, (uint64_t)freeB / 8 );
+			uint64_t cap = std::min<uint64_t>( hardBudget, 2ull << 30 ) / ( 8ull * nWarps );
+			if( ctx->lastVoxTriangles == nTriangles && ctx->lastVoxGrid > 0 && ctx->lastVoxPerWarp > 0.0 )
+			{
+				const double scale = (double)gridRes / (double)ctx->lastVoxGrid;
+				cap = std::min<uint64_t>( (uint64_t)( 3.0 * ctx->lastVoxPerWarp * scale * scale ) + 64, hardBudget / ( 8ull * nWarps ) );
+			}
+			cap = std::min<uint64_t>( 4096, cap ) & ~31ull;
 			if( cap >= 256 ) slabCap = (uint32_t)cap;
 			static const int capEnv = getenv( "HAKO_VOX_SLAB_CAP" ) ? atoi( getenv( "HAKO_VOX_SLAB_CAP" ) ) : 0; // tests: force overflowing warps
 			if( capEnv > 0 ) slabCap = (uint32_t)capEnv;
@@ -1055,6 +1063,12 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		const uint64_t nColumns = ctx->pinned[0];
 		const uint64_t smallVoxels = ctx->pinned[1];
 		const uint64_t overflowWarps = ctx->pinned[3];
+		if( nWarps )
+		{
+			ctx->lastVoxTriangles = nTriangles;
+			ctx->lastVoxGrid = gridRes;
+			ctx->lastVoxPerWarp = (double)smallVoxels / (double)nWarps;
+		}
 		if( nColumns >= 0xFFFFFFFFull )
 		{
 			setError( "voxelize: %llu (triangle, x) columns exceed the 32-bit work index", (unsigned long long)nColumns );
