@@ -21,7 +21,7 @@ struct hako_ctx
 	std::atomic<uint64_t> launches{ 0 };
 	hako_build_stats stats{};
 	bool statsPending = false; // the stage times of the last build are still in the events ev[0..5]
-	// voxelizer: voxels per 32-triangle warp of the last build of an equally large mesh (sizes the next build's record slabs)
+	// voxelizer: voxels of the LARGEST 32-triangle warp in the last build of an equally large mesh (sizes the next build's record slabs)
 	uint32_t lastVoxTriangles = 0;
 	int lastVoxGrid = 0;
 	double lastVoxPerWarp = 0.0;

@@ -10,6 +10,7 @@
 //     resolves its global offsets by decoupled look-back over the preceding tiles, and scatters through shared
 //     memory so that global stores are runs of consecutive addresses.
 // Algorithmic traffic: n * (8 + P * 32) bytes for pairs, vs n * P * (8 + 32) for the reference.
+#include <algorithm>
 #include <cstdlib>
 
 #include "internal.cuh"
@@ -31,6 +32,9 @@ constexpr int MAX_PASSES = 8;
 #define LB_FLAG_AGG ( 1ull << 62 )
 #define LB_FLAG_INC ( 2ull << 62 )
 #define LB_VALUE_MASK ( ( 1ull << 62 ) - 1 )
+#ifndef LB_BACKOFF_NS
+#define LB_BACKOFF_NS 100
+#endif
 
 __device__ __forceinline__ uint32_t digitOf( uint64_t key, int shift, uint32_t mask ) { return (uint32_t)( key >> shift ) & mask; }
 
@@ -320,7 +324,7 @@ template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS>
 __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
 																 uint64_t* __restrict__ keysOut, uint64_t* __restrict__ valuesOut, uint64_t n,
 																 int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [RADIX] exclusive */,
-																 unsigned long long* __restrict__ lookback /* [tiles][RADIX], zeroed */, uint32_t* __restrict__ ticket )
+																 unsigned long long* __restrict__ lookback /* [tiles][RADIX], zeroed */, uint32_t* __restrict__ ticket, uint32_t backoffNs, uint32_t lbBatch )
 {
 	using L = SortV2Smem<RBITS, BLOCK, ITEMS>;
 	constexpr int RADIX = L::RADIX, WARPS = L::WARPS, TILE = L::TILE;
@@ -430,17 +434,35 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 		{
 			const uint32_t d = threadIdx.x * DPT + j;
 			if( !owner || tile == 0 ) continue;
+			// look back over the predecessors' descriptors, lbBatch of them per round trip: the loads of a batch are independent,
+			// so a chain of AGGREGATE entries costs one L2 latency per batch instead of one per tile (descriptors behind the
+			// first INCLUSIVE one are fetched for nothing)
 			int64_t t = (int64_t)tile - 1;
-			for( ;; )
+			bool done = false;
+			while( !done )
 			{
-				unsigned long long v;
-				do
+				unsigned long long v[8];
+#pragma unroll
+				for( int k = 0; k < 8; k++ )
 				{
-					v = *(const volatile unsigned long long*)( lookback + (size_t)t * RADIX + d );
-				} while( ( v >> 62 ) == 0 );
-				excl[j] += v & LB_VALUE_MASK;
-				if( ( v >> 62 ) == 2 ) break;
-				t--;
+					const int64_t p = t - k;
+					v[k] = LB_FLAG_INC; // in front of tile 0: inclusive prefix 0
+					if( k < (int)lbBatch && p >= 0 ) v[k] = *(const volatile unsigned long long*)( lookback + (size_t)p * RADIX + d );
+				}
+#pragma unroll
+				for( int k = 0; k < 8; k++ )
+				{
+					if( done || k >= (int)lbBatch ) continue;
+					unsigned long long vv = v[k];
+					while( ( vv >> 62 ) == 0 )
+					{
+						if( backoffNs ) __nanosleep( backoffNs );
+						vv = *(const volatile unsigned long long*)( lookback + (size_t)( t - k ) * RADIX + d );
+					}
+					excl[j] += vv & LB_VALUE_MASK;
+					if( ( vv >> 62 ) == 2 ) done = true;
+				}
+				t -= lbBatch;
 			}
 			*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + d ) = LB_FLAG_INC | ( excl[j] + total[j] );
 		}
@@ -533,7 +555,10 @@ int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t
 		HAKO_CUDA( cudaFuncSetAttribute( k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes ) );
 		configured[dev] = true;
 	}
-	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
+	static const int backoffEnv = getenv( "HAKO_SORT_BACKOFF" ) ? atoi( getenv( "HAKO_SORT_BACKOFF" ) ) : LB_BACKOFF_NS; // ns a look-back poll sleeps when its predecessor is not ready
+	static const int batchEnv = getenv( "HAKO_SORT_LOOKBACK" ) ? atoi( getenv( "HAKO_SORT_LOOKBACK" ) ) : 4; // predecessors per look-back round trip (1..8)
+	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket, (uint32_t)( backoffEnv > 0 ? backoffEnv : 0 ),
+				 (uint32_t)std::max( 1, std::min( 8, batchEnv ) ) );
 	return 0;
 }
 template <int RBITS, bool PAIRS>

@@ -963,13 +963,15 @@ __global__ void __launch_bounds__( VW_WARPS * 32, 8 ) shadeRecordsKernel( const 
 	}
 }
 
-// warps whose voxel count (difference of neighbouring offsets) exceeds the slab capacity
+// warps whose voxel count (difference of neighbouring offsets) exceeds the slab capacity -> out[0]; the largest count -> out[1]
 __global__ void __launch_bounds__( 256 ) countAboveKernel( const uint32_t* __restrict__ offsets, uint32_t n, uint32_t cap, unsigned long long* __restrict__ out )
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	const bool above = i < n && offsets[i + 1] - offsets[i] > cap;
-	const uint32_t m = __ballot_sync( 0xFFFFFFFFu, above );
+	const uint32_t cnt = i < n ? offsets[i + 1] - offsets[i] : 0u;
+	const uint32_t m = __ballot_sync( 0xFFFFFFFFu, cnt > cap );
 	if( ( threadIdx.x & 31u ) == 0 && m ) atomicAdd( out, (unsigned long long)__popc( m ) );
+	const uint32_t mx = __reduce_max_sync( 0xFFFFFFFFu, cnt );
+	if( ( threadIdx.x & 31u ) == 0 && mx ) atomicMax( out + 1, (unsigned long long)mx ); // the largest warp: sizes the next build's slabs
 }
 
 int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float* col, const float* emi, uint32_t nTriangles,
@@ -989,7 +991,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 	uint32_t* colCount = nullptr;
 	uint32_t* warpCount = nullptr;
 	uint64_t* slab = nullptr;	// voxel records of the small triangles (record path)
-	uint64_t* totals = nullptr; // [0] columns of the large triangles, [1] voxels of the small triangles, [2] voxels of the large ones, [3] warps beyond their slab
+	uint64_t* totals = nullptr; // [0] columns of the large triangles, [1] voxels of the small triangles, [2] voxels of the large ones, [3] warps beyond their slab, [4] largest warp
 	int r = 0;
 	do
 	{
@@ -997,12 +999,12 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		const uint32_t nWarps = nWarpBlocks * VW_WARPS;
 		if( ( r = dalloc( ctx, &colOffset, (uint64_t)nTriangles + 1, s ) ) ) break;
 		if( ( r = dalloc( ctx, &warpCount, (uint64_t)nWarps + 1, s ) ) ) break;
-		if( ( r = dalloc( ctx, &totals, 4, s ) ) ) break;
+		if( ( r = dalloc( ctx, &totals, 5, s ) ) ) break;
 		// Record path: the counting pass keeps every voxel it finds (8 bytes) in a per-warp slab, and the emit pass only shades.
-		// Slab capacity: three times the voxels per warp of the previous build of this mesh on this context, scaled by the change
-		// of resolution (RTCamp rebuilds the same mesh every frame) -- else what a 2 GiB temporary gives every warp; at most 4 096
-		// records and a 4 GiB temporary (an eighth of the free memory).  Scenes too dense for 256 records per warp (32768^3:
-		// ~18 k voxels per warp) enumerate twice as before, and so does any single warp that overflows its slab.
+		// Slab capacity: what a 4 GiB temporary (at most an eighth of the free memory) gives every warp, at most 4 096 records; when
+		// this context has built the same mesh before (RTCamp rebuilds it every frame), 1.25 x the largest warp of that build,
+		// scaled by the change of resolution.  Scenes too dense for 256 records per warp (32768^3: ~18 k voxels per warp)
+		// enumerate twice as before, and so does any single warp that overflows its slab.
 		// HAKO_VOX_RECORD=0: always enumerate twice (A/B reference).
 		static const bool recordOff = getenv( "HAKO_VOX_RECORD" ) && atoi( getenv( "HAKO_VOX_RECORD" ) ) == 0;
 		uint32_t slabCap = 0;
@@ -1011,11 +1013,11 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 			size_t freeB = 0, totalB = 0;
 			cudaMemGetInfo( &freeB, &totalB );
 			const uint64_t hardBudget = std::min<uint64_t>( 4ull << 30, (uint64_t)freeB / 8 );
-			uint64_t cap = std::min<uint64_t>( hardBudget, 2ull << 30 ) / ( 8ull * nWarps );
+			uint64_t cap = hardBudget / ( 8ull * nWarps );
 			if( ctx->lastVoxTriangles == nTriangles && ctx->lastVoxGrid > 0 && ctx->lastVoxPerWarp > 0.0 )
 			{
 				const double scale = (double)gridRes / (double)ctx->lastVoxGrid;
-				cap = std::min<uint64_t>( (uint64_t)( 3.0 * ctx->lastVoxPerWarp * scale * scale ) + 64, hardBudget / ( 8ull * nWarps ) );
+				cap = std::min<uint64_t>( (uint64_t)( 1.25 * ctx->lastVoxPerWarp * scale * scale ) + 64, cap );
 			}
 			cap = std::min<uint64_t>( 4096, cap ) & ~31ull;
 			if( cap >= 256 ) slabCap = (uint32_t)cap;
@@ -1023,7 +1025,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 			if( capEnv > 0 ) slabCap = (uint32_t)capEnv;
 		}
 		if( slabCap && ( r = dalloc( ctx, &slab, (uint64_t)nWarps * slabCap, s ) ) ) break;
-		cudaError_t e = cudaMemsetAsync( totals, 0, 32, s );
+		cudaError_t e = cudaMemsetAsync( totals, 0, 40, s );
 		if( e != cudaSuccess )
 		{
 			r = cudaFail( e, "memset totals", __FILE__, __LINE__ );
@@ -1052,7 +1054,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		}
 		HAKO_LAUNCH_R( ctx, r, triColumnsKernel, divUp( nTriangles, 256 ), 256, 0, s, pos, nTriangles, origin, dps, gridRes, colOffset, columnsOnly ? 0 : 1 );
 		if( ( r = scanU32( ctx, s, colOffset, colOffset, nTriangles, totals ) ) ) break;
-		e = cudaMemcpyAsync( ctx->pinned, totals, 32, cudaMemcpyDeviceToHost, s );
+		e = cudaMemcpyAsync( ctx->pinned, totals, 40, cudaMemcpyDeviceToHost, s );
 		if( e == cudaSuccess ) e = cudaStreamSynchronize( s );
 		ctx->stats.hostSyncs++;
 		if( e != cudaSuccess )
@@ -1067,7 +1069,7 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		{
 			ctx->lastVoxTriangles = nTriangles;
 			ctx->lastVoxGrid = gridRes;
-			ctx->lastVoxPerWarp = (double)smallVoxels / (double)nWarps;
+			ctx->lastVoxPerWarp = slabCap ? (double)ctx->pinned[4] : 0.0; // the LARGEST warp of this build (0: not measured)
 		}
 		if( nColumns >= 0xFFFFFFFFull )
 		{

@@ -12,7 +12,7 @@ vals = torch.arange(n, dtype=torch.int64, device='cuda')
 small_k = torch.randint(0, 1 << 20, (1_000_003,), dtype=torch.int64, device='cuda', generator=g)   # odd length, many duplicates
 small_v = torch.arange(small_k.numel(), dtype=torch.int64, device='cuda')
 ref_k, ref_i = torch.sort(small_k, stable=True)
-for variant in (0, 1, 2, 3):
+for variant in [int(v) for v in os.environ.get('PROBE_VARIANTS', '0,1,2,3').split(',')]:
     os.environ['HAKO_SORT_VARIANT'] = str(variant)
     k, v = small_k.clone(), small_v.clone()
     ctx.sort_pairs_device(k, v, 0, 20); torch.cuda.synchronize()
