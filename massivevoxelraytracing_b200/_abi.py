@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libhako_b200.so")
+# HAKO_LIB_PATH: measurement tooling only (a variant build of the same sources, e.g. tools/ A/B probes)
+LIB_PATH = os.environ.get("HAKO_LIB_PATH") or os.path.join(HERE, "libhako_b200.so")
 
 HAKO_OK, HAKO_E_INVALID, HAKO_E_CUDA, HAKO_E_LIMIT, HAKO_E_STATE = 0, -1, -2, -3, -4
 

@@ -33,7 +33,10 @@ constexpr int MAX_PASSES = 8;
 #define LB_FLAG_INC ( 2ull << 62 )
 #define LB_VALUE_MASK ( ( 1ull << 62 ) - 1 )
 #ifndef LB_BACKOFF_NS
-#define LB_BACKOFF_NS 100
+#define LB_BACKOFF_NS 0 // sweep 0..1000 ns: no effect (profiles/r2n_sort_backoff.log) -- the look-back waits on round trips, not on unpublished tiles
+#endif
+#ifndef HAKO_SORT_LB
+#define HAKO_SORT_LB 2 // predecessors fetched per look-back round trip, both digits of a thread side by side: 1 / 2 / 4 / 8 = 4.14 / 4.01 / 4.31 / 5.69 ms (profiles/r2p_sort_lookback.log): deeper batches over-fetch 4 KB descriptors
 #endif
 
 __device__ __forceinline__ uint32_t digitOf( uint64_t key, int shift, uint32_t mask ) { return (uint32_t)( key >> shift ) & mask; }
@@ -324,7 +327,7 @@ template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS>
 __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
 																 uint64_t* __restrict__ keysOut, uint64_t* __restrict__ valuesOut, uint64_t n,
 																 int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [RADIX] exclusive */,
-																 unsigned long long* __restrict__ lookback /* [tiles][RADIX], zeroed */, uint32_t* __restrict__ ticket, uint32_t backoffNs, uint32_t lbBatch )
+																 unsigned long long* __restrict__ lookback /* [tiles][RADIX], zeroed */, uint32_t* __restrict__ ticket, uint32_t backoffNs )
 {
 	using L = SortV2Smem<RBITS, BLOCK, ITEMS>;
 	constexpr int RADIX = L::RADIX, WARPS = L::WARPS, TILE = L::TILE;
@@ -429,42 +432,52 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 			mine += tot;
 			*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + d ) = ( tile == 0 ? LB_FLAG_INC : LB_FLAG_AGG ) | (unsigned long long)tot;
 		}
-#pragma unroll
-		for( int j = 0; j < DPT; j++ )
+		// Decoupled look-back, LB predecessors per round trip and the thread's DPT digits side by side: the loads of a round are
+		// independent, so a chain of AGGREGATE descriptors costs one L2 latency per LB tiles instead of one per tile and digit
+		// (descriptors behind the first INCLUSIVE one are fetched for nothing).  HAKO_SORT_LOOKBACK sweep: profiles/r2o, r2p.
+		if( owner && tile != 0 )
 		{
-			const uint32_t d = threadIdx.x * DPT + j;
-			if( !owner || tile == 0 ) continue;
-			// look back over the predecessors' descriptors, lbBatch of them per round trip: the loads of a batch are independent,
-			// so a chain of AGGREGATE entries costs one L2 latency per batch instead of one per tile (descriptors behind the
-			// first INCLUSIVE one are fetched for nothing)
+			constexpr int LB = HAKO_SORT_LB;
+			bool done[DPT];
+#pragma unroll
+			for( int j = 0; j < DPT; j++ ) done[j] = false;
 			int64_t t = (int64_t)tile - 1;
-			bool done = false;
-			while( !done )
+			bool all = false;
+			while( !all )
 			{
-				unsigned long long v[8];
+				unsigned long long v[DPT][LB];
 #pragma unroll
-				for( int k = 0; k < 8; k++ )
-				{
-					const int64_t p = t - k;
-					v[k] = LB_FLAG_INC; // in front of tile 0: inclusive prefix 0
-					if( k < (int)lbBatch && p >= 0 ) v[k] = *(const volatile unsigned long long*)( lookback + (size_t)p * RADIX + d );
-				}
+				for( int j = 0; j < DPT; j++ )
 #pragma unroll
-				for( int k = 0; k < 8; k++ )
-				{
-					if( done || k >= (int)lbBatch ) continue;
-					unsigned long long vv = v[k];
-					while( ( vv >> 62 ) == 0 )
+					for( int k = 0; k < LB; k++ )
 					{
-						if( backoffNs ) __nanosleep( backoffNs );
-						vv = *(const volatile unsigned long long*)( lookback + (size_t)( t - k ) * RADIX + d );
+						v[j][k] = LB_FLAG_INC; // in front of tile 0 (or a digit that is done): inclusive prefix 0
+						if( !done[j] && t - k >= 0 ) v[j][k] = *(const volatile unsigned long long*)( lookback + (size_t)( t - k ) * RADIX + threadIdx.x * DPT + j );
 					}
-					excl[j] += vv & LB_VALUE_MASK;
-					if( ( vv >> 62 ) == 2 ) done = true;
+				all = true;
+#pragma unroll
+				for( int j = 0; j < DPT; j++ )
+				{
+#pragma unroll
+					for( int k = 0; k < LB; k++ )
+					{
+						if( done[j] ) continue;
+						unsigned long long vv = v[j][k];
+						while( ( vv >> 62 ) == 0 )
+						{
+							if( backoffNs ) __nanosleep( backoffNs );
+							vv = *(const volatile unsigned long long*)( lookback + (size_t)( t - k ) * RADIX + threadIdx.x * DPT + j );
+						}
+						excl[j] += vv & LB_VALUE_MASK;
+						if( ( vv >> 62 ) == 2 ) done[j] = true;
+					}
+					all = all && done[j];
 				}
-				t -= lbBatch;
+				t -= LB;
 			}
-			*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + d ) = LB_FLAG_INC | ( excl[j] + total[j] );
+#pragma unroll
+			for( int j = 0; j < DPT; j++ )
+				*(volatile unsigned long long*)( lookback + (size_t)tile * RADIX + threadIdx.x * DPT + j ) = LB_FLAG_INC | ( excl[j] + total[j] );
 		}
 		uint32_t inc = mine;
 #pragma unroll
@@ -556,9 +569,7 @@ int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t
 		configured[dev] = true;
 	}
 	static const int backoffEnv = getenv( "HAKO_SORT_BACKOFF" ) ? atoi( getenv( "HAKO_SORT_BACKOFF" ) ) : LB_BACKOFF_NS; // ns a look-back poll sleeps when its predecessor is not ready
-	static const int batchEnv = getenv( "HAKO_SORT_LOOKBACK" ) ? atoi( getenv( "HAKO_SORT_LOOKBACK" ) ) : 4; // predecessors per look-back round trip (1..8)
-	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket, (uint32_t)( backoffEnv > 0 ? backoffEnv : 0 ),
-				 (uint32_t)std::max( 1, std::min( 8, batchEnv ) ) );
+	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket, (uint32_t)( backoffEnv > 0 ? backoffEnv : 0 ) );
 	return 0;
 }
 template <int RBITS, bool PAIRS>
