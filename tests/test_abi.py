@@ -94,3 +94,23 @@ def test_cpp_shims_compile_and_fail_loudly_without_gpu(tmp_path):
         pytest.skip("a GPU is present (the demo itself runs in tests/test_gpu_shim.py)")
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 1 and "no CPU fallback" in r.stderr
+
+
+def test_reference_gpu_launcher_loads_and_fails_loudly_without_a_driver():
+    """oracle/librefgpu.so (the driver-API launcher of the reference's own kernels; test infrastructure) exports its ABI and, on a
+    machine without libcuda, refuses to open with a message instead of crashing"""
+    import ctypes as C
+    import subprocess
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
+    path = os.path.join(ROOT, "oracle", "librefgpu.so")
+    lib = C.CDLL(path)
+    for name in ("refgpu_open", "refgpu_close", "refgpu_set_octree", "refgpu_set_attrs", "refgpu_render", "refgpu_load_hdri", "refgpu_get_sats", "refgpu_set_pmj",
+                 "refgpu_pt_resize", "refgpu_pt_clear", "refgpu_pt_step", "refgpu_pt_read_accum", "refgpu_pt_write_accum", "refgpu_pt_resolve", "refgpu_set_scales",
+                 "refgpu_last_error"):
+        assert hasattr(lib, name), name
+    import torch
+    if not torch.cuda.is_available():
+        lib.refgpu_last_error.restype = C.c_char_p
+        h = C.c_void_p()
+        rc = lib.refgpu_open(b"/nonexistent.cubin", 0, C.byref(h))
+        assert rc != 0 and not h.value and lib.refgpu_last_error()
