@@ -1251,6 +1251,9 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 		// fork: the lanes start after everything queued on `s` (allocations, the previous step's accumulate)
 		HAKO_CUDA( cudaEventRecord( pt->laneEv[PT_LANES], s ) );
 		for( int k = 0; k < lanes; k++ ) HAKO_CUDA( cudaStreamWaitEvent( pt->laneStream[k], pt->laneEv[PT_LANES], 0 ) );
+		// the bands are enqueued inside a callable so that a failure in the middle still reaches the join below: the lanes must never
+		// be left forked from `s`
+		const auto enqueueBands = [&]() -> int {
 		int band = 0;
 		for( int b0 = y0; b0 < y1; b0 += (int)rowsPerBand, band++ )
 		{
@@ -1305,12 +1308,19 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 					HAKO_LAUNCH( ctx, kTrace5, traceGrid, 256, 0, ls, q.tree, tp );
 			}
 		}
-		// join: the accumulate below (and whatever the caller queues next) waits for every lane
+		return 0;
+		};
+		const int bandsResult = enqueueBands();
+		// join: the accumulate below (and whatever the caller queues next) waits for every lane -- also when a band failed
+		cudaError_t je = cudaSuccess;
 		for( int k = 0; k < lanes; k++ )
 		{
-			HAKO_CUDA( cudaEventRecord( pt->laneEv[k], pt->laneStream[k] ) );
-			HAKO_CUDA( cudaStreamWaitEvent( s, pt->laneEv[k], 0 ) );
+			cudaError_t e1 = cudaEventRecord( pt->laneEv[k], pt->laneStream[k] );
+			if( e1 == cudaSuccess ) e1 = cudaStreamWaitEvent( s, pt->laneEv[k], 0 );
+			if( e1 != cudaSuccess && je == cudaSuccess ) je = e1;
 		}
+		if( bandsResult ) return bandsResult;
+		HAKO_CUDA( je );
 	}
 	else
 	{
