@@ -728,17 +728,24 @@ def run_massive_leg(hk, hdist, nd, ctx, dev, rank, world, scene):
         out["voxels"], out["nodes"], out["wide_index"], out["device_GB"] = int(info.numberOfVoxels), int(info.numberOfNodes), int(info.wideIndex), round(info.deviceBytes / 1e9, 2)
         out["build_device_ms"] = {k: round(st[k], 1) for k in ("ms_voxelize", "ms_sort", "ms_unique", "ms_octree", "ms_total")}
     if world > 1:
-        torch.cuda.synchronize(dev)
-        dist.barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(stream)
-        g = nd.broadcast_octree(hk.IntersectorOctreeGPU, g, 0, stream=stream)
-        b.record(stream)
-        torch.cuda.synchronize(dev)
-        dist.barrier()
-        ms = mx(a.elapsed_time(b))
+        # replicate twice: the first call makes the receivers' memory pools map 47 GB (host time in front of the collective),
+        # the second is the steady-state replication a frame loop would see
+        src = g
+        times = []
+        for rep in range(2):
+            if rep and rank != 0:
+                g.cleanUp()
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            g = nd.broadcast_octree(hk.IntersectorOctreeGPU, src, 0, stream=stream)
+            b.record(stream)
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            times.append(mx(a.elapsed_time(b)))
         nbytes = sum(nb for _, nb in g.device_arrays())
-        out["broadcast"] = {"device_ms": round(ms, 1), "GB": round(nbytes / 1e9, 2), "GBps": round(nbytes / ms / 1e6, 1)}
+        out["broadcast"] = {"first_ms": round(times[0], 1), "device_ms": round(times[1], 1), "GB": round(nbytes / 1e9, 2), "GBps": round(nbytes / times[1] / 1e6, 1)}
     cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=MW, height=MH, focus=6.0, lensR=0.0)
     t_d = torch.empty(MW * MH, dtype=torch.float32, device=dev)
     nm_d = torch.empty(MW * MH, dtype=torch.int32, device=dev)
