@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "internal.cuh"
+#include "scan.cuh"
 #include "traverse.cuh"
 
 using namespace hako;
@@ -65,6 +66,13 @@ struct hako_pt
 	uint64_t waveCap = 0;
 	int waveRefillMin = 24, waveBurst = 16; // traceWaveKernel knobs (HAKO_PT_REFILL_MIN / HAKO_PT_BURST); B200 sweep in profiles/r1f_pt_sweep.txt
 	int waveTraceCtas = 5;
+	// ray binning in front of every trace wave (HAKO_PT_BIN = bits per axis of the origin grid, 0 = off): the rays of a wave are
+	// counting-sorted by ( kind, direction octant, Morton code of the origin cell ) and the trace kernel draws them in that order
+	uint32_t* binKeys[PT_LANES] = {};
+	uint32_t* binOrder[PT_LANES] = {};
+	uint32_t* binHist[PT_LANES] = {}; // scan state, then one counter per bin
+	uint64_t binCap = 0;
+	int binBits = 0, binCellMajor = 0;
 	uint64_t waveBandPaths = 16u << 20;	  // paths per internal row band of a step (bounds the wavefront buffers)
 	// 0: single persistent kernel (pathTraceKernel<false>); 1: primaryWaveKernel + pathTraceKernel<true>;
 	// 2: full wavefront (primaryWaveKernel, then shadeWaveKernel / traceWaveKernel per vertex).  HAKO_PT_WAVEFRONT overrides
@@ -680,7 +688,102 @@ struct TraceWaveParams
 	int shadowFirst; // ray 0 of every vertex is a shadow ray (any-hit semantics: no voxel-rank accumulation)
 	int refillMin;	 // refill when at least this many lanes of the warp are idle
 	int burst;		 // traversal steps between two refill checks
+	const uint32_t* order; // binned wave: position in the work queue -> ray index (nullptr: identity)
 };
+
+// ---- ray binning: a counting sort of the wave's ray indices --------------------------------------------------------------
+// The results of a ray are written to the slot its (kind, vertex) pair owns, whoever traces it, so the order in which the trace
+// kernel draws rays changes which lanes share a warp and nothing else: the accumulators stay bit-identical.
+#define BIN_SCAN_TILE 4096 // bins per CTA of binScanKernel (1024 threads x 4)
+struct BinParams
+{
+	const WaveVertex* vertices;
+	const float4* dirs;
+	const unsigned long long* nVertices; // nVertices[-1] = pitch of dirs
+	int raysPerVertex;
+	int cellBits;  // per axis
+	int cellMajor; // key = kind | cell | octant instead of kind | octant | cell
+	V3 lower;
+	V3 scale; // cells per world unit
+	uint32_t* keys;	 // [nRays]
+	uint32_t* hist;	 // [bins]: counts, then (after binScanKernel) the running cursors
+	uint32_t* order; // [nRays]
+	uint32_t bins;
+	ScanState scan;
+};
+__device__ __forceinline__ uint32_t binSpread3( uint32_t v ) // 6 bits -> every third bit
+{
+	v = ( v | ( v << 8 ) ) & 0x0000F00Fu;
+	v = ( v | ( v << 4 ) ) & 0x000C30C3u;
+	v = ( v | ( v << 2 ) ) & 0x00249249u;
+	return v;
+}
+__global__ void __launch_bounds__( 256 ) binCountKernel( const BinParams bp )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t nVertices = (uint32_t)*bp.nVertices;
+	const uint32_t stride = (uint32_t)bp.nVertices[-1];
+	const uint32_t nRays = nVertices * (uint32_t)bp.raysPerVertex;
+	const int cmax = ( 1 << bp.cellBits ) - 1;
+	for( uint32_t base = ( blockIdx.x * blockDim.x + threadIdx.x ) & ~31u; base < nRays; base += gridDim.x * blockDim.x )
+	{
+		const uint32_t r = base + lane;
+		const bool valid = r < nRays;
+		uint32_t key = 0xFFFFFFFFu;
+		if( valid )
+		{
+			const uint32_t k = r / nVertices, slot = r - k * nVertices;
+			const float4 o = __ldg( &bp.vertices[slot].a );
+			const float4 d = __ldg( bp.dirs + (size_t)k * stride + slot );
+			const int cx = min( max( (int)( ( o.x - bp.lower.x ) * bp.scale.x ), 0 ), cmax );
+			const int cy = min( max( (int)( ( o.y - bp.lower.y ) * bp.scale.y ), 0 ), cmax );
+			const int cz = min( max( (int)( ( o.z - bp.lower.z ) * bp.scale.z ), 0 ), cmax );
+			const uint32_t cell = binSpread3( (uint32_t)cx ) | ( binSpread3( (uint32_t)cy ) << 1 ) | ( binSpread3( (uint32_t)cz ) << 2 );
+			const uint32_t oct = ( d.x < 0.0f ? 1u : 0u ) | ( d.y < 0.0f ? 2u : 0u ) | ( d.z < 0.0f ? 4u : 0u );
+			const int cb3 = 3 * bp.cellBits;
+			key = bp.cellMajor ? ( ( ( k << cb3 ) | cell ) << 3 ) | oct : ( ( ( k << 3 ) | oct ) << cb3 ) | cell;
+			bp.keys[r] = key;
+		}
+		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, key );
+		if( valid && lane == (uint32_t)( __ffs( peers ) - 1 ) ) atomicAdd( bp.hist + key, (uint32_t)__popc( peers ) );
+	}
+}
+// exclusive scan of the bin counters in place (decoupled look-back over 4 096-bin tiles)
+__global__ void __launch_bounds__( 1024 ) binScanKernel( const BinParams bp )
+{
+	const uint32_t tile = scanTakeTicket( bp.scan );
+	const uint32_t i0 = tile * BIN_SCAN_TILE + threadIdx.x * 4u;
+	uint32_t c[4];
+#pragma unroll
+	for( int j = 0; j < 4; j++ ) c[j] = ( i0 + j < bp.bins ) ? bp.hist[i0 + j] : 0u;
+	uint32_t total = 0;
+	const uint32_t excl = blockExclusiveScan<1024>( c[0] + c[1] + c[2] + c[3], &total );
+	const uint32_t prefix = (uint32_t)scanTilePrefix( bp.scan, tile, (uint64_t)total );
+	uint32_t run = prefix + excl;
+#pragma unroll
+	for( int j = 0; j < 4; j++ )
+	{
+		if( i0 + j < bp.bins ) bp.hist[i0 + j] = run;
+		run += c[j];
+	}
+}
+__global__ void __launch_bounds__( 256 ) binScatterKernel( const BinParams bp )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t nRays = (uint32_t)*bp.nVertices * (uint32_t)bp.raysPerVertex;
+	for( uint32_t base = ( blockIdx.x * blockDim.x + threadIdx.x ) & ~31u; base < nRays; base += gridDim.x * blockDim.x )
+	{
+		const uint32_t r = base + lane;
+		const bool valid = r < nRays;
+		const uint32_t key = valid ? __ldcs( bp.keys + r ) : 0xFFFFFFFFu;
+		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, key );
+		const int leader = __ffs( peers ) - 1;
+		uint32_t pos = 0;
+		if( valid && (int)lane == leader ) pos = atomicAdd( bp.hist + key, (uint32_t)__popc( peers ) );
+		pos = __shfl_sync( 0xFFFFFFFFu, pos, leader );
+		if( valid ) bp.order[pos + __popc( peers & ( ( 1u << lane ) - 1u ) )] = r;
+	}
+}
 template <int MIN_CTAS, int TOPK = 0>
 __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const OctreeView tree, const TraceWaveParams tp )
 {
@@ -727,7 +830,7 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 				const uint32_t avail = wEnd - wNext;
 				if( !flying && rank < avail )
 				{
-					const uint32_t ray = wNext + rank;
+					const uint32_t ray = tp.order ? __ldg( tp.order + wNext + rank ) : wNext + rank;
 					const uint32_t k = ray / nVertices, slot = ray - k * nVertices;
 					addr = k * stride + slot;
 					const float4 o = __ldg( &tp.vertices[slot].a );
@@ -978,6 +1081,8 @@ int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out )
 	if( const char* e = getenv( "HAKO_PT_TRACE_CTAS" ) ) pt->waveTraceCtas = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_BAND_PATHS" ) ) pt->waveBandPaths = strtoull( e, nullptr, 10 );
 	if( const char* e = getenv( "HAKO_PT_LANES" ) ) pt->lanes = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_BIN" ) ) pt->binBits = std::max( 0, std::min( 6, atoi( e ) ) );
+	if( const char* e = getenv( "HAKO_PT_BIN_CELL_MAJOR" ) ) pt->binCellMajor = atoi( e ) != 0;
 	pt->lanes = std::max( 1, std::min( PT_LANES, pt->lanes ) );
 	std::vector<float> table( (size_t)2 * PMJ_LENGTH * PMJ_NSEQ );
 	HostPCG32 rng;
@@ -1019,6 +1124,7 @@ void hako_pt_destroy( hako_pt* pt )
 		if( pt->laneStream[k] ) cudaStreamSynchronize( pt->laneStream[k] );
 		for( int i = 0; i < 2; i++ ) dfree( pt->waveV[k][i], s ), dfree( pt->waveDir[k][i], s );
 		dfree( pt->waveRes[k], s );
+		dfree( pt->binKeys[k], s ), dfree( pt->binOrder[k], s ), dfree( pt->binHist[k], s );
 		if( pt->laneStream[k] ) cudaStreamDestroy( pt->laneStream[k] );
 	}
 	for( int k = 0; k <= PT_LANES; k++ )
@@ -1239,6 +1345,26 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 			}
 			pt->waveCap = bandCap;
 		}
+		// bins of a trace wave: ( up to 3 ray kinds ) x 8 octants x cells, scanned in tiles of BIN_SCAN_TILE
+		const uint32_t bins = pt->binBits ? ( 3u * 8u ) << ( 3 * pt->binBits ) : 0u;
+		const uint32_t binTiles = ( bins + BIN_SCAN_TILE - 1 ) / BIN_SCAN_TILE;
+		const uint64_t binStateWords = ( scanStateBytes( binTiles ) + 3 ) / 4;
+		if( bins && pt->binCap < bandCap )
+		{
+			for( int k = 0; k < PT_LANES; k++ )
+			{
+				dfree( pt->binKeys[k], s ), dfree( pt->binOrder[k], s ), dfree( pt->binHist[k], s );
+				pt->binKeys[k] = pt->binOrder[k] = pt->binHist[k] = nullptr;
+			}
+			pt->binCap = 0;
+			for( int k = 0; k < lanes; k++ )
+			{
+				HAKO_TRY( dalloc( ctx, &pt->binKeys[k], bandCap * 3, s ) );
+				HAKO_TRY( dalloc( ctx, &pt->binOrder[k], bandCap * 3, s ) );
+				HAKO_TRY( dalloc( ctx, &pt->binHist[k], binStateWords + bins, s ) );
+			}
+			pt->binCap = bandCap;
+		}
 		// occupancy target of the trace kernel: 5 CTAs/SM = 48 registers, 6 = 40, 8 = 32 (HAKO_PT_TRACE_CTAS)
 		auto kTrace5 = traceWaveKernel<5>;
 		auto kTrace6 = traceWaveKernel<6>;
@@ -1298,6 +1424,25 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 				tp.shadowFirst = envOn ? 1 : 0;
 				tp.refillMin = std::max( 1, std::min( 32, pt->waveRefillMin ) );
 				tp.burst = std::max( 1, pt->waveBurst );
+				tp.order = nullptr;
+				if( bins )
+				{
+					BinParams bp;
+					bp.vertices = tp.vertices, bp.dirs = tp.dirs, bp.nVertices = tp.nVertices, bp.raysPerVertex = tp.raysPerVertex;
+					bp.cellBits = pt->binBits, bp.cellMajor = pt->binCellMajor;
+					bp.lower = q.tree.lower;
+					const float cells = (float)( 1 << pt->binBits );
+					bp.scale = V3{ cells / ( q.tree.upper.x - q.tree.lower.x ), cells / ( q.tree.upper.y - q.tree.lower.y ), cells / ( q.tree.upper.z - q.tree.lower.z ) };
+					bp.keys = pt->binKeys[lane], bp.order = pt->binOrder[lane];
+					bp.hist = pt->binHist[lane] + binStateWords;
+					bp.bins = bins;
+					bp.scan = makeScanState( pt->binHist[lane], binTiles );
+					HAKO_CUDA( cudaMemsetAsync( pt->binHist[lane], 0, ( binStateWords + bins ) * sizeof( uint32_t ), ls ) );
+					HAKO_LAUNCH( ctx, binCountKernel, shadeGrid, 256, 0, ls, bp );
+					HAKO_LAUNCH( ctx, binScanKernel, binTiles, 1024, 0, ls, bp );
+					HAKO_LAUNCH( ctx, binScatterKernel, shadeGrid, 256, 0, ls, bp );
+					tp.order = bp.order;
+				}
 				if( topEnv == 512 )
 					HAKO_LAUNCH( ctx, kTrace5Top, traceGrid, 256, 0, ls, q.tree, tp );
 				else if( occ == 8 )

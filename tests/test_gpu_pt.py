@@ -153,8 +153,8 @@ def test_step_is_deterministic_and_shards_by_rows(hk, ctx, pt, scene):
 @pytest.mark.parametrize("with_env,with_emission,max_depth", [(True, True, 4), (True, False, 8), (False, True, 3), (True, True, 0)])
 def test_pt_modes_identical(hk, ctx, pt, scene, monkeypatch, with_env, with_emission, max_depth):
     """the single persistent kernel, the primary-wave + continuation pair and the full wavefront (also split into row bands on
-    1, 3 or 4 concurrent lanes, with different refill knobs) evaluate the same fp32 expressions per path: accumulators and ray
-    counts are bit-identical"""
+    1, 3 or 4 concurrent lanes, with different refill knobs, with and without ray binning) evaluate the same fp32 expressions per
+    path: accumulators and ray counts are bit-identical"""
     W, H = 100, 52          # not a multiple of the 4x4 primary tiles
     s = scene
     emi = s["emi"] if with_emission else np.zeros_like(s["emi"])
@@ -166,8 +166,12 @@ def test_pt_modes_identical(hk, ctx, pt, scene, monkeypatch, with_env, with_emis
                 {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BAND_PATHS": str(W * 16 * 12), "HAKO_PT_REFILL_MIN": "1", "HAKO_PT_BURST": "3"},
                 {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_REFILL_MIN": "32", "HAKO_PT_BURST": "1"},
                 {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_LANES": "1"},
-                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_LANES": "4", "HAKO_PT_BAND_PATHS": str(W * 16 * 4)}):
-        for k in ("HAKO_PT_WAVEFRONT", "HAKO_PT_BAND_PATHS", "HAKO_PT_REFILL_MIN", "HAKO_PT_BURST", "HAKO_PT_LANES"):
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_LANES": "4", "HAKO_PT_BAND_PATHS": str(W * 16 * 4)},
+                # rays of every trace wave binned by (kind, octant, origin cell): another order of the same rays
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "4"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "6", "HAKO_PT_BIN_CELL_MAJOR": "1", "HAKO_PT_LANES": "2"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "1", "HAKO_PT_BAND_PATHS": str(W * 16 * 12)}):
+        for k in ("HAKO_PT_WAVEFRONT", "HAKO_PT_BAND_PATHS", "HAKO_PT_REFILL_MIN", "HAKO_PT_BURST", "HAKO_PT_LANES", "HAKO_PT_BIN", "HAKO_PT_BIN_CELL_MAJOR"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)

@@ -12,10 +12,10 @@ vals = torch.arange(n, dtype=torch.int64, device='cuda')
 small_k = torch.randint(0, 1 << 20, (1_000_003,), dtype=torch.int64, device='cuda', generator=g)   # odd length, many duplicates
 small_v = torch.arange(small_k.numel(), dtype=torch.int64, device='cuda')
 ref_k, ref_i = torch.sort(small_k, stable=True)
-for variant in [int(v) for v in os.environ.get('PROBE_VARIANTS', '0,1,2,3').split(',')]:
+for variant in [int(v) for v in os.environ.get('PROBE_VARIANTS', '0,1,2,3,4').split(',')]:
     os.environ['HAKO_SORT_VARIANT'] = str(variant)
     k, v = small_k.clone(), small_v.clone()
-    ctx.sort_pairs_device(k, v, 0, 20); torch.cuda.synchronize()
+    ctx.sort_pairs_device(k, v, 0, 27); torch.cuda.synchronize()   # 27-bit window: three 9-bit passes
     ok = bool(torch.equal(k, ref_k) and torch.equal(v, ref_i))
     times = []
     for rep in range(5):
