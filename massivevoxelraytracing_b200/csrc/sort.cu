@@ -646,6 +646,9 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 // of a cluster take CL consecutive tiles, exchange their per-digit counts through distributed shared memory (one cluster barrier), and
 // the decoupled look-back runs over CLUSTERS: CL times fewer descriptors, CL times more keys per round trip.  Every CTA of the cluster
 // walks the (same) cluster chain itself -- no second barrier; CTA 0 publishes.
+// MEASURED AND NOT ADOPTED: correct (stable) but slower than the bulk pass -- 2 / 4 / 8 CTAs per cluster 4.52 / 4.49 / 4.78 ms against 3.44 ms
+// for 72.7 M pairs x 36 bits (profiles/r2v_sort_cluster.log): the tile loads cannot start before the whole cluster runs (barrier 0), and
+// barrier 1 makes every tile wait for the slowest ranking of its cluster, which costs more than the look-back round trips it saves.
 __device__ __forceinline__ uint32_t clusterCtaRank()
 {
 	uint32_t r;
@@ -970,6 +973,8 @@ int launchClusterRP( hako_ctx* ctx, cudaStream_t s, int cl, bool d32, uint32_t t
 
 // variants of the bulk-copy pass: block size x items per thread x resident CTAs per SM (HAKO_SORT_VARIANT)
 //   1: 256 x 15 x 3 (3 840-pair tiles, 71 KB)   2: 512 x 8 x 2 (4 096-pair tiles, 83 KB)   3: 256 x 16 x 2 (4 096, 79 KB)
+//   4: the cluster pass above.  Smaller tiles at higher occupancy were measured and dropped: 256 x 10 x 4 3.95 ms, 256 x 7 x 5 4.82 ms
+//   against 3.45 ms for variant 1 (profiles/r2w_sort_tiles.log); the cluster pass 4.49-4.78 ms (profiles/r2v_sort_cluster.log).
 int sortVariantTile( int variant ) { return ( variant == 1 || variant == 4 ) ? 256 * 15 : ( variant == 0 ? SORT_TILE : 4096 ); }
 template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0>
 int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t* kin, const uint64_t* vin, uint64_t* kout, uint64_t* vout, uint64_t n, int shift, uint32_t mask,
