@@ -173,6 +173,107 @@ __global__ void __launch_bounds__( OB_BLOCK ) groupBuildKernel( const uint64_t* 
 	}
 }
 
+// ---- DAG, leaf level: the groups of the voxels themselves ----
+// Same result as groupBuildKernel<true, true> (parent key, voxel count and child mask of every group of <= 8 sibling voxels, plus the
+// first group of each of the 255 masks), restructured like uniqueMergeKernel: 8 keys per thread in registers and ONE pass over them with a
+// running mask (the generic kernel re-reads the <= 8 members of every group from global memory), warp 0 resolves the tile's offset by
+// look-back while the other warps already build their masks, and the groups leave through shared memory as contiguous, coalesced rows.
+constexpr int LG_ITEMS = 8;
+constexpr int LG_TILE = OB_BLOCK * LG_ITEMS;
+__global__ void __launch_bounds__( OB_BLOCK, 4 ) leafGroupDagKernel( const uint64_t* __restrict__ mortons, uint64_t n, ScanState st, uint64_t* __restrict__ nextMorton,
+																	 uint32_t* __restrict__ nextVox, uint8_t* __restrict__ groupMask, uint32_t* __restrict__ leafFirst /* [256] */ )
+{
+	__shared__ uint32_t s_first[256];
+	__shared__ uint64_t s_parent[LG_TILE];
+	__shared__ uint8_t s_mask[LG_TILE];
+	__shared__ unsigned long long s_prefix;
+	s_first[threadIdx.x] = SENTINEL;
+	const uint32_t tile = scanTakeTicket( st ); // has a __syncthreads
+	const uint64_t base = (uint64_t)tile * LG_TILE + (uint64_t)threadIdx.x * LG_ITEMS;
+	uint64_t m[LG_ITEMS];
+	if( base + LG_ITEMS <= n )
+	{
+#pragma unroll
+		for( int i = 0; i < LG_ITEMS; i += 2 )
+		{
+			const ulonglong2 mm = *reinterpret_cast<const ulonglong2*>( mortons + base + i );
+			m[i] = mm.x, m[i + 1] = mm.y;
+		}
+	}
+	else
+	{
+#pragma unroll
+		for( int i = 0; i < LG_ITEMS; i++ ) m[i] = ( base + i < n ) ? mortons[base + i] : 0ull;
+	}
+	uint32_t heads = 0, nHeads = 0;
+	uint64_t prev = ( base > 0 && base <= n ) ? mortons[base - 1] : 0ull;
+#pragma unroll
+	for( int i = 0; i < LG_ITEMS; i++ )
+	{
+		const uint64_t idx = base + i;
+		const bool head = ( idx < n ) && ( idx == 0 || ( m[i] >> 3 ) != ( prev >> 3 ) );
+		prev = m[i];
+		if( head )
+		{
+			heads |= 1u << i;
+			nHeads++;
+		}
+	}
+	uint32_t total;
+	const uint32_t excl = blockExclusiveScan<OB_BLOCK>( nHeads, &total );
+	if( threadIdx.x < 32 )
+	{
+		const uint64_t pre = scanTilePrefixWarp( st, tile, total );
+		if( threadIdx.x == 0 ) s_prefix = pre;
+	}
+	uint32_t slot = excl, mask = 0;
+	uint64_t parent = 0;
+	bool open = false;
+#pragma unroll
+	for( int i = 0; i < LG_ITEMS; i++ )
+	{
+		if( ( heads >> i ) & 1u )
+		{
+			if( open )
+			{
+				s_parent[slot] = parent;
+				s_mask[slot] = (uint8_t)mask;
+				slot++;
+			}
+			parent = m[i] >> 3;
+			mask = 0;
+			open = true;
+		}
+		if( open && base + i < n ) mask |= 1u << (uint32_t)( m[i] & 7u );
+	}
+	if( open )
+	{
+		// the thread's last group may continue in the keys of the following threads (at most 7 more)
+		for( uint64_t j = base + LG_ITEMS; j < n; j++ )
+		{
+			const uint64_t mj = mortons[j];
+			if( ( mj >> 3 ) != parent ) break;
+			mask |= 1u << (uint32_t)( mj & 7u );
+		}
+		s_parent[slot] = parent;
+		s_mask[slot] = (uint8_t)mask;
+	}
+	__syncthreads();
+	const uint64_t prefix = s_prefix;
+	for( uint32_t i = threadIdx.x; i < total; i += OB_BLOCK )
+	{
+		const uint32_t g = (uint32_t)prefix + i;
+		const uint32_t mk = s_mask[i];
+		nextMorton[g] = s_parent[i];
+		nextVox[g] = (uint32_t)__popc( mk ); // one voxel per set child bit
+		groupMask[g] = (uint8_t)mk;
+		if( s_first[mk] > g ) atomicMin( &s_first[mk], g );
+	}
+	__syncthreads();
+	const uint32_t f = s_first[threadIdx.x];
+	if( f != SENTINEL ) atomicMin( &leafFirst[threadIdx.x], f );
+}
+
 // ---- DAG, leaf level: <= 255 distinct masks ----
 __global__ void __launch_bounds__( 256 ) leafRankKernel( const uint32_t* __restrict__ leafFirst, uint32_t* __restrict__ leafIndexOfMask,
 														 TraceNode* __restrict__ nodes, uint8_t* __restrict__ masks, LevelState* __restrict__ ls )
@@ -466,7 +567,10 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 		uint32_t naiveBase = 0;
 		for( int l = 0; l < levels && r == 0; l++ )
 		{
-			const uint64_t tiles = ( nTasks + OB_TILE - 1 ) / OB_TILE;
+			static const bool genericLeaf = getenv( "HAKO_OCTREE_GENERIC_LEAF" ) && atoi( getenv( "HAKO_OCTREE_GENERIC_LEAF" ) ) != 0; // A/B knob
+			const bool fastLeaf = dag && l == 0 && !genericLeaf && ( ( (uintptr_t)mortons & 15u ) == 0 );
+			const uint64_t tileSize = fastLeaf ? LG_TILE : OB_TILE;
+			const uint64_t tiles = ( nTasks + tileSize - 1 ) / tileSize;
 			ScanState st;
 			if( ( r = zeroedScanState( ctx, s, tiles, &scanMem, &st ) ) ) break;
 			const uint32_t Gl = (uint32_t)G[l];
@@ -475,8 +579,11 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 				if( l == 0 )
 				{
 					CK( cudaMemsetAsync( leafTables, 0xFF, 512 * 4, s ) );
-					HAKO_LAUNCH_R( ctx, r, kLeafDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
-								 leafTables, nodes, masks, 0u, wide );
+					if( fastLeaf )
+						HAKO_LAUNCH_R( ctx, r, leafGroupDagKernel, (uint32_t)tiles, OB_BLOCK, 0, s, tM, nTasks, st, nM, nV, groupMask, leafTables );
+					else
+						HAKO_LAUNCH_R( ctx, r, kLeafDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
+									 leafTables, nodes, masks, 0u, wide );
 					HAKO_LAUNCH_R( ctx, r, leafRankKernel, 1, 256, 0, s, leafTables, leafTables + 256, nodes, masks, ls );
 					HAKO_LAUNCH_R( ctx, r, leafAssignKernel, divUp( Gl, 256 ), 256, 0, s, groupMask, Gl, leafTables + 256, nC, wide );
 				}

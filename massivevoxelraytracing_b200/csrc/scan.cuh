@@ -43,6 +43,44 @@ __device__ __forceinline__ uint32_t scanTakeTicket( const ScanState& st )
 __device__ __forceinline__ unsigned long long ldVolatile( const unsigned long long* p ) { return *(const volatile unsigned long long*)p; }
 __device__ __forceinline__ void stVolatile( unsigned long long* p, unsigned long long v ) { *(volatile unsigned long long*)p = v; }
 
+// The look-back itself, for ONE warp (all 32 lanes call it with the tile's total): publishes the tile's aggregate, walks back over the
+// predecessors 32 at a time, publishes the inclusive prefix and returns the exclusive one (to every lane).  A kernel whose other warps
+// have work that does not need the prefix calls this from warp 0 and synchronises later (uniqueMergeKernel).
+__device__ __forceinline__ uint64_t scanTilePrefixWarp( const ScanState& st, uint32_t tile, uint64_t tileTotal )
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	if( tile == 0 )
+	{
+		if( lane == 0 ) stVolatile( &st.desc[0], SCAN_FLAG_INC | tileTotal );
+		return 0;
+	}
+	if( lane == 0 ) stVolatile( &st.desc[tile], SCAN_FLAG_AGG | tileTotal );
+	uint64_t prefix = 0;
+	int64_t base = (int64_t)tile - 1; // lane l inspects tile base - l
+	for( ;; )
+	{
+		const int64_t idx = base - lane;
+		unsigned long long d = SCAN_FLAG_INC; // virtual tiles before 0: inclusive prefix 0
+		if( idx >= 0 )
+		{
+			do
+			{
+				d = ldVolatile( &st.desc[idx] );
+			} while( ( d >> 62 ) == 0 );
+		}
+		const uint32_t incMask = __ballot_sync( 0xFFFFFFFFu, ( d >> 62 ) == 2 );
+		const uint32_t firstInc = incMask ? ( __ffs( incMask ) - 1 ) : 32u;
+		uint64_t v = ( lane <= firstInc ) ? ( d & SCAN_VALUE_MASK ) : 0ull;
+#pragma unroll
+		for( int o = 16; o > 0; o >>= 1 ) v += __shfl_xor_sync( 0xFFFFFFFFu, v, o );
+		prefix += v;
+		if( incMask ) break;
+		base -= 32;
+	}
+	if( lane == 0 ) stVolatile( &st.desc[tile], SCAN_FLAG_INC | ( prefix + tileTotal ) );
+	return prefix;
+}
+
 // Called by ALL threads of the block with the tile's total (valid in thread 0 at least); returns the exclusive prefix of the
 // tile (sum of the totals of tiles 0..tile-1) to all threads.  Warp 0 does the look-back.
 __device__ __forceinline__ uint64_t scanTilePrefix( const ScanState& st, uint32_t tile, uint64_t tileTotal )
@@ -50,47 +88,9 @@ __device__ __forceinline__ uint64_t scanTilePrefix( const ScanState& st, uint32_
 	__shared__ unsigned long long s_prefix;
 	if( threadIdx.x < 32 )
 	{
-		const uint32_t lane = threadIdx.x;
 		tileTotal = __shfl_sync( 0xFFFFFFFFu, tileTotal, 0 );
-		if( tile == 0 )
-		{
-			if( lane == 0 )
-			{
-				stVolatile( &st.desc[0], SCAN_FLAG_INC | tileTotal );
-				s_prefix = 0;
-			}
-		}
-		else
-		{
-			if( lane == 0 ) stVolatile( &st.desc[tile], SCAN_FLAG_AGG | tileTotal );
-			uint64_t prefix = 0;
-			int64_t base = (int64_t)tile - 1; // lane l inspects tile base - l
-			for( ;; )
-			{
-				const int64_t idx = base - lane;
-				unsigned long long d = SCAN_FLAG_INC; // virtual tiles before 0: inclusive prefix 0
-				if( idx >= 0 )
-				{
-					do
-					{
-						d = ldVolatile( &st.desc[idx] );
-					} while( ( d >> 62 ) == 0 );
-				}
-				const uint32_t incMask = __ballot_sync( 0xFFFFFFFFu, ( d >> 62 ) == 2 );
-				const uint32_t firstInc = incMask ? ( __ffs( incMask ) - 1 ) : 32u;
-				uint64_t v = ( lane <= firstInc ) ? ( d & SCAN_VALUE_MASK ) : 0ull;
-#pragma unroll
-				for( int o = 16; o > 0; o >>= 1 ) v += __shfl_xor_sync( 0xFFFFFFFFu, v, o );
-				prefix += v;
-				if( incMask ) break;
-				base -= 32;
-			}
-			if( lane == 0 )
-			{
-				stVolatile( &st.desc[tile], SCAN_FLAG_INC | ( prefix + tileTotal ) );
-				s_prefix = prefix;
-			}
-		}
+		const uint64_t prefix = scanTilePrefixWarp( st, tile, tileTotal );
+		if( threadIdx.x == 0 ) s_prefix = prefix;
 	}
 	__syncthreads();
 	return s_prefix;

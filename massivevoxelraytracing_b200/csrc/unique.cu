@@ -20,7 +20,7 @@ constexpr int UQ_ITEMS = 8;
 constexpr int UQ_TILE = UQ_BLOCK * UQ_ITEMS;
 } // namespace
 
-__global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t* __restrict__ keys, const uint64_t* __restrict__ values, uint64_t n,
+__global__ void __launch_bounds__( UQ_BLOCK, 4 ) uniqueMergeKernel( const uint64_t* __restrict__ keys, const uint64_t* __restrict__ values, uint64_t n,
 																 uint64_t* __restrict__ keysOut, uint64_t* __restrict__ attrsOut, ScanState st,
 																 unsigned long long* __restrict__ counters /* [0] = U, [1] = hasEmission */ )
 {
@@ -65,7 +65,14 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 	}
 	uint32_t total;
 	const uint32_t excl = blockExclusiveScan<UQ_BLOCK>( nHeads, &total );
-	const uint64_t prefix = scanTilePrefix( st, tile, total );
+	// warp 0 resolves the tile's global offset while the other warps already merge their runs (which needs only the tile-local slots);
+	// everyone meets at the barrier in front of the write-out
+	__shared__ unsigned long long s_prefix;
+	if( threadIdx.x < 32 )
+	{
+		const uint64_t pre = scanTilePrefixWarp( st, tile, total );
+		if( threadIdx.x == 0 ) s_prefix = pre;
+	}
 	// The merged voxels of the tile are staged in shared memory in output order and written out as one contiguous, coalesced
 	// block (a thread's own outputs are a strided dribble of up to 8 entries).
 	__shared__ uint64_t s_outK[UQ_TILE];
@@ -91,7 +98,18 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 		uint32_t q0 = c0, q1 = c1, q2 = c2, r0 = e0, r1 = e1, r2 = e2;
 		if( cnt > 1 )
 		{
-			q0 /= cnt, q1 /= cnt, q2 /= cnt, r0 /= cnt, r1 /= cnt, r2 /= cnt;
+			if( cnt <= 4096u )
+			{
+				// six quotients by one divisor: m = ceil( 2^32 / cnt ), q = floor( c * m / 2^32 ).  With e = m * cnt - 2^32 in [0, cnt)
+				// the product overshoots c / cnt by c * e / ( cnt * 2^32 ) < 1 / cnt whenever c * cnt < 2^32, and c <= 255 * cnt, so
+				// the floor is exact for cnt <= 4 103 (one u32 division per run instead of six: they were ~40 % of this kernel's
+				// instructions)
+				const uint32_t m = 0xFFFFFFFFu / cnt + 1u;
+				q0 = __umulhi( q0, m ), q1 = __umulhi( q1, m ), q2 = __umulhi( q2, m );
+				r0 = __umulhi( r0, m ), r1 = __umulhi( r1, m ), r2 = __umulhi( r2, m );
+			}
+			else
+				q0 /= cnt, q1 /= cnt, q2 /= cnt, r0 /= cnt, r1 /= cnt, r2 /= cnt;
 		}
 		anyEmission |= r0 | r1 | r2;
 		s_outK[slot] = kcur;
@@ -123,6 +141,7 @@ __global__ void __launch_bounds__( UQ_BLOCK ) uniqueMergeKernel( const uint64_t*
 		emit();
 	}
 	__syncthreads();
+	const uint64_t prefix = s_prefix;
 	for( uint32_t i = threadIdx.x; i < total; i += UQ_BLOCK )
 	{
 		keysOut[prefix + i] = s_outK[i];

@@ -194,6 +194,30 @@ def test_unique_long_runs(hk, ctx, oracle):
     assert uk.size == 0
 
 
+def test_unique_integer_means_are_exact_for_every_run_length(hk, ctx, oracle):
+    """the integer means of a run (voxRT.cpp:38-47) for run lengths 1..300, around the 4 096 boundary below which the kernel divides by
+    multiplying with ceil(2^32 / count), and far above it; channel sums at their extremes (all 255, all 0, one 255)"""
+    rng = np.random.default_rng(10)
+    lengths = list(range(1, 301)) + [4095, 4096, 4097, 4103, 4104, 9001, 70000]
+    keys = np.repeat(np.arange(len(lengths), dtype=np.uint64) * 3 + 7, lengths)
+    attrs = np.zeros(keys.size, hk.VOXEL_ATTRIB)
+    attrs["color"] = rng.integers(0, 256, (keys.size, 4), dtype=np.uint8)
+    attrs["emission"] = rng.integers(0, 256, (keys.size, 4), dtype=np.uint8)
+    start = np.concatenate([[0], np.cumsum(lengths)])
+    for i in range(0, len(lengths), 3):         # every third run saturated: sum = 255 * count, the largest dividend
+        attrs["color"][start[i]:start[i + 1]] = 255
+        attrs["emission"][start[i]:start[i + 1]] = 255
+    for i in range(1, len(lengths), 3):         # one 255 among zeros: quotient 0 unless the run has one voxel ... 255 / count
+        attrs["color"][start[i]:start[i + 1]] = 0
+        attrs["color"][start[i]] = 255
+    mk, mc, me = oracle.merge_voxels(keys, attrs["color"], attrs["emission"])
+    uk, ua, he = ctx.unique_merge(keys, attrs)
+    np.testing.assert_array_equal(uk, mk)
+    np.testing.assert_array_equal(ua["color"][:, :3], mc[:, :3])
+    np.testing.assert_array_equal(ua["emission"][:, :3], me[:, :3])
+    assert he
+
+
 # ---------------------------------------------------------------- octree
 def _cmp_nodes(a, b):
     assert a.size == b.size
