@@ -1005,6 +1005,10 @@ int launchClusterRP( hako_ctx* ctx, cudaStream_t s, int cl, bool d32, uint32_t t
 //   1: 256 x 15 x 3 (3 840-pair tiles, 71 KB)   2: 512 x 8 x 2 (4 096-pair tiles, 83 KB)   3: 256 x 16 x 2 (4 096, 79 KB)
 //   4: the cluster pass above.  Smaller tiles at higher occupancy were measured and dropped: 256 x 10 x 4 3.95 ms, 256 x 7 x 5 4.82 ms
 //   against 3.45 ms for variant 1 (profiles/r2w_sort_tiles.log); the cluster pass 4.49-4.78 ms (profiles/r2v_sort_cluster.log).
+//   Not staging the value tile (L2 prefetch at entry, late loads into registers, a u16 digit per sorted position instead of the
+//   destinations in registers) buys a 4th / 5th CTA per SM and nothing else: 256 x 15 x 4 3.55 ms, 256 x 12 x 5 3.88 ms
+//   (profiles/r3b_sort_latev.log).  More tiles in flight only lengthen every look-back walk: the pass is bound by how fast inclusive
+//   prefixes propagate from tile to tile, not by occupancy.
 int sortVariantTile( int variant ) { return ( variant == 1 || variant == 4 || variant == 5 ) ? 256 * 15 : ( variant == 6 ? 256 * 12 : ( variant == 0 ? SORT_TILE : 4096 ) ); }
 template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0, bool LATEV = false>
 int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t* kin, const uint64_t* vin, uint64_t* kout, uint64_t* vout, uint64_t n, int shift, uint32_t mask,
