@@ -328,10 +328,7 @@ __device__ unsigned long long g_sortProf[16];
 	} while( 0 )
 #endif
 
-// LATEV: the value tile is not staged in shared memory (only prefetched into L2 at kernel entry and read straight into registers when
-// the keys have left); a u16 digit per sorted position takes its place so that the destinations need not stay in registers.  23 KB less
-// per CTA: 4 CTAs/SM instead of 3.
-template <int RBITS, int BLOCK, int ITEMS, bool LATEV = false>
+template <int RBITS, int BLOCK, int ITEMS>
 struct SortV2Smem
 {
 	static constexpr int RADIX = 1 << RBITS;
@@ -339,7 +336,7 @@ struct SortV2Smem
 	static constexpr int TILE = BLOCK * ITEMS;
 	static constexpr size_t OFF_KEYS = 0;								 // u64[TILE]: key tile, later the sorted staging buffer
 	static constexpr size_t OFF_VALUES = OFF_KEYS + (size_t)TILE * 8;	 // u64[TILE]: value tile in input order
-	static constexpr size_t OFF_GBASE = OFF_VALUES + (size_t)TILE * ( LATEV ? 2 : 8 ); // u64[RADIX]
+	static constexpr size_t OFF_GBASE = OFF_VALUES + (size_t)TILE * 8;	 // u64[RADIX]
 	static constexpr size_t OFF_TBASE = OFF_GBASE + (size_t)RADIX * 8;	 // u32[RADIX]
 	static constexpr size_t OFF_WHIST = OFF_TBASE + (size_t)RADIX * 4;	 // u16[WARPS][RADIX]
 	static constexpr size_t OFF_WTOT = OFF_WHIST + (size_t)WARPS * RADIX * 2; // u32[WARPS]
@@ -353,7 +350,7 @@ struct SortV2Smem
 // (profiles/r2s..r2u_sort_knobs.log, tools/sort_phase_probe.py): 64-bit + match + atomic 4.00 ms, D32 3.82, D32 + ballots + plain 3.43;
 // LB = 4 with D32 3.53-3.78.  A tile's life is then ~35 000 cycles: ranking 9 600, look-back 11 400 (8.6 round trips, 2 polls of
 // descriptors not yet published), the data movement itself (tile in, two shared-memory scatters, two write-outs) the remaining 40 %.
-template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0, bool LATEV = false>
+template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0>
 __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
 																 uint64_t* __restrict__ keysOut, uint64_t* __restrict__ valuesOut, uint64_t n,
 																 int shift, uint32_t mask, const unsigned long long* __restrict__ digitBase /* [RADIX] exclusive */,
@@ -363,13 +360,12 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 	constexpr int FSH = D32 ? 30 : 62;
 	constexpr DescT F_AGG = (DescT)1 << FSH, F_INC = (DescT)2 << FSH, V_MASK = ( (DescT)1 << FSH ) - 1;
 	DescT* __restrict__ lookback = (DescT*)lookbackRaw;
-	using L = SortV2Smem<RBITS, BLOCK, ITEMS, LATEV>;
+	using L = SortV2Smem<RBITS, BLOCK, ITEMS>;
 	constexpr int RADIX = L::RADIX, WARPS = L::WARPS, TILE = L::TILE;
 	constexpr int DPT = ( RADIX + BLOCK - 1 ) / BLOCK; // digits per thread in the per-digit phase (threads beyond RADIX / DPT idle there)
 	extern __shared__ __align__( 128 ) unsigned char s_raw[];
 	uint64_t* s_keys = (uint64_t*)( s_raw + L::OFF_KEYS );
 	uint64_t* s_values = (uint64_t*)( s_raw + L::OFF_VALUES );
-	uint16_t* s_digit = (uint16_t*)( s_raw + L::OFF_VALUES ); // LATEV
 	unsigned long long* s_globalBase = (unsigned long long*)( s_raw + L::OFF_GBASE );
 	uint32_t* s_tileBase = (uint32_t*)( s_raw + L::OFF_TBASE );
 	uint16_t* s_warpHist = (uint16_t*)( s_raw + L::OFF_WHIST ); // [WARPS][RADIX]
@@ -395,12 +391,11 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 		{
 			mbarExpectTx( &s_bar[0], bytes );
 			bulkLoad( s_keys, keysIn + start, bytes, &s_bar[0] );
-			if( PAIRS && !LATEV )
+			if( PAIRS )
 			{
 				mbarExpectTx( &s_bar[1], bytes );
 				bulkLoad( s_values, valuesIn + start, bytes, &s_bar[1] );
 			}
-			if( PAIRS && LATEV ) asm volatile( "cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"( valuesIn + start ), "r"( bytes ) : "memory" );
 		}
 	}
 	for( int i = threadIdx.x; i < WARPS * RADIX / 2; i += BLOCK ) ( (uint32_t*)s_warpHist )[i] = 0;
@@ -613,47 +608,22 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 		if( p < tileCount )
 		{
 			const uint64_t k = s_keys[p];
-			const uint32_t dg = digitOf( k, shift, mask );
-			if( LATEV )
-			{
-				s_digit[p] = (uint16_t)dg;
-				keysOut[s_globalBase[dg] + p] = k;
-			}
-			else
-			{
-				dst[i] = s_globalBase[dg] + p;
-				keysOut[dst[i]] = k;
-			}
+			dst[i] = s_globalBase[digitOf( k, shift, mask )] + p;
+			keysOut[dst[i]] = k;
 		}
 	}
 	SORT_PROF_MARK( 7 ); // key stores issued
 	if( PAIRS )
 	{
 		// the value tile has been in flight since kernel entry
-		uint64_t val[LATEV ? ITEMS : 1];
-		if( LATEV )
-		{
-#pragma unroll
-			for( int i = 0; i < ITEMS; i++ )
-			{
-				const uint32_t idx = warpBase + i * 32 + lane;
-				if( idx < tileCount ) val[i] = __ldcs( valuesIn + tileStart + idx ); // L2 hits (prefetched at entry), read once
-			}
-		}
-		else if( bulk )
-			mbarWait( &s_bar[1], 0 );
+		if( bulk ) mbarWait( &s_bar[1], 0 );
 		__syncthreads(); // the sorted keys have left s_keys
 		SORT_PROF_MARK( 8 );
 #pragma unroll
 		for( int i = 0; i < ITEMS; i++ )
 		{
 			const uint32_t idx = warpBase + i * 32 + lane;
-			if( LATEV )
-			{
-				if( idx < tileCount ) s_keys[rank[i]] = val[i];
-			}
-			else if( idx < tileCount )
-				s_keys[rank[i]] = ( oddTail && idx == tileCount - 1 ) ? valuesIn[tileStart + idx] : s_values[idx];
+			if( idx < tileCount ) s_keys[rank[i]] = ( oddTail && idx == tileCount - 1 ) ? valuesIn[tileStart + idx] : s_values[idx];
 		}
 		__syncthreads();
 		SORT_PROF_MARK( 9 ); // values in sorted order in shared memory
@@ -661,7 +631,7 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 		for( int i = 0; i < ITEMS; i++ )
 		{
 			const uint32_t p = i * BLOCK + threadIdx.x;
-			if( p < tileCount ) valuesOut[LATEV ? s_globalBase[s_digit[p]] + p : dst[i]] = s_keys[p];
+			if( p < tileCount ) valuesOut[dst[i]] = s_keys[p];
 		}
 		SORT_PROF_MARK( 10 ); // value stores issued
 	}
@@ -1007,15 +977,15 @@ int launchClusterRP( hako_ctx* ctx, cudaStream_t s, int cl, bool d32, uint32_t t
 //   against 3.45 ms for variant 1 (profiles/r2w_sort_tiles.log); the cluster pass 4.49-4.78 ms (profiles/r2v_sort_cluster.log).
 //   Not staging the value tile (L2 prefetch at entry, late loads into registers, a u16 digit per sorted position instead of the
 //   destinations in registers) buys a 4th / 5th CTA per SM and nothing else: 256 x 15 x 4 3.55 ms, 256 x 12 x 5 3.88 ms
-//   (profiles/r3b_sort_latev.log).  More tiles in flight only lengthen every look-back walk: the pass is bound by how fast inclusive
-//   prefixes propagate from tile to tile, not by occupancy.
-int sortVariantTile( int variant ) { return ( variant == 1 || variant == 4 || variant == 5 ) ? 256 * 15 : ( variant == 6 ? 256 * 12 : ( variant == 0 ? SORT_TILE : 4096 ) ); }
-template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0, bool LATEV = false>
+//   (profiles/r3b_sort_latev.log; the code is in the history, not in the tree).  More tiles in flight only lengthen every look-back
+//   walk: the pass is bound by how fast inclusive prefixes propagate from tile to tile, not by occupancy.
+int sortVariantTile( int variant ) { return ( variant == 1 || variant == 4 ) ? 256 * 15 : ( variant == 0 ? SORT_TILE : 4096 ); }
+template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0>
 int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t* kin, const uint64_t* vin, uint64_t* kout, uint64_t* vout, uint64_t n, int shift, uint32_t mask,
 				   const unsigned long long* digitBase, unsigned long long* lookback, uint32_t* ticket )
 {
-	auto k = onesweepBulkKernel<RBITS, PAIRS, BLOCK, ITEMS, MIN_CTAS, D32, LB, RANK, LATEV>;
-	constexpr size_t bytes = SortV2Smem<RBITS, BLOCK, ITEMS, LATEV>::BYTES;
+	auto k = onesweepBulkKernel<RBITS, PAIRS, BLOCK, ITEMS, MIN_CTAS, D32, LB, RANK>;
+	constexpr size_t bytes = SortV2Smem<RBITS, BLOCK, ITEMS>::BYTES;
 	static bool configured[16] = {}; // per device and instantiation
 	int dev = ctx->device & 15;
 	if( !configured[dev] )
@@ -1047,9 +1017,6 @@ int launchBulkRP( hako_ctx* ctx, cudaStream_t s, int variant, uint32_t tiles, co
 		HAKO_BULK1( false, 0 );
 #undef HAKO_BULK1
 	}
-	// 5 / 6: values not staged (L2 prefetch + late loads), 4 / 5 CTAs per SM; 32-bit descriptors only (n < 2^30, else variant 1)
-	if( variant == 5 ) return launchBulkOne<RBITS, PAIRS, 256, 15, 4, true, HAKO_SORT_LB, 3, true>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
-	if( variant == 6 ) return launchBulkOne<RBITS, PAIRS, 256, 12, 5, true, HAKO_SORT_LB, 3, true>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
 	if( variant == 3 ) return launchBulkOne<RBITS, PAIRS, 256, 16, 2>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
 	return launchBulkOne<RBITS, PAIRS, 512, 8, 2>( ctx, s, tiles, kin, vin, kout, vout, n, shift, mask, digitBase, lookback, ticket );
 }
@@ -1098,8 +1065,7 @@ int sortPairsDevice( hako_ctx* ctx, cudaStream_t s, uint64_t* keys, uint64_t* va
 	const bool aligned16 = ( ( (uintptr_t)keys | (uintptr_t)keysTmp | (uintptr_t)values | (uintptr_t)valuesTmp ) & 15u ) == 0;
 	const char* varEnv = getenv( "HAKO_SORT_VARIANT" ); // 0: first-generation kernel (plain loads, 4 096-pair tiles)
 	int variant = varEnv ? atoi( varEnv ) : 1; // B200, 72.7 M pairs x 36 bits: variant 0 4.46 ms, 1 4.18, 2 4.62, 3 5.23 (profiles/r2e_sort_variants.log)
-	if( variant < 0 || variant > 6 || !aligned16 ) variant = 0;
-	if( ( variant == 5 || variant == 6 ) && n >= ( 1ull << 30 ) ) variant = 1;
+	if( variant < 0 || variant > 4 || !aligned16 ) variant = 0;
 	const uint64_t tileSize = (uint64_t)sortVariantTile( variant );
 	const uint64_t tiles = ( n + tileSize - 1 ) / tileSize;
 	if( tiles >= 0x7FFFFFFFull )
