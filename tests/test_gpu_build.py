@@ -164,6 +164,34 @@ def test_sort_extreme(hk, ctx):
         np.testing.assert_array_equal(v, vals[order])
 
 
+def test_sort_variants_agree():
+    """every selectable form of the onesweep pass (bulk-copy tiles with 32- or 64-bit look-back descriptors, ballot or match.any ranking,
+    the 512 x 8 and 256 x 16 tilings, the thread-block-cluster pass with 2 / 8 tiles per cluster, the first-generation kernel) is the same
+    stable sort: pairs, keys only, ragged and odd lengths, 9-bit (27- and 36-bit windows) and 8-bit digits (16-bit window)"""
+    import subprocess, sys, os
+    code = ("import sys, hashlib, numpy as np; sys.path.insert(0, %r)\n"
+            "import massivevoxelraytracing_b200 as hk\nctx = hk.Context(0)\n"
+            "for n, bits in ((0, 27), (1, 27), (3839, 27), (3841, 36), (100001, 27), (1 << 20, 36), (250007, 16)):\n"
+            "    rng = np.random.default_rng(n + bits)\n"
+            "    keys = rng.integers(0, 1 << bits, n, dtype=np.uint64) | (rng.integers(0, 1 << 20, n, dtype=np.uint64) << np.uint64(40))\n"
+            "    if n > 100: keys[: n // 2] &= np.uint64(0xFF)\n"
+            "    vals = np.arange(n, dtype=np.uint64)\n"
+            "    k, v = ctx.sort_pairs(keys, vals, 0, bits)\n"
+            "    k2 = ctx.sort_pairs(keys, None, 0, bits)\n"
+            "    order = np.argsort(keys & np.uint64((1 << bits) - 1), kind='stable')\n"
+            "    ok = bool(np.array_equal(k, keys[order]) and np.array_equal(v, vals[order]) and np.array_equal(k2, keys[order]))\n"
+            "    print(n, bits, ok, hashlib.sha1(k.tobytes() + v.tobytes()).hexdigest())\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
+    outs = []
+    for extra in ({}, {"HAKO_SORT_D32": "0"}, {"HAKO_SORT_RANK": "0"}, {"HAKO_SORT_VARIANT": "2"}, {"HAKO_SORT_VARIANT": "3"}, {"HAKO_SORT_VARIANT": "0"},
+                  {"HAKO_SORT_VARIANT": "4", "HAKO_SORT_CLUSTER": "2"}, {"HAKO_SORT_VARIANT": "4", "HAKO_SORT_CLUSTER": "8"},
+                  {"HAKO_SORT_VARIANT": "4", "HAKO_SORT_CLUSTER": "4", "HAKO_SORT_D32": "0"}):
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=dict(os.environ, **extra))
+        assert r.returncode == 0, (extra, r.stderr[-2000:])
+        outs.append(r.stdout)
+        assert all(line.split()[2] == "True" for line in r.stdout.splitlines()), (extra, r.stdout)
+    assert all(o == outs[0] for o in outs) and len(outs[0].splitlines()) == 7
+
+
 # ---------------------------------------------------------------- unique
 @pytest.mark.parametrize("grid", [16, 64, 256])
 def test_unique_merge_matches_oracle(hk, ctx, oracle, bunny, grid):
