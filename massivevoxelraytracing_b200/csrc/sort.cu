@@ -348,7 +348,8 @@ struct SortV2Smem
 // RANK bit 1: the lanes that share a digit come from one ballot per digit bit instead of MATCH.ANY; bit 0: the class leader bumps its
 // 16-bit counter with a plain load / add / store instead of a packed shared-memory atomic.  72.7 M pairs x 36 bits on the B200
 // (profiles/r2s..r2u_sort_knobs.log, tools/sort_phase_probe.py): 64-bit + match + atomic 4.00 ms, D32 3.82, D32 + ballots + plain 3.43;
-// LB = 4 with D32 3.53-3.78.  A tile's life is then ~35 000 cycles: ranking 9 600, look-back 11 400 (8.6 round trips, 2 polls of
+// LB = 4 with D32 3.53-3.78; MATCH.ANY for all 15 rows up front (so that their latencies overlap), then the counter chain: 4.00 -- the
+// instruction itself is the cost (profiles/r3e_rank1.log).  A tile's life is then ~35 000 cycles: ranking 9 600, look-back 11 400 (8.6 round trips, 2 polls of
 // descriptors not yet published), the data movement itself (tile in, two shared-memory scatters, two write-outs) the remaining 40 %.
 template <int RBITS, bool PAIRS, int BLOCK, int ITEMS, int MIN_CTAS, bool D32 = false, int LB = HAKO_SORT_LB, int RANK = 0>
 __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const uint64_t* __restrict__ keysIn, const uint64_t* __restrict__ valuesIn,
