@@ -654,6 +654,7 @@ def run_pt_leg(hk, hdist, nd, ctx, octree, dev, rank, world, args, multi):
         frame(iters)
         sync_all()
         pt.ray_count(reset=True)
+        pt.trace_steps(reset=True)
         l0 = ctx.launch_count
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -661,12 +662,14 @@ def run_pt_leg(hk, hdist, nd, ctx, octree, dev, rank, world, args, multi):
             frame(iters)
         e1.record(stream)
         sync_all()
+        timed.steps = mx(pt.trace_steps() / reps, dist.ReduceOp.SUM if world > 1 else None)   # node visits of the secondary rays, all ranks
         return mx(e0.elapsed_time(e1) / reps), mx(pt.ray_count() / reps, dist.ReduceOp.SUM if world > 1 else None), (ctx.launch_count - l0) // reps
 
     # weak scaling: PT_STEPS steps per rank, whatever N
     iters = hdist.spp_shard(PT_STEPS * world, rank, world)
     reps = 3
     ms, rays, launches = timed(iters, reps)
+    trace_steps = timed.steps
     spp = 16 * PT_STEPS * world
     a = pt.accumulators() if rank == 0 else None
     # e2e: the PathTracer calls a voxPTGPU frame makes (clear, steps, reduce, toImageAsync = resolve + D2H of the RGBA8 frame)
@@ -691,6 +694,10 @@ def run_pt_leg(hk, hdist, nd, ctx, octree, dev, rank, world, args, multi):
                            % (PT_GRID, W, H, PT_DEPTH, spp, PT_STEPS),
                "ms_per_frame": ms, "ms_per_spp_per_gpu": ms / (16 * PT_STEPS), "mpaths_per_s": paths / (ms * 1e-3) / 1e6,
                "mrays_per_s": rays / (ms * 1e-3) / 1e6, "rays_per_path": rays / paths,
+               # how long the secondary rays are: node visits per ray of the trace waves (hako_pt_trace_steps) -- the primary rays of the headline
+               # need ~12; visits/s of the whole frame time is a LOWER bound of the trace kernel's rate (primary wave and shading are inside it)
+               "secondary_rays": {"per_path": (rays - paths) / paths, "node_visits_per_ray": trace_steps / max(rays - paths, 1.0),
+                                  "gvisits_per_s_over_frame_time": trace_steps / (ms * 1e-3) / 1e9},
                "e2e_ms_per_frame": e2e_ms, "e2e_mpaths_per_s": paths / (e2e_ms * 1e-3) / 1e6, "d2h_bytes_per_frame": W * H * 4,
                "launches_per_frame_per_gpu": int(launches), "spp_count_ok": ok, "mean_radiance": float(a[..., :3].mean() / spp),
                "collective": "ncclReduce(sum) of %d MB float4 accumulators" % (W * H * 16 // 1000000) if world > 1 else "none (1 GPU)",

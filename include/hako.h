@@ -237,6 +237,9 @@ int hako_pt_read_rgba8_async( hako_pt* pt, hako_stream stream, uint8_t* rgba );	
 int hako_pt_read_accum( hako_pt* pt, hako_stream stream, float* rgbw );						/* float4 accumulators (HOST) */
 int hako_pt_accum_device( hako_pt* pt, void** accum_d, uint64_t* bytes );					/* for ncclReduce by the host layer */
 int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, int reset ); /* traversal calls since reset */
+/* node visits of the secondary rays (trace waves of the wavefront path tracer) since reset: with hako_pt_ray_count the measure of how long
+   those rays are; 0 in the persistent-kernel modes (HAKO_PT_WAVEFRONT=0/1) */
+int hako_pt_trace_steps( hako_pt* pt, hako_stream stream, uint64_t* steps, int reset );
 /* pieces of the sampler / environment exposed for parity tests */
 int hako_pt_pmj_table( hako_pt* pt, hako_stream stream, float* samples /* [128][4096][2], HOST */ );
 int hako_pt_hdri_sats( hako_pt* pt, hako_stream stream, uint32_t* sats /* [7][w*h], HOST */ );

@@ -102,6 +102,7 @@ SIGNATURES = {
     "hako_pt_read_accum": (i32, [vp, vp, vp]),
     "hako_pt_accum_device": (i32, [vp, pp, pu64]),
     "hako_pt_ray_count": (i32, [vp, vp, pu64, i32]),
+    "hako_pt_trace_steps": (i32, [vp, vp, pu64, i32]),
     "hako_pt_pmj_table": (i32, [vp, vp, vp]),
     "hako_pt_hdri_sats": (i32, [vp, vp, vp]),
     "hako_pt_rgba8_device": (i32, [vp, pp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -30,7 +30,7 @@ using namespace hako;
 #define PT_CHUNK 256	  // paths fetched from the global counter per warp-level atomic
 #define PMJ_LENGTH 4096	  // pmjSampler.hpp:107-111
 #define PMJ_NSEQ 128
-#define PT_COUNTERS 64	  // [0] work, [1] rays traced, [2 + v] live paths at vertex v, [32 + v] ray work counter of wave v
+#define PT_COUNTERS 64	  // [0] work, [1] rays traced, [2 + v] live paths at vertex v, [32 + v] ray work counter of wave v, [63] traversal steps of the trace waves
 #define PT_LANES 4 // concurrent row bands of a wavefront step; each has its own PT_COUNTERS block and wave buffers
 #define PT_MAX_WAVES 28
 
@@ -684,6 +684,7 @@ struct TraceWaveParams
 	const unsigned long long* nVertices; // nVertices[-1] = live paths one vertex earlier = pitch of dirs / results
 	unsigned long long* work; // ray index counter of this wave (zeroed)
 	unsigned long long* rays; // total rays traced
+	unsigned long long* steps; // total traversal steps (node visits) of the rays traced by this kernel
 	int raysPerVertex;
 	int shadowFirst; // ray 0 of every vertex is a shadow ray (any-hit semantics: no voxel-rank accumulation)
 	int refillMin;	 // refill when at least this many lanes of the warp are idle
@@ -802,6 +803,7 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 	bool flying = false, shadow = false;
 	uint32_t addr = 0; // k * stride + slot of the ray in flight
 	uint32_t traced = 0;
+	unsigned long long steps = 0;
 	for( ;; )
 	{
 		const uint32_t idleMask = __ballot_sync( 0xFFFFFFFFu, !flying );
@@ -846,8 +848,9 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 		}
 		if( flying )
 		{
+			int it = 0;
 #pragma unroll 1
-			for( int it = 0; it < tp.burst; it++ )
+			for( ; it < tp.burst; it++ )
 			{
 				const int r = tree.wide ? ( tr.ordinary ? tr.template step<true, true, ( TOPK > 0 )>( tree, shadow, stk, tc ) : tr.template step<false, true, ( TOPK > 0 )>( tree, shadow, stk, tc ) )
 										: ( tr.ordinary ? tr.template step<true, false, ( TOPK > 0 )>( tree, shadow, stk, tc ) : tr.template step<false, false, ( TOPK > 0 )>( tree, shadow, stk, tc ) );
@@ -857,12 +860,16 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 					__stcs( tp.results + addr, make_float4( tr.t, __uint_as_float( tr.skipped ), __int_as_float( tr.nMajor ), 1.0f ) );
 				else
 					__stcs( tp.results + addr, make_float4( 0.0f, 0.0f, 0.0f, 0.0f ) );
+				it++;
 				break;
 			}
+			steps += (uint32_t)it; // one add per burst, not per step
 		}
 	}
 	for( int off = 16; off; off >>= 1 ) traced += __shfl_down_sync( 0xFFFFFFFFu, traced, off );
 	if( lane == 0 && traced ) atomicAdd( tp.rays, (unsigned long long)traced );
+	for( int off = 16; off; off >>= 1 ) steps += __shfl_down_sync( 0xFFFFFFFFu, steps, off );
+	if( lane == 0 && steps ) atomicAdd( tp.steps, steps );
 }
 
 // per-pixel reduction in localSpp order, then `frameBuffer += `, voxKernel.cu:763-774
@@ -1394,7 +1401,7 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 			q.counters = counters;
 			q.nPaths = (uint32_t)( (uint64_t)( b1 - b0 ) * pt->w * PT_SPP );
 			// live counts [2 .. 2 + waves] and the waves' ray counters [32 .. 32 + waves)
-			HAKO_CUDA( cudaMemsetAsync( counters + 2, 0, ( PT_COUNTERS - 2 ) * sizeof( unsigned long long ), ls ) );
+			HAKO_CUDA( cudaMemsetAsync( counters + 2, 0, ( PT_COUNTERS - 3 ) * sizeof( unsigned long long ), ls ) ); // [1] rays and [63] steps keep counting
 			const uint32_t tiles = ( ( (uint32_t)pt->w + 3u ) / 4u ) * ( ( (uint32_t)( b1 - b0 ) + 3u ) / 4u );
 			HAKO_LAUNCH( ctx, primaryWaveKernel, tiles, PT_BLOCK, 0, ls, q, b1 - b0 );
 			for( int v = 0; v <= waves; v++ )
@@ -1420,6 +1427,7 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 				tp.nVertices = wp.nOut;
 				tp.work = counters + 32 + v;
 				tp.rays = counters + 1;
+				tp.steps = counters + PT_COUNTERS - 1;
 				tp.raysPerVertex = wp.rOut;
 				tp.shadowFirst = envOn ? 1 : 0;
 				tp.refillMin = std::max( 1, std::min( 32, pt->waveRefillMin ) );
@@ -1575,6 +1583,22 @@ int hako_pt_ray_count( hako_pt* pt, hako_stream stream, uint64_t* raysTraced, in
 	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
 	*raysTraced = 0;
 	for( int k = 0; k < PT_LANES; k++ ) *raysTraced += v[k];
+	return HAKO_OK;
+}
+
+int hako_pt_trace_steps( hako_pt* pt, hako_stream stream, uint64_t* steps, int reset )
+{
+	PT_ARG( pt && steps, "hako_pt_trace_steps: null argument" );
+	HAKO_CUDA( cudaSetDevice( pt->ctx->device ) );
+	unsigned long long v[PT_LANES] = {};
+	for( int k = 0; k < PT_LANES; k++ )
+	{
+		HAKO_CUDA( cudaMemcpyAsync( &v[k], pt->counters + k * PT_COUNTERS + PT_COUNTERS - 1, sizeof( v[k] ), cudaMemcpyDeviceToHost, (cudaStream_t)stream ) );
+		if( reset ) HAKO_CUDA( cudaMemsetAsync( pt->counters + k * PT_COUNTERS + PT_COUNTERS - 1, 0, sizeof( v[k] ), (cudaStream_t)stream ) );
+	}
+	HAKO_CUDA( cudaStreamSynchronize( (cudaStream_t)stream ) );
+	*steps = 0;
+	for( int k = 0; k < PT_LANES; k++ ) *steps += v[k];
 	return HAKO_OK;
 }
 

@@ -120,6 +120,12 @@ class PathTracer:
         check(self.lib.hako_pt_ray_count(self.h, _stream(stream), C.byref(v), int(reset)))
         return int(v.value)
 
+    def trace_steps(self, stream=None, reset=False):
+        """node visits of the secondary rays traced by the wavefront's trace waves since the last reset"""
+        v = C.c_uint64()
+        check(self.lib.hako_pt_trace_steps(self.h, _stream(stream), C.byref(v), int(reset)))
+        return int(v.value)
+
     def pmj_table(self, stream=None):
         out = np.empty(128 * 4096 * 2, np.float32)
         check(self.lib.hako_pt_pmj_table(self.h, _stream(stream), _ptr(out)))

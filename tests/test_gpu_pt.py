@@ -182,16 +182,22 @@ def test_pt_modes_identical(hk, ctx, pt, scene, monkeypatch, with_env, with_emis
         p2.maxDepth = max_depth
         p2.resizeFrameBufferIfNeeded(None, W, H)
         p2.ray_count(reset=True)
+        p2.trace_steps(reset=True)
         for it in range(2):
             p2.step(None, cam, iteration=it)
         p2.step(None, cam, rows=(5, 31), iteration=2)
-        outs.append((p2.accumulators().copy(), p2.ray_count()))
+        outs.append((p2.accumulators().copy(), p2.ray_count(), p2.trace_steps(), env["HAKO_PT_WAVEFRONT"]))
         p2.m_intersectorOctreeGPU = hk.IntersectorOctreeGPU(ctx)
         p2.cleanUp()
-    for acc, rays in outs[1:]:
+    for acc, rays, _, _ in outs[1:]:
         assert np.array_equal(acc.view(np.uint32), outs[0][0].view(np.uint32))
         assert rays == outs[0][1]
     assert outs[0][1] > W * H * 16 * 2
+    # node visits of the secondary rays (hako_pt_trace_steps): a property of the rays, not of the order they are traced in -- the same
+    # for every wavefront setting; the persistent-kernel modes do not count them
+    wave_steps = {st for _, _, st, mode in outs if mode == "2"}
+    assert len(wave_steps) == 1 and min(wave_steps) > 0
+    assert all(st == 0 for _, _, st, mode in outs if mode != "2")
 
 
 def test_resolve_matches_oracle(hk, ctx, pt, oracle, scene):
