@@ -14,6 +14,8 @@ cam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=W, height=H, focus=6.0, lensR
 ref = None
 variants = [(0, 8, 8, 5)] + [(2, r, b, c) for c in (5, 6, 8) for (r, b) in ((8, 16), (16, 16), (24, 16), (16, 32), (28, 32), (32, 16))]
 if len(sys.argv) > 2: variants = [(0, 8, 8, 5)] + [(2, r, b, c) for c in (5, 6) for (r, b) in ((8, 16), (16, 16), (24, 16), (28, 16), (28, 32), (32, 16), (32, 64))]
+if os.environ.get('PT_SWEEP'):   # "refillMin:burst:ctas,..."
+    variants = [(0, 8, 8, 5)] + [(2,) + tuple(int(x) for x in v.split(':')) for v in os.environ['PT_SWEEP'].split(',')]
 for wf, rmin, burst, ctas in variants:
     os.environ['HAKO_PT_WAVEFRONT'] = str(wf); os.environ['HAKO_PT_REFILL_MIN'] = str(rmin); os.environ['HAKO_PT_BURST'] = str(burst); os.environ['HAKO_PT_TRACE_CTAS'] = str(ctas)
     pt = hk.PathTracer(ctx).setup()
