@@ -506,6 +506,15 @@ __global__ void __launch_bounds__( BLOCK, MIN_CTAS ) onesweepBulkKernel( const u
 		// Decoupled look-back, LB predecessors per round trip and the thread's DPT digits side by side: the loads of a round are
 		// independent, so a chain of AGGREGATE descriptors costs one L2 latency per LB tiles instead of one per tile and digit
 		// (descriptors behind the first INCLUSIVE one are fetched for nothing).  HAKO_SORT_LOOKBACK sweep: profiles/r2o, r2p.
+#ifdef HAKO_SORT_PROFILE
+		// timing experiment only (WRONG output): no look-back at all, a made-up prefix that keeps the write addresses spread like the real ones
+		if( backoffNs == 0xFFFFFFFFu )
+		{
+#pragma unroll
+			for( int j = 0; j < DPT; j++ ) excl[j] = (unsigned long long)tile * ( TILE / RADIX );
+		}
+		else
+#endif
 		if( owner && tile != 0 )
 		{
 			bool done[DPT];
@@ -995,7 +1004,7 @@ int launchBulkOne( hako_ctx* ctx, cudaStream_t s, uint32_t tiles, const uint64_t
 		configured[dev] = true;
 	}
 	static const int backoffEnv = getenv( "HAKO_SORT_BACKOFF" ) ? atoi( getenv( "HAKO_SORT_BACKOFF" ) ) : LB_BACKOFF_NS; // ns a look-back poll sleeps when its predecessor is not ready
-	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, (void*)lookback, ticket, (uint32_t)( backoffEnv > 0 ? backoffEnv : 0 ) );
+	HAKO_LAUNCH( ctx, k, tiles, BLOCK, bytes, s, kin, vin, kout, vout, n, shift, mask, digitBase, (void*)lookback, ticket, (uint32_t)( backoffEnv > 0 ? backoffEnv : ( backoffEnv == -1 ? 0xFFFFFFFFu : 0u ) ) ); // -1: profiling builds only, see the kernel
 	return 0;
 }
 template <int RBITS, bool PAIRS>
