@@ -487,16 +487,12 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 		for( int j = 0; j < 22; j++ ) bounds[j] = ctx->pinned[j];
 	}
 	uint64_t G[MAX_LEVELS + 1]; // G[l] = groups (= nodes before dedupe) at level l
+	for( int l = levels - 1; l >= 0; l-- )
 	{
-		uint64_t above = 0; // boundaries with top/3 > l
-		for( int l = levels - 1; l >= 0; l-- )
-		{
-			// a boundary between i-1 and i exists at level l iff top/3 >= l + 1
-			uint64_t b = 0;
-			for( int j = l + 1; j < 22; j++ ) b += bounds[j];
-			G[l] = 1 + b;
-			(void)above;
-		}
+		// a boundary between i-1 and i exists at level l iff top/3 >= l + 1
+		uint64_t b = 0;
+		for( int j = l + 1; j < 22; j++ ) b += bounds[j];
+		G[l] = 1 + b;
 	}
 	uint64_t pool = 0;
 	for( int l = 0; l < levels; l++ ) pool += ( dag && l == 0 ) ? ( G[0] < 255 ? G[0] : 255 ) : G[l];

@@ -24,7 +24,6 @@ constexpr int SORT_BLOCK = 256;
 constexpr int SORT_WARPS = SORT_BLOCK / 32;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_BLOCK * SORT_ITEMS; // 4096 pairs
-constexpr int MAX_RADIX = 512;
 constexpr int MAX_PASSES = 8;
 
 #ifndef HAKO_SORT_PREFETCH

@@ -198,25 +198,6 @@ __device__ __forceinline__ uint32_t packRGB255fast( V3 c )
 {
 	return f2u8_fast( c.x * 255.0f + 0.5f ) | ( f2u8_fast( c.y * 255.0f + 0.5f ) << 8 ) | ( f2u8_fast( c.z * 255.0f + 0.5f ) << 16 ) | 0xFF000000u;
 }
-// Morton code from a 256-entry table of 8 bits spread to every third position (24 bits): three look-ups per axis instead of the
-// five 64-bit shift / or / and rounds of splitBy3 (== encode2mortonCode_LUT, morton.hpp; all variants agree, unittest.cpp:183-216)
-__device__ __forceinline__ uint32_t spread8( uint32_t b )
-{
-	uint32_t x = b & 0xFFu;
-	x = ( x | x << 8 ) & 0x00F00Fu;
-	x = ( x | x << 4 ) & 0x0C30C3u;
-	x = ( x | x << 2 ) & 0x249249u;
-	return x;
-}
-__device__ __forceinline__ uint64_t mortonAxisLut( const uint32_t* lut, uint32_t v )
-{
-	return (uint64_t)lut[v & 0xFFu] | ( (uint64_t)lut[( v >> 8 ) & 0xFFu] << 24 ) | ( (uint64_t)lut[( v >> 16 ) & 0x1Fu] << 48 );
-}
-__device__ __forceinline__ uint64_t mortonEncodeLut( const uint32_t* lut, uint32_t x, uint32_t y, uint32_t z )
-{
-	return mortonAxisLut( lut, x ) | ( mortonAxisLut( lut, y ) << 1 ) | ( mortonAxisLut( lut, z ) << 2 );
-}
-
 __device__ __forceinline__ uint32_t packRGB255( V3 c )
 {
 	// (uint8_t)( v * 255.0f + 0.5f ) with x86 cast semantics; alpha = 255 (voxRT.cpp:230-234, voxKernel.cu:151-158)
