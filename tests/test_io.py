@@ -101,6 +101,20 @@ def test_hdr_matches_stbi_loadf(hk, tmp_path):
     assert got.shape == ref.shape and np.array_equal(got.view(np.uint32), ref.view(np.uint32))
 
 
+def test_hdr_matches_stbi_golden(hk, tmp_path):
+    """the same comparison without the reference checkout: tests/golden/hdr_golden.npz holds small synthetic .hdr files and what the
+    reference's decoder (stbi_loadf( .., 4 ), libs/prlib/src/prp.cpp:353-366) returned for them (tests/golden/make_hdr_golden.py)"""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "hdr_golden.npz"))
+    cases = sorted(k for k in g.files if k.startswith("file"))
+    assert len(cases) == 5
+    for k in cases:
+        p = tmp_path / (k + ".hdr")
+        p.write_bytes(g[k].tobytes())
+        ref = g["image" + k[4:]]
+        got = hk.io.load_hdr(p)
+        assert got.shape == ref.shape and np.array_equal(got.view(np.uint32), ref.view(np.uint32)), k
+
+
 # ---------------------------------------------------------------- PNG
 def _read_png(path):
     b = open(path, "rb").read()
@@ -242,7 +256,9 @@ def test_bounds_device(hk, bunny):
 @pytest.mark.gpu
 def test_frame_sequence_matches_direct_calls(hk, bunny, tmp_path):
     """RTCamp frame loop: animated resolution, PNG per frame written by the pool threads == the same frames through the plain
-    PathTracer calls"""
+    PathTracer calls.  This compares the library with itself on purpose: it checks the ORCHESTRATION (build of frame f + 1 overlapped with
+    the steps of frame f, resolve, asynchronous download, PNG writer threads); what a step computes is pinned elsewhere
+    (tests/test_gpu_pt.py against the oracle, tests/test_gpu_refgpu.py against the reference's own kernels)"""
     from scenes import procedural_hdri
     tris, col, emi = bunny
     ctx = hk.Context(0)
