@@ -118,6 +118,9 @@ int hako_ctx_synchronize( hako_ctx* ctx, hako_stream stream );
 int hako_ctx_build_stats( const hako_ctx* ctx, hako_build_stats* out );
 /* number of kernel launches issued through this context since creation (bench.py's gpu_launches claim) */
 uint64_t hako_ctx_launch_count( const hako_ctx* ctx );
+/* map `bytes` of device memory into the context's stream-ordered pool now (kept there), so that the first build does not grow the pool
+ * on the caller's critical path; optional -- the pool grows on demand otherwise */
+int hako_ctx_reserve( hako_ctx* ctx, hako_stream stream, uint64_t bytes );
 /* measurement: the L2 read roof of the device (traversal is served by L2 while the node array fits it).  Sweeps a
  * buffer of setBytes (0 = a quarter of the L2) `reps` times; *l2Bytes = cudaDevAttrL2CacheSize, *readGBs = best of three. */
 int hako_ctx_l2_probe( hako_ctx* ctx, hako_stream stream, uint64_t setBytes, int reps, uint64_t* l2Bytes, float* readGBs );

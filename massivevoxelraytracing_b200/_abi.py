@@ -62,6 +62,7 @@ SIGNATURES = {
     "hako_ctx_build_stats": (i32, [vp, C.POINTER(BuildStats)]),
     "hako_ctx_launch_count": (u64, [vp]),
     "hako_ctx_l2_probe": (i32, [vp, vp, u64, i32, pu64, C.POINTER(C.c_float)]),
+    "hako_ctx_reserve": (i32, [vp, vp, u64]),
     "hako_octree_build": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, pp]),
     "hako_octree_build_device": (i32, [vp, vp, vp, vp, vp, u32, vp, f32, i32, pp]),
     "hako_octree_build_from_morton": (i32, [vp, vp, vp, vp, u64, vp, f32, i32, i32, pp]),

@@ -172,6 +172,27 @@ int hako_ctx_build_stats( const hako_ctx* cc, hako_build_stats* out )
 
 uint64_t hako_ctx_launch_count( const hako_ctx* c ) { return c ? c->launches.load() : 0; }
 
+// Grow the context's memory pool to `bytes` now (one allocation, released back INTO the pool: its release threshold keeps the memory
+// mapped), so that the first build of an application does not pay for the mapping on its critical path.
+int hako_ctx_reserve( hako_ctx* c, hako_stream stream, uint64_t bytes )
+{
+	if( !c ) return HAKO_E_INVALID;
+	if( bytes == 0 ) return HAKO_OK;
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( c->device ) );
+	void* p = nullptr;
+	cudaError_t e = cudaMallocFromPoolAsync( &p, (size_t)bytes, c->pool, s );
+	if( e != cudaSuccess )
+	{
+		cudaGetLastError();
+		hako::setError( "hako_ctx_reserve: %llu bytes: %s", (unsigned long long)bytes, cudaGetErrorString( e ) );
+		return HAKO_E_CUDA;
+	}
+	HAKO_CUDA( cudaFreeAsync( p, s ) );
+	HAKO_CUDA( cudaStreamSynchronize( s ) );
+	return HAKO_OK;
+}
+
 // The L2 roof of this device, measured ("B200 L2 peak is not in MEASURED_PEAKS -- measure once with a resident-set
 // microbenchmark and record"): read bandwidth over a buffer of setBytes (0: a quarter of the L2) that is swept `reps` times.
 int hako_ctx_l2_probe( hako_ctx* c, hako_stream stream, uint64_t setBytes, int reps, uint64_t* l2Bytes, float* readGBs )

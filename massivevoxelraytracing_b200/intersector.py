@@ -64,6 +64,10 @@ class Context:
     def launch_count(self):
         return int(self.lib.hako_ctx_launch_count(self.h))
 
+    def reserve(self, nbytes, stream=None):
+        """grow the context's memory pool to nbytes now instead of during the first build"""
+        check(self.lib.hako_ctx_reserve(self.h, _stream(stream), int(nbytes)))
+
     def l2_probe(self, set_bytes=0, reps=20, stream=None):
         """(L2 size in bytes, measured L2 read bandwidth in GB/s over a resident set) -- the roof the traversal is held against"""
         l2, gbs = C.c_uint64(), C.c_float()

@@ -461,3 +461,15 @@ def test_build_rejects_bad_grid(hk, ctx, bunny):
     tris, col, emi = bunny
     with pytest.raises(hk.HakoError):
         hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, (0, 0, 0), 0.1, 100)      # not a power of two (reference abort()s)
+
+
+def test_context_reserve(hk):
+    """hako_ctx_reserve maps memory into the context's pool up front; an impossible size fails with an error and leaves the context usable"""
+    c = hk.Context(0)
+    c.reserve(0)
+    c.reserve(64 << 20)
+    with pytest.raises(hk.HakoError):
+        c.reserve(1 << 50)
+    keys = np.arange(1000, dtype=np.uint64)[::-1].copy()
+    np.testing.assert_array_equal(c.sort_pairs(keys), np.arange(1000, dtype=np.uint64))
+    c.close()
