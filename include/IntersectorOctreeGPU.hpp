@@ -43,6 +43,7 @@ public:
 	Context& operator=( const Context& ) = delete;
 	hako_ctx* get() const { return m_ctx; }
 	void synchronize( hako_stream stream = nullptr ) { check( hako_ctx_synchronize( m_ctx, stream ) ); }
+	void reserve( uint64_t bytes, hako_stream stream = nullptr ) { check( hako_ctx_reserve( m_ctx, stream, bytes ) ); } // size the memory pool at start-up
 	hako_build_stats buildStats() const
 	{
 		hako_build_stats s;
