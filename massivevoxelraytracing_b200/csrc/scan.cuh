@@ -61,15 +61,19 @@ __device__ __forceinline__ uint64_t scanTilePrefixWarp( const ScanState& st, uin
 	{
 		const int64_t idx = base - lane;
 		unsigned long long d = SCAN_FLAG_INC; // virtual tiles before 0: inclusive prefix 0
-		if( idx >= 0 )
+		uint32_t incMask, firstInc;
+		// poll the window until every predecessor UP TO the nearest inclusive one has published something; tiles behind that one are
+		// not needed, so a straggler among them must not hold this tile (and through it its successors) up
+		for( ;; )
 		{
-			do
-			{
-				d = ldVolatile( &st.desc[idx] );
-			} while( ( d >> 62 ) == 0 );
+			if( idx >= 0 ) d = ldVolatile( &st.desc[idx] );
+			const uint32_t status = (uint32_t)( d >> 62 );
+			incMask = __ballot_sync( 0xFFFFFFFFu, status == 2u );
+			const uint32_t pendMask = __ballot_sync( 0xFFFFFFFFu, status == 0u );
+			firstInc = incMask ? ( __ffs( incMask ) - 1 ) : 32u;
+			const uint32_t need = firstInc >= 31u ? 0xFFFFFFFFu : ( ( 2u << firstInc ) - 1u ); // lanes 0 .. firstInc
+			if( ( pendMask & need ) == 0u ) break;
 		}
-		const uint32_t incMask = __ballot_sync( 0xFFFFFFFFu, ( d >> 62 ) == 2 );
-		const uint32_t firstInc = incMask ? ( __ffs( incMask ) - 1 ) : 32u;
 		uint64_t v = ( lane <= firstInc ) ? ( d & SCAN_VALUE_MASK ) : 0ull;
 #pragma unroll
 		for( int o = 16; o > 0; o >>= 1 ) v += __shfl_xor_sync( 0xFFFFFFFFu, v, o );
