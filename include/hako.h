@@ -191,6 +191,17 @@ int hako_sort_pairs( hako_ctx* ctx, hako_stream stream, uint64_t* keys, uint64_t
 /* `unique` kernel, voxKernel.cu:170-243 == mergeVoxels, voxRT.cpp:14-51: sorted (key, attrib) -> first of each run,
  * integer-mean attributes.  HOST in/out (in place), *U receives the count. */
 int hako_unique_merge( hako_ctx* ctx, hako_stream stream, uint64_t* keys, hako_voxel_attrib* attrs, uint64_t n, uint64_t* U, uint32_t* hasEmission );
+/* The same merge for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.  Calls no cudaMalloc / cudaFree / pool allocation and does
+ * not wait for the stream: it enqueues two memsets and the merge kernel.  DEVICE pointers throughout: sorted keys_d / attrs_d (n entries,
+ * 16-byte aligned) -> keysOut_d / attrsOut_d (room for n entries) and counts_d[2] = { number of runs U, hasEmission }, all written
+ * stream-ordered.  The kernel's scratch (scan descriptors) is a static device array of 64.3 KB that every GPU loading the library holds
+ * until exit, which bounds n: more than HAKO_UNIQUE_NOALLOC_MAX_ITEMS entries -> HAKO_E_LIMIT.  All calls on a device share that array:
+ * calls that overlap on the GPU (different streams without a dependency) race; calls on one stream, or ordered by events, do not.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress); make it once outside any graph capture. */
+#define HAKO_UNIQUE_NOALLOC_MAX_ITEMS ( 1ull << 24 )
+int hako_unique_merge_noalloc( hako_ctx* ctx, hako_stream stream, const uint64_t* keys_d, const hako_voxel_attrib* attrs_d, uint64_t n,
+							   uint64_t* keysOut_d, hako_voxel_attrib* attrsOut_d, uint64_t* counts_d );
 
 /* ---- intersect: IntersectorOctreeGPU::intersect (device, :243-251) / IntersectorOctree::intersect (:248-257) ----
  * ro/rd: 3 floats per ray (rd un-normalised).  Caller presets t = FLT_MAX; a miss leaves t / nMajor / vIndex

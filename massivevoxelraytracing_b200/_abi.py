@@ -84,6 +84,7 @@ SIGNATURES = {
     "hako_sort_pairs_device": (i32, [vp, vp, vp, vp, u64, i32, i32]),
     "hako_sort_pairs": (i32, [vp, vp, vp, vp, u64, i32, i32]),
     "hako_unique_merge": (i32, [vp, vp, vp, vp, u64, pu64, pu32]),
+    "hako_unique_merge_noalloc": (i32, [vp, vp, vp, vp, u64, vp, vp, vp]),
     "hako_intersect_batch": (i32, [vp, vp, vp, vp, u64, i32, vp, vp, vp]),
     "hako_intersect_batch_device": (i32, [vp, vp, vp, vp, u64, i32, vp, vp, vp]),
     "hako_render_primary": (i32, [vp, vp, C.POINTER(Camera), i32, i32, i32, i32, i32, vp, vp, vp, vp]),

@@ -7,6 +7,7 @@
 // (StreamCompaction.hpp:121-138,186-196).  Here: one fused kernel, out of place -- head flags, block scan, decoupled
 // look-back for the tile prefix, and the head thread of each run walks its run and writes the merged voxel.
 #include <algorithm>
+#include <mutex>
 
 #include "internal.cuh"
 #include "scan.cuh"
@@ -244,3 +245,71 @@ int uniqueMergeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, cons
 	return r;
 }
 } // namespace hako
+
+// ---- hako_unique_merge_noalloc: the merge for callers that may not allocate (CUDA graph capture, serving loops) --------------------
+// No counterpart in the reference.  Same kernel (uniqueMergeKernel) as every other merge
+// of the library; the only scratch it needs -- the descriptors and the ticket of its decoupled look-back scan -- lives in a file-scope
+// device array instead of the context's memory pool.  Every GPU that loads the library holds these 64.3 KB until the process exits.
+// ONE array per device: all calls share it, it keeps the last call's contents (cleared here, stream-ordered, before every launch), and
+// two calls that overlap on the GPU (different streams, no dependency between them) race on it.
+namespace
+{
+constexpr uint64_t UQ_NOALLOC_MAX_TILES = ( HAKO_UNIQUE_NOALLOC_MAX_ITEMS + hako::UQ_TILE - 1 ) / hako::UQ_TILE;
+constexpr uint64_t UQ_NOALLOC_BYTES = ( ( UQ_NOALLOC_MAX_TILES + 2 ) * 8 + 255 ) & ~255ull; // scanStateBytes( max tiles ), rounded up
+static __device__ __align__( 256 ) unsigned char g_uniqueNoAllocScratch[UQ_NOALLOC_BYTES];
+
+// In host code the array's name is a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+int uniqueNoAllocScratch( int device, void** out )
+{
+	static void* addr[64] = {};
+	static std::mutex lock;
+	if( device < 0 || device >= 64 )
+	{
+		hako::setError( "hako_unique_merge_noalloc: device index %d out of range", device );
+		return HAKO_E_INVALID;
+	}
+	std::lock_guard<std::mutex> g( lock );
+	if( !addr[device] )
+	{
+		void* p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress( &p, g_uniqueNoAllocScratch );
+		if( e != cudaSuccess ) return hako::cudaFail( e, "cudaGetSymbolAddress( g_uniqueNoAllocScratch )", __FILE__, __LINE__ );
+		addr[device] = p;
+	}
+	*out = addr[device];
+	return HAKO_OK;
+}
+} // namespace
+
+extern "C" int hako_unique_merge_noalloc( hako_ctx* ctx, hako_stream stream, const uint64_t* keys_d, const hako_voxel_attrib* attrs_d, uint64_t n,
+										  uint64_t* keysOut_d, hako_voxel_attrib* attrsOut_d, uint64_t* counts_d )
+{
+	if( !ctx || !counts_d || ( n && ( !keys_d || !attrs_d || !keysOut_d || !attrsOut_d ) ) )
+	{
+		hako::setError( "hako_unique_merge_noalloc: null argument" );
+		return HAKO_E_INVALID;
+	}
+	if( n > HAKO_UNIQUE_NOALLOC_MAX_ITEMS )
+	{
+		hako::setError( "hako_unique_merge_noalloc: %llu items exceed the static scratch (HAKO_UNIQUE_NOALLOC_MAX_ITEMS = %llu); use hako_sort_unique_device",
+						(unsigned long long)n, (unsigned long long)HAKO_UNIQUE_NOALLOC_MAX_ITEMS );
+		return HAKO_E_LIMIT;
+	}
+	if( ( ( (uintptr_t)keys_d | (uintptr_t)attrs_d ) & 15u ) || ( ( (uintptr_t)keysOut_d | (uintptr_t)attrsOut_d | (uintptr_t)counts_d ) & 7u ) )
+	{
+		hako::setError( "hako_unique_merge_noalloc: keys_d / attrs_d must be 16-byte aligned, the outputs 8-byte aligned" );
+		return HAKO_E_INVALID;
+	}
+	cudaStream_t s = (cudaStream_t)stream;
+	HAKO_CUDA( cudaSetDevice( ctx->device ) );
+	void* scratch = nullptr;
+	HAKO_TRY( uniqueNoAllocScratch( ctx->device, &scratch ) );
+	HAKO_CUDA( cudaMemsetAsync( counts_d, 0, 16, s ) ); // [0] = U, [1] = hasEmission
+	if( n == 0 ) return HAKO_OK;
+	const uint64_t tiles = ( n + hako::UQ_TILE - 1 ) / hako::UQ_TILE;
+	HAKO_CUDA( cudaMemsetAsync( scratch, 0, hako::scanStateBytes( tiles ), s ) ); // the array keeps the last call's descriptors and ticket
+	HAKO_LAUNCH( ctx, hako::uniqueMergeKernel, (uint32_t)tiles, hako::UQ_BLOCK, 0, s, keys_d, (const uint64_t*)attrs_d, n, keysOut_d, (uint64_t*)attrsOut_d,
+				 hako::makeScanState( scratch, tiles ), (unsigned long long*)counts_d );
+	return HAKO_OK;
+}
