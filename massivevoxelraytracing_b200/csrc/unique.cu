@@ -216,10 +216,19 @@ int uniqueMergeLaunch( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, cons
 	const uint64_t tiles = ( n + UQ_TILE - 1 ) / UQ_TILE;
 	void* mem = nullptr;
 	HAKO_CUDA( cudaMallocFromPoolAsync( &mem, scanStateBytes( tiles ), ctx->pool, s ) );
-	HAKO_CUDA( cudaMemsetAsync( mem, 0, scanStateBytes( tiles ), s ) );
-	HAKO_LAUNCH( ctx, uniqueMergeKernel, (uint32_t)tiles, UQ_BLOCK, 0, s, keys, values, n, keysOut, (uint64_t*)attrsOut, makeScanState( mem, tiles ), counters_d );
-	cudaFreeAsync( mem, s );
-	return 0;
+	int r = 0;
+	do
+	{
+		const cudaError_t e = cudaMemsetAsync( mem, 0, scanStateBytes( tiles ), s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "memset scan state", __FILE__, __LINE__ );
+			break;
+		}
+		HAKO_LAUNCH_R( ctx, r, uniqueMergeKernel, (uint32_t)tiles, UQ_BLOCK, 0, s, keys, values, n, keysOut, (uint64_t*)attrsOut, makeScanState( mem, tiles ), counters_d );
+	} while( 0 );
+	cudaFreeAsync( mem, s ); // also when the launch failed
+	return r;
 }
 
 int uniqueMergeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* keys, const uint64_t* values, uint64_t n,

@@ -262,10 +262,19 @@ int scanU32( hako_ctx* ctx, cudaStream_t s, const uint32_t* in, uint32_t* out, u
 	const uint64_t tiles = ( n + 256 * SCAN_ITEMS - 1 ) / ( 256 * SCAN_ITEMS );
 	void* mem = nullptr;
 	HAKO_CUDA( cudaMallocFromPoolAsync( &mem, scanStateBytes( tiles ), ctx->pool, s ) );
-	HAKO_CUDA( cudaMemsetAsync( mem, 0, scanStateBytes( tiles ), s ) );
-	HAKO_LAUNCH( ctx, scanU32Kernel, (uint32_t)tiles, 256, 0, s, in, out, n, makeScanState( mem, tiles ), totalOut_d );
-	cudaFreeAsync( mem, s );
-	return 0;
+	int r = 0;
+	do
+	{
+		const cudaError_t e = cudaMemsetAsync( mem, 0, scanStateBytes( tiles ), s );
+		if( e != cudaSuccess )
+		{
+			r = cudaFail( e, "memset scan state", __FILE__, __LINE__ );
+			break;
+		}
+		HAKO_LAUNCH_R( ctx, r, scanU32Kernel, (uint32_t)tiles, 256, 0, s, in, out, n, makeScanState( mem, tiles ), totalOut_d );
+	} while( 0 );
+	cudaFreeAsync( mem, s ); // also when the launch failed
+	return r;
 }
 
 // ---- 3./5. per-column enumeration ----
