@@ -122,6 +122,28 @@ def test_voxelize_out_of_range_colours(hk, ctx, oracle):
     _assert_same_voxels(gk, ga, keys, c, e)
 
 
+def test_voxelize_zero_emission_triangles(hk, ctx, oracle):
+    """the shading pass skips the emission interpolation of a triangle whose nine emission values are all +-0; the bytes must still be
+    the reference's for degenerate triangles (NaN / infinite barycentrics), negative zeros, and emissive triangles in the same warp"""
+    rng = np.random.default_rng(6)
+    T = 96
+    tris = rng.random((T, 3, 3)).astype(np.float32)
+    tris[::7, 1] = tris[::7, 0]                        # two equal vertices: zero area
+    tris[3::11, 1] = tris[3::11, 0]
+    tris[3::11, 2] = tris[3::11, 0]                    # a point
+    tris[5::13, 2] = (tris[5::13, 0] + tris[5::13, 1]) * np.float32(0.5)   # collinear
+    col = rng.random((T, 3, 3)).astype(np.float32)
+    emi = np.zeros((T, 3, 3), np.float32)
+    emi[::3] = rng.random((len(emi[::3]), 3, 3)).astype(np.float32)        # every third triangle emits
+    emi[1::6] = np.float32(-0.0)                       # negative zeros count as zero
+    emi[2::9, 2, 1] = np.float32(1e-30)                # one tiny non-zero value: not the fast path
+    origin = np.zeros(3, np.float32)
+    for grid in (32, 128):
+        keys, c, e = oracle.voxelize(tris, col, emi, origin, 1.0 / grid, grid)
+        gk, ga = ctx.voxelize(tris, col, emi, origin, 1.0 / grid, grid)
+        _assert_same_voxels(gk, ga, keys, c, e)
+
+
 # ---------------------------------------------------------------- sort
 @pytest.mark.parametrize("n", [0, 1, 31, 4096, 4097, 100000, 1 << 20])
 def test_sort_pairs_stable(hk, ctx, n):
