@@ -849,7 +849,7 @@ def run_reference_gpu(hk, ctx, octree, pt_octree, cam0, args):
 
 def run_build_sweep(hk, ctx, scene):
     """BASELINE config[3]: voxelization + Morton radix sort + octree build at 2^10 .. 2^14 on the bench mesh (host-buffer call,
-    best of 2 after a warm-up; per-stage device times from hako_ctx_build_stats).  A grid whose octree exceeds the reference
+    best of 3 after a warm-up; per-stage device times from hako_ctx_build_stats).  A grid whose octree exceeds the reference
     format's 24-bit node index is reported as such (HAKO_E_LIMIT), not skipped silently."""
     from scenes import scene_params
     tris, col, emi, _, _, _ = scene
@@ -859,7 +859,7 @@ def run_build_sweep(hk, ctx, scene):
         row = {"grid": grid}
         try:
             best = None
-            for i in range(3):
+            for i in range(4):
                 t0 = time.perf_counter()
                 g = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, origin, float(dps), grid)
                 wall = (time.perf_counter() - t0) * 1e3
