@@ -25,6 +25,7 @@ struct hako_ctx
 	uint32_t lastVoxTriangles = 0;
 	int lastVoxGrid = 0;
 	double lastVoxPerWarp = 0.0;
+	uint64_t voxFreeBytes = 0; // free device memory as last queried by the voxelizer (cudaMemGetInfo costs 0.1 - 3 ms and more: asked once per mesh, not per build)
 	cudaEvent_t ev[8] = {};
 	// pinned staging word(s) for the few device->host counter reads a build needs
 	uint64_t* pinned = nullptr; // 64 x u64

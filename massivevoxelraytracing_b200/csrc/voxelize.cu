@@ -1000,11 +1000,19 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 		uint32_t slabCap = 0;
 		if( nWarps && keysOut && !recordOff && gridRes <= ( 1 << VR_COORD_BITS ) )
 		{
-			size_t freeB = 0, totalB = 0;
-			cudaMemGetInfo( &freeB, &totalB );
-			const uint64_t hardBudget = std::min<uint64_t>( 4ull << 30, (uint64_t)freeB / 8 );
+			// cudaMemGetInfo takes 0.1 ms when the device is idle and 1 - 20 ms when frees of the previous build are still in flight
+			// (tools/build_device_probe.py, profiles/r4b_vox_timing.log): ask when a mesh is seen for the first time, reuse the answer
+			// while the same mesh is rebuilt (a slab that then fails to allocate falls back to two enumerations below)
+			const bool sameMesh = ctx->lastVoxTriangles == nTriangles && ctx->lastVoxGrid > 0 && ctx->lastVoxPerWarp > 0.0;
+			if( !sameMesh || ctx->voxFreeBytes == 0 )
+			{
+				size_t freeB = 0, totalB = 0;
+				cudaMemGetInfo( &freeB, &totalB );
+				ctx->voxFreeBytes = (uint64_t)freeB;
+			}
+			const uint64_t hardBudget = std::min<uint64_t>( 4ull << 30, ctx->voxFreeBytes / 8 );
 			uint64_t cap = hardBudget / ( 8ull * nWarps );
-			if( ctx->lastVoxTriangles == nTriangles && ctx->lastVoxGrid > 0 && ctx->lastVoxPerWarp > 0.0 )
+			if( sameMesh )
 			{
 				const double scale = (double)gridRes / (double)ctx->lastVoxGrid;
 				cap = std::min<uint64_t>( (uint64_t)( 1.25 * ctx->lastVoxPerWarp * scale * scale ) + 64, cap );
@@ -1014,7 +1022,14 @@ int voxelizeDevice( hako_ctx* ctx, cudaStream_t s, const float* pos, const float
 			static const int capEnv = getenv( "HAKO_VOX_SLAB_CAP" ) ? atoi( getenv( "HAKO_VOX_SLAB_CAP" ) ) : 0; // tests: force overflowing warps
 			if( capEnv > 0 ) slabCap = (uint32_t)capEnv;
 		}
-		if( slabCap && ( r = dalloc( ctx, &slab, (uint64_t)nWarps * slabCap, s ) ) ) break;
+		if( slabCap && dalloc( ctx, &slab, (uint64_t)nWarps * slabCap, s ) )
+		{
+			// no room for the records (the free-memory figure may be stale): enumerate twice instead, and ask again next time
+			cudaGetLastError();
+			slab = nullptr;
+			slabCap = 0;
+			ctx->voxFreeBytes = 0;
+		}
 		cudaError_t e = cudaMemsetAsync( totals, 0, 40, s );
 		if( e != cudaSuccess )
 		{

@@ -15,6 +15,7 @@ for i in range(6):
     wall = (time.perf_counter() - t0) * 1e3
     st = dict(ctx.build_stats()); g.cleanUp()
     if best is None or st['ms_total'] < best[1]['ms_total']: best = (wall, st)
+    if os.environ.get('PROBE_ALL'): print('   build %d: wall %.2f vox %.2f sort %.2f uniq %.2f oct %.2f' % (i, wall, st['ms_voxelize'], st['ms_sort'], st['ms_unique'], st['ms_octree']), flush=True)
 wall, st = best
 print('grid %d resident input: wall %.2f ms | vox %.2f sort %.2f uniq %.2f oct %.2f total %.2f | D %d U %d nodes %d' % (
     grid, wall, st['ms_voxelize'], st['ms_sort'], st['ms_unique'], st['ms_octree'], st['ms_total'], st['dumpedVoxels'], st['uniqueVoxels'], st['numberOfNodes']), flush=True)
