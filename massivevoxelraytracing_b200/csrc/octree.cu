@@ -274,6 +274,123 @@ __global__ void __launch_bounds__( OB_BLOCK, 4 ) leafGroupDagKernel( const uint6
 	if( f != SENTINEL ) atomicMin( &leafFirst[threadIdx.x], f );
 }
 
+// ---- DAG, levels above the leaves: the groups of the previous level's groups ----
+// Same result as groupBuildKernel<false, true> (the temporary 64-byte node, parent key, voxel count and child mask of every group of
+// <= 8 sibling tasks).  There a thread loops over its four items and, for every item that heads a group, walks that group's tasks from
+// global memory: 7 of 32 lanes are active in that walk (profiles/r4e_r4e_octree.json), and the kernel is issue-bound.  Here every thread
+// walks its four tasks ONCE, in registers, with all lanes active, filling the slots of the node under construction; a head closes the
+// node before it (the only divergent part: prefix over the eight counts + the stores), and the last node of a thread continues into the
+// <= 7 tasks of the following threads.
+__global__ void __launch_bounds__( OB_BLOCK ) upperGroupDagKernel( const uint64_t* __restrict__ taskMorton, const uint32_t* __restrict__ taskChild, const uint32_t* __restrict__ taskVox,
+																   uint64_t n, ScanState st, uint64_t* __restrict__ nextMorton, uint32_t* __restrict__ nextVox,
+																   TraceNode* __restrict__ groupNode, uint8_t* __restrict__ groupMask )
+{
+	const uint32_t tile = scanTakeTicket( st ); // has a __syncthreads
+	const uint64_t base = (uint64_t)tile * OB_TILE + (uint64_t)threadIdx.x * OB_ITEMS;
+	static_assert( OB_ITEMS == 4, "vector loads below assume four tasks per thread" );
+	uint64_t m[OB_ITEMS];
+	uint32_t c[OB_ITEMS], v[OB_ITEMS];
+	if( base + OB_ITEMS <= n )
+	{
+		const ulonglong2 m01 = *reinterpret_cast<const ulonglong2*>( taskMorton + base ), m23 = *reinterpret_cast<const ulonglong2*>( taskMorton + base + 2 );
+		const uint4 cc = *reinterpret_cast<const uint4*>( taskChild + base ), vv = *reinterpret_cast<const uint4*>( taskVox + base );
+		m[0] = m01.x, m[1] = m01.y, m[2] = m23.x, m[3] = m23.y;
+		c[0] = cc.x, c[1] = cc.y, c[2] = cc.z, c[3] = cc.w;
+		v[0] = vv.x, v[1] = vv.y, v[2] = vv.z, v[3] = vv.w;
+	}
+	else
+	{
+#pragma unroll
+		for( int i = 0; i < OB_ITEMS; i++ )
+		{
+			const bool in = base + i < n;
+			m[i] = in ? taskMorton[base + i] : 0ull;
+			c[i] = in ? taskChild[base + i] : SENTINEL;
+			v[i] = in ? taskVox[base + i] : 0u;
+		}
+	}
+	uint32_t heads = 0, nHeads = 0;
+	uint64_t prev = ( base > 0 && base <= n ) ? taskMorton[base - 1] : 0ull;
+#pragma unroll
+	for( int i = 0; i < OB_ITEMS; i++ )
+	{
+		const uint64_t idx = base + i;
+		const bool head = ( idx < n ) && ( idx == 0 || ( m[i] >> 3 ) != ( prev >> 3 ) );
+		prev = m[i];
+		if( head )
+		{
+			heads |= 1u << i;
+			nHeads++;
+		}
+	}
+	uint32_t total;
+	const uint32_t excl = blockExclusiveScan<OB_BLOCK>( nHeads, &total );
+	const uint64_t prefix = scanTilePrefix( st, tile, total );
+	uint32_t g = (uint32_t)prefix + excl;
+
+	uint32_t children[8], cnt[8];
+	uint32_t mask = 0;
+	uint64_t parent = 0;
+	bool open = false;
+	auto place = [&]( const uint64_t mj, const uint32_t ch, const uint32_t nv ) {
+		const uint32_t s = (uint32_t)( mj & 7u );
+		mask |= 1u << s;
+#pragma unroll
+		for( int q = 0; q < 8; q++ )
+		{
+			if( q == (int)s )
+			{
+				children[q] = ch;
+				cnt[q] = nv;
+			}
+		}
+	};
+	auto flush = [&]() {
+		// IntersectorOctree.hpp:88-95: exclusive prefix of the voxel counts over the 8 slots
+		uint32_t psum[8];
+		uint32_t sum = 0;
+#pragma unroll
+		for( int q = 0; q < 8; q++ )
+		{
+			psum[q] = sum;
+			sum += cnt[q];
+		}
+		nextMorton[g] = parent;
+		nextVox[g] = sum;
+		groupMask[g] = (uint8_t)mask;
+		storeNode( &groupNode[g], children, psum );
+		g++;
+	};
+#pragma unroll
+	for( int i = 0; i < OB_ITEMS; i++ )
+	{
+		if( ( heads >> i ) & 1u )
+		{
+			if( open ) flush();
+			parent = m[i] >> 3;
+			mask = 0;
+#pragma unroll
+			for( int q = 0; q < 8; q++ )
+			{
+				children[q] = SENTINEL;
+				cnt[q] = 0;
+			}
+			open = true;
+		}
+		if( open && base + i < n ) place( m[i], c[i], v[i] );
+	}
+	if( open )
+	{
+		for( uint64_t j = base + OB_ITEMS; j < n; j++ )
+		{
+			const uint64_t mj = taskMorton[j];
+			if( ( mj >> 3 ) != parent ) break;
+			place( mj, taskChild[j], taskVox[j] );
+		}
+		flush();
+	}
+}
+
 // ---- DAG, leaf level: <= 255 distinct masks ----
 __global__ void __launch_bounds__( 256 ) leafRankKernel( const uint32_t* __restrict__ leafFirst, uint32_t* __restrict__ leafIndexOfMask,
 														 TraceNode* __restrict__ nodes, uint8_t* __restrict__ masks, LevelState* __restrict__ ls )
@@ -585,8 +702,12 @@ int buildOctreeDevice( hako_ctx* ctx, cudaStream_t s, const uint64_t* mortons, u
 				}
 				else
 				{
-					HAKO_LAUNCH_R( ctx, r, kUpperDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
-								 (uint32_t*)nullptr, nodes, masks, 0u, wide );
+					static const bool genericUpper = getenv( "HAKO_OCTREE_GENERIC_UPPER" ) && atoi( getenv( "HAKO_OCTREE_GENERIC_UPPER" ) ) != 0; // A/B knob
+					if( !genericUpper )
+						HAKO_LAUNCH_R( ctx, r, upperGroupDagKernel, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nV, groupNode, groupMask );
+					else
+						HAKO_LAUNCH_R( ctx, r, kUpperDag, (uint32_t)tiles, OB_BLOCK, 0, s, tM, tC, tV, nTasks, st, nM, nC, nV, groupNode, groupMask,
+									 (uint32_t*)nullptr, nodes, masks, 0u, wide );
 					uint32_t tsz = 1;
 					while( tsz < 2 * (uint64_t)Gl ) tsz <<= 1;
 					CK( cudaMemsetAsync( table, 0xFF, (size_t)tsz * 4, s ) );
