@@ -467,9 +467,14 @@ def run_ours(args):
         tris, col, emi, _, _, _ = scene
         from scenes import scene_params
         pt_origin, pt_dps = scene_params(tris, PT_GRID)
-        t0 = time.perf_counter()
-        pt_octree = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, pt_origin, float(pt_dps), PT_GRID)
-        pt_build_ms = (time.perf_counter() - t0) * 1e3
+        pt_build_all = []
+        for _ in range(2):          # the first build at this grid grows the memory pool (hundreds of ms on a run without the build sweep)
+            if pt_octree is not None:
+                pt_octree.cleanUp()
+            t0 = time.perf_counter()
+            pt_octree = hk.IntersectorOctreeGPU(ctx).build(tris, col, emi, None, pt_origin, float(pt_dps), PT_GRID)
+            pt_build_all.append((time.perf_counter() - t0) * 1e3)
+        pt_build_ms = min(pt_build_all)
     if world > 1:
         sync_all()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -483,7 +488,7 @@ def run_ours(args):
     pt_res = run_pt_leg(hk, hdist, nd, ctx, pt_octree, dev, rank, world, args, multi)
     if rank == 0 and pt_res is not None:
         pt_info = pt_octree.info()
-        pt_res["octree"] = {"grid": PT_GRID, "voxels": int(pt_info.numberOfVoxels), "nodes": int(pt_info.numberOfNodes), "build_e2e_ms": pt_build_ms,
+        pt_res["octree"] = {"grid": PT_GRID, "voxels": int(pt_info.numberOfVoxels), "nodes": int(pt_info.numberOfNodes), "build_e2e_ms": pt_build_ms, "build_e2e_ms_first": pt_build_all[0],
                             "device_bytes": int(pt_info.deviceBytes)}
     # the reference's own GPU kernels on this GPU, same scenes (the bar the new kernels must beat)
     ref_gpu = run_reference_gpu(hk, ctx, octree, pt_octree, cams[0], args) if (rank == 0 and not args.no_cpu) else None
