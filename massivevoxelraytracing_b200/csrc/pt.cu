@@ -66,6 +66,8 @@ struct hako_pt
 	uint64_t waveCap = 0;
 	int waveRefillMin = 24, waveBurst = 16; // traceWaveKernel knobs (HAKO_PT_REFILL_MIN / HAKO_PT_BURST); B200 sweep in profiles/r1f_pt_sweep.txt
 	int waveTraceCtas = 5;
+	int waveSmemStack = 1;	   // HAKO_PT_SMEM_STACK=0: traversal stack of the trace waves in local memory (A/B reference)
+	int waveRefillMinSmem = 4; // refill threshold of the trace waves when their stack is in shared memory (refills are cheap there)
 	// ray binning in front of every trace wave (HAKO_PT_BIN = bits per axis of the origin grid, 0 = off): the rays of a wave are
 	// counting-sorted by ( kind, direction octant, Morton code of the origin cell ) and the trace kernel draws them in that order
 	uint32_t* binKeys[PT_LANES] = {};
@@ -872,6 +874,98 @@ __global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveKernel( const Octree
 	if( lane == 0 && steps ) atomicAdd( tp.steps, steps );
 }
 
+// traceWaveKernel with the traversal stack in shared memory (TravStackShared, traverse.cuh): `depth` entries per thread, dynamic shared
+// memory = depth x 24 B (22 B PACKED) x 256 threads per CTA, as many CTAs per SM as that leaves room for.
+template <int MIN_CTAS, bool PACKED>
+__global__ void __launch_bounds__( 256, MIN_CTAS ) traceWaveSmemKernel( const OctreeView tree, const TraceWaveParams tp, const int depth )
+{
+	extern __shared__ __align__( 16 ) unsigned char s_stack[];
+	constexpr int TOPK = 0;
+	// TOPK > 0 (HAKO_SMEM_TOP, A/B variant): the persistent CTA keeps the top TOPK nodes of the tree in shared memory
+	__shared__ uint2 s_top[TOPK > 0 ? TOPK * 8 : 1];
+	TopCache tc{ nullptr, 0xFFFFFFFFu };
+	if( TOPK > 0 ) tc = stageTop<( TOPK > 0 ? TOPK : 1 )>( tree, s_top );
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t nVertices = (uint32_t)*tp.nVertices;
+	const uint32_t stride = (uint32_t)tp.nVertices[-1]; // live paths one vertex earlier: the pitch of the kind-major ray arrays
+	const uint32_t nRays = nVertices * (uint32_t)tp.raysPerVertex;
+	uint32_t wNext = 0, wEnd = 0;
+	bool drained = false;
+	Traversal tr;
+	TravStackShared<PACKED> stk;
+	stk.bind( s_stack, depth, 256, threadIdx.x );
+	bool flying = false, shadow = false;
+	uint32_t addr = 0; // k * stride + slot of the ray in flight
+	uint32_t traced = 0;
+	unsigned long long steps = 0;
+	for( ;; )
+	{
+		const uint32_t idleMask = __ballot_sync( 0xFFFFFFFFu, !flying );
+		if( idleMask == 0xFFFFFFFFu || ( !drained && __popc( idleMask ) >= tp.refillMin ) )
+		{
+			if( !drained && wNext == wEnd )
+			{
+				uint32_t base = 0;
+				if( lane == 0 ) base = (uint32_t)atomicAdd( tp.work, (unsigned long long)PT_CHUNK );
+				base = __shfl_sync( 0xFFFFFFFFu, base, 0 );
+				if( base >= nRays )
+					drained = true;
+				else
+				{
+					wNext = base;
+					wEnd = min( base + PT_CHUNK, nRays );
+				}
+			}
+			if( drained )
+			{
+				if( idleMask == 0xFFFFFFFFu ) break;
+			}
+			else
+			{
+				const uint32_t rank = __popc( idleMask & ( ( 1u << lane ) - 1u ) );
+				const uint32_t avail = wEnd - wNext;
+				if( !flying && rank < avail )
+				{
+					const uint32_t ray = tp.order ? __ldg( tp.order + wNext + rank ) : wNext + rank;
+					const uint32_t k = ray / nVertices, slot = ray - k * nVertices;
+					addr = k * stride + slot;
+					const float4 o = __ldg( &tp.vertices[slot].a );
+					const float4 d = __ldcs( tp.dirs + addr );
+					shadow = tp.shadowFirst && k == 0;
+					flying = tree.wide ? tr.template begin<true>( tree, V3{ o.x, o.y, o.z }, V3{ d.x, d.y, d.z } )
+									   : tr.template begin<false>( tree, V3{ o.x, o.y, o.z }, V3{ d.x, d.y, d.z } );
+					if( !flying ) __stcs( tp.results + addr, make_float4( 0.0f, 0.0f, 0.0f, 0.0f ) ); // misses the root box
+					traced++;
+				}
+				wNext += min( (uint32_t)__popc( idleMask ), avail );
+			}
+		}
+		if( flying )
+		{
+			int it = 0;
+#pragma unroll 1
+			for( ; it < tp.burst; it++ )
+			{
+				const int r = tree.wide ? ( tr.ordinary ? tr.template step<true, true, ( TOPK > 0 ), TravStackShared<PACKED>>( tree, shadow, stk, tc ) : tr.template step<false, true, ( TOPK > 0 ), TravStackShared<PACKED>>( tree, shadow, stk, tc ) )
+										: ( tr.ordinary ? tr.template step<true, false, ( TOPK > 0 ), TravStackShared<PACKED>>( tree, shadow, stk, tc ) : tr.template step<false, false, ( TOPK > 0 ), TravStackShared<PACKED>>( tree, shadow, stk, tc ) );
+				if( r == TRAV_CONTINUE ) continue;
+				flying = false;
+				if( r == TRAV_HIT )
+					__stcs( tp.results + addr, make_float4( tr.t, __uint_as_float( tr.skipped ), __int_as_float( tr.nMajor ), 1.0f ) );
+				else
+					__stcs( tp.results + addr, make_float4( 0.0f, 0.0f, 0.0f, 0.0f ) );
+				it++;
+				break;
+			}
+			steps += (uint32_t)it; // one add per burst, not per step
+		}
+	}
+	for( int off = 16; off; off >>= 1 ) traced += __shfl_down_sync( 0xFFFFFFFFu, traced, off );
+	if( lane == 0 && traced ) atomicAdd( tp.rays, (unsigned long long)traced );
+	for( int off = 16; off; off >>= 1 ) steps += __shfl_down_sync( 0xFFFFFFFFu, steps, off );
+	if( lane == 0 && steps ) atomicAdd( tp.steps, steps );
+}
+
 // per-pixel reduction in localSpp order, then `frameBuffer += `, voxKernel.cu:763-774
 __global__ void __launch_bounds__( 256 ) accumulateKernel( const float4* __restrict__ pathL, float4* __restrict__ accum, uint32_t nPixels )
 {
@@ -1083,9 +1177,10 @@ int hako_pt_create( hako_ctx* ctx, hako_stream stream, hako_pt** out )
 	hako_pt* pt = new hako_pt();
 	pt->ctx = ctx;
 	if( const char* e = getenv( "HAKO_PT_WAVEFRONT" ) ) pt->wavefront = atoi( e );
-	if( const char* e = getenv( "HAKO_PT_REFILL_MIN" ) ) pt->waveRefillMin = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_REFILL_MIN" ) ) pt->waveRefillMin = pt->waveRefillMinSmem = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_BURST" ) ) pt->waveBurst = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_TRACE_CTAS" ) ) pt->waveTraceCtas = atoi( e );
+	if( const char* e = getenv( "HAKO_PT_SMEM_STACK" ) ) pt->waveSmemStack = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_BAND_PATHS" ) ) pt->waveBandPaths = strtoull( e, nullptr, 10 );
 	if( const char* e = getenv( "HAKO_PT_LANES" ) ) pt->lanes = atoi( e );
 	if( const char* e = getenv( "HAKO_PT_BIN" ) ) pt->binBits = std::max( 0, std::min( 6, atoi( e ) ) );
@@ -1376,6 +1471,8 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 		auto kTrace5 = traceWaveKernel<5>;
 		auto kTrace6 = traceWaveKernel<6>;
 		auto kTrace8 = traceWaveKernel<8>;
+		auto kTraceSmem = traceWaveSmemKernel<3, false>;
+		auto kTraceSmemPacked = traceWaveSmemKernel<3, true>;
 		auto kTrace5Top = traceWaveKernel<5, 512>; // HAKO_SMEM_TOP=512: top 512 nodes in shared memory (A/B)
 		static const int topEnv = getenv( "HAKO_SMEM_TOP" ) ? atoi( getenv( "HAKO_SMEM_TOP" ) ) : 0;
 		const int occ = pt->waveTraceCtas >= 8 ? 8 : ( pt->waveTraceCtas >= 6 ? 6 : 5 );
@@ -1451,7 +1548,40 @@ int hako_pt_step( hako_pt* pt, const hako_octree* o, hako_stream stream, const h
 					HAKO_LAUNCH( ctx, binScatterKernel, shadeGrid, 256, 0, ls, bp );
 					tp.order = bp.order;
 				}
-				if( topEnv == 512 )
+				int smemDepth = 0;
+				if( pt->waveSmemStack )
+				{
+					// one push per level at most
+					int lv = 0;
+					while( ( 1 << lv ) < o->gridRes ) lv++;
+					if( o->gridRes > 0 && lv >= 1 && lv <= HAKO_STACK_DEPTH ) smemDepth = lv;
+				}
+				// whole 24-byte entries when three CTAs of them fit an SM (up to 4096^3), else 22-byte entries; trees too deep for three CTAs
+				// of those keep the stack in local memory (two CTAs per SM measured no faster than the local stack at 5)
+				auto ctasFor = []( size_t bytes ) { return (uint32_t)std::min<size_t>( 4, ( 227u * 1024u ) / ( bytes + 1024 ) ); };
+				const size_t smemBytes24 = (size_t)smemDepth * 24 * 256, smemBytes22 = (size_t)smemDepth * 22 * 256;
+				const bool smemPacked = smemDepth && ctasFor( smemBytes24 ) < 3;
+				const size_t smemBytes = smemPacked ? smemBytes22 : smemBytes24;
+				const uint32_t smemPerSm = smemDepth ? ctasFor( smemBytes ) : 0u;
+				const bool smemStack = smemDepth && smemPerSm >= 3;
+				if( smemStack )
+				{
+					tp.refillMin = std::max( 1, std::min( 32, pt->waveRefillMinSmem ) );
+					static size_t configured[16][2] = {};
+					if( configured[ctx->device & 15][smemPacked] < smemBytes )
+					{
+						if( smemPacked )
+							HAKO_CUDA( cudaFuncSetAttribute( kTraceSmemPacked, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes ) );
+						else
+							HAKO_CUDA( cudaFuncSetAttribute( kTraceSmem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes ) );
+						configured[ctx->device & 15][smemPacked] = smemBytes;
+					}
+					if( smemPacked )
+						HAKO_LAUNCH( ctx, kTraceSmemPacked, smemPerSm * ctx->smCount, 256, smemBytes, ls, q.tree, tp, smemDepth );
+					else
+						HAKO_LAUNCH( ctx, kTraceSmem, smemPerSm * ctx->smCount, 256, smemBytes, ls, q.tree, tp, smemDepth );
+				}
+				else if( topEnv == 512 )
 					HAKO_LAUNCH( ctx, kTrace5Top, traceGrid, 256, 0, ls, q.tree, tp );
 				else if( occ == 8 )
 					HAKO_LAUNCH( ctx, kTrace8, traceGrid, 256, 0, ls, q.tree, tp );

@@ -40,6 +40,71 @@ struct TravStack
 {
 	uint4 a[HAKO_STACK_DEPTH]; // node, tx1, ty1, tz1
 	uint2 b[HAKO_STACK_DEPTH]; // childMask | level << 8, nVoxelSkipped
+	__device__ __forceinline__ void push( int& sp, const uint4 na, const uint2 nb )
+	{
+		a[sp] = na;
+		b[sp] = nb;
+		sp++;
+	}
+	__device__ __forceinline__ void pop( int& sp, uint4& oa, uint2& ob )
+	{
+		sp--;
+		oa = a[sp];
+		ob = b[sp];
+	}
+};
+// The same stack in SHARED memory, entry-major and thread-minor: entry k of thread t is a[k * BLOCK + t] / b[k * BLOCK + t], so a thread's
+// banks depend on t only and a warp's pushes and pops are conflict-free whatever the depths of its lanes.  Local memory interleaves the
+// lanes of a warp word by word instead: the 24-byte entries of lanes at d different depths cost 6 d L1 tag look-ups per push and per pop,
+// and in the trace waves of the path tracer that traffic is 85 % of all L1 sectors (profiles/r3s).  `depth` entries per thread (the tree's
+// number of levels: at most one push per level) bound the threads per SM: depth x 24 B x threads <= 227 KB, 768 threads up to 4096^3.
+// PACKED squeezes an entry into 22 bytes (the child mask in progress is 3 bits, the level 5) at the price of a few instructions per push
+// and pop, which keeps 768 threads at 8192^3.  Tried and much slower than either: the 8-byte half of an entry left in local memory, and
+// only the first K entries in shared memory with the rest in local memory (profiles/r4l, r4m).
+template <bool PACKED>
+struct TravStackShared
+{
+	uint4* a;	 // node, tx1, ty1, tz1
+	uint2* b;	 // !PACKED: childMask | level << 8 [| mask << 16], nVoxelSkipped
+	uint32_t* s; // PACKED: nVoxelSkipped
+	uint16_t* c; // PACKED: childMask (3 bits) | level (5 bits) | mask of the node (wide trees, 8 bits)
+	uint32_t stride; // threads per CTA
+	static constexpr int ENTRY_BYTES = PACKED ? 22 : 24;
+	// pointers into a CTA's dynamic shared memory for `depth` entries per thread
+	__device__ __forceinline__ void bind( unsigned char* smem, int depth, uint32_t threads, uint32_t tid )
+	{
+		stride = threads;
+		a = (uint4*)smem + tid;
+		b = (uint2*)( smem + (size_t)depth * threads * 16 ) + tid;
+		s = (uint32_t*)( smem + (size_t)depth * threads * 16 ) + tid;
+		c = (uint16_t*)( smem + (size_t)depth * threads * 20 ) + tid;
+	}
+	__device__ __forceinline__ void push( int& sp, const uint4 na, const uint2 nb )
+	{
+		const uint32_t i = (uint32_t)sp * stride;
+		a[i] = na;
+		if( PACKED )
+		{
+			s[i] = nb.y;
+			c[i] = (uint16_t)( ( nb.x & 7u ) | ( ( ( nb.x >> 8 ) & 31u ) << 3 ) | ( ( nb.x >> 16 ) << 8 ) );
+		}
+		else
+			b[i] = nb;
+		sp++;
+	}
+	__device__ __forceinline__ void pop( int& sp, uint4& oa, uint2& ob )
+	{
+		sp--;
+		const uint32_t i = (uint32_t)sp * stride;
+		oa = a[i];
+		if( PACKED )
+		{
+			const uint32_t p = c[i];
+			ob = make_uint2( ( p & 7u ) | ( ( ( p >> 3 ) & 31u ) << 8 ) | ( ( p >> 8 ) << 16 ), s[i] );
+		}
+		else
+			ob = b[i];
+	}
 };
 // Optional shared-memory copy of the LAST `count` nodes of the array = the top of the tree (numbering is bottom-up, the root is
 // last): north_star's "octree top staged in shared memory".  Built per CTA by stageTop(); step<.., TOP = true> reads a node's slot
@@ -128,8 +193,8 @@ struct Traversal
 	// 0 < lmax): one FMNMX3 instead of two FSETP + FSEL pairs, ~6 of ~95 instructions per step.  Rays with huge slab distances
 	// (a zero or denormal direction component against the clamped 1/rd) can produce inf - inf = NaN, where the two forms
 	// differ; they take the exact path (tests/test_gpu_traverse.py::test_random_rays_and_shadow has such rays).
-	template <bool FINITE = false, bool WIDE = false, bool TOP = false>
-	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, TravStack& stk, const TopCache tc = TopCache{ nullptr, 0xFFFFFFFFu } )
+	template <bool FINITE = false, bool WIDE = false, bool TOP = false, class STACK = TravStack>
+	__device__ __forceinline__ int step( const OctreeView& v, const bool shadow, STACK& stk, const TopCache tc = TopCache{ nullptr, 0xFFFFFFFFu } )
 	{
 		const float scale = levelScale( level );
 		// :317-319 t0 is recomputed from t1 each visit
@@ -171,9 +236,8 @@ struct Traversal
 			{
 				if( hasNext )
 				{
-					stk.a[sp] = make_uint4( node, __float_as_uint( tx1 ), __float_as_uint( ty1 ), __float_as_uint( tz1 ) );
-					stk.b[sp] = make_uint2( childMask | ( level << 8 ) | ( WIDE ? nmask << 16 : 0u ), skipped );
-					sp++;
+					stk.push( sp, make_uint4( node, __float_as_uint( tx1 ), __float_as_uint( ty1 ), __float_as_uint( tz1 ) ),
+							  make_uint2( childMask | ( level << 8 ) | ( WIDE ? nmask << 16 : 0u ), skipped ) );
 				}
 				const uint32_t nidx = WIDE ? node : ( node & 0xFFFFFFu );
 				const uint2 slot = ( TOP && nidx >= tc.base ) ? tc.slots[( nidx - tc.base ) * 8u + ci] : ldg_u2( &v.nodes[nidx].slot[ci] );
@@ -193,9 +257,9 @@ struct Traversal
 		{
 			// :414-422
 			if( sp == 0 ) return TRAV_MISS;
-			sp--;
-			const uint4 a = stk.a[sp];
-			const uint2 b = stk.b[sp];
+			uint4 a;
+			uint2 b;
+			stk.pop( sp, a, b );
 			node = a.x;
 			tx1 = __uint_as_float( a.y );
 			ty1 = __uint_as_float( a.z );

@@ -170,8 +170,15 @@ def test_pt_modes_identical(hk, ctx, pt, scene, monkeypatch, with_env, with_emis
                 # rays of every trace wave binned by (kind, octant, origin cell): another order of the same rays
                 {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "4"},
                 {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "6", "HAKO_PT_BIN_CELL_MAJOR": "1", "HAKO_PT_LANES": "2"},
-                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "1", "HAKO_PT_BAND_PATHS": str(W * 16 * 12)}):
-        for k in ("HAKO_PT_WAVEFRONT", "HAKO_PT_BAND_PATHS", "HAKO_PT_REFILL_MIN", "HAKO_PT_BURST", "HAKO_PT_LANES", "HAKO_PT_BIN", "HAKO_PT_BIN_CELL_MAJOR"):
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_BIN": "1", "HAKO_PT_BAND_PATHS": str(W * 16 * 12)},
+                # traversal stack of the trace waves in shared memory
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_SMEM_STACK": "1"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_SMEM_STACK": "1", "HAKO_PT_REFILL_MIN": "24"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_SMEM_STACK": "1", "HAKO_PT_REFILL_MIN": "8", "HAKO_PT_LANES": "2"},
+                # ... and in local memory (the default is shared memory)
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_SMEM_STACK": "0"},
+                {"HAKO_PT_WAVEFRONT": "2", "HAKO_PT_SMEM_STACK": "0", "HAKO_PT_REFILL_MIN": "4"}):
+        for k in ("HAKO_PT_WAVEFRONT", "HAKO_PT_BAND_PATHS", "HAKO_PT_REFILL_MIN", "HAKO_PT_BURST", "HAKO_PT_LANES", "HAKO_PT_BIN", "HAKO_PT_BIN_CELL_MAJOR", "HAKO_PT_SMEM_STACK"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)

@@ -225,6 +225,19 @@ def test_wide_index_layout_matches_reference_layout(hk, ctx, bunny, small_cases,
         pcam = hk.camera_lookat((4, 4, 4), (0, 0, 0), width=96, height=64, focus=6.0, lensR=0.01)
         pt.step(None, pcam)
         acc = pt.accumulators().copy()
+        # the trace waves keep their traversal stack in shared memory by default; the local-memory form must agree (wide trees carry
+        # the node's mask in the stack entry)
+        monkeypatch.setenv("HAKO_PT_SMEM_STACK", "0")
+        pt2 = hk.PathTracer(ctx).setup()
+        monkeypatch.delenv("HAKO_PT_SMEM_STACK")
+        pt2.m_intersectorOctreeGPU = g
+        pt2.maxDepth = 4
+        pt2.resizeFrameBufferIfNeeded(None, 96, 64)
+        pt2.loadHDRI(None, env)
+        pt2.step(None, pcam)
+        assert np.array_equal(pt2.accumulators().view(np.uint32), acc.view(np.uint32))
+        pt2.m_intersectorOctreeGPU = hk.IntersectorOctreeGPU(ctx)
+        pt2.cleanUp()
         if force == "1":
             with pytest.raises(hk.HakoError):
                 g.export(True, False, False)
