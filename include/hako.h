@@ -18,6 +18,9 @@
  *     results have landed in them; the *_device variants take DEVICE pointers and only enqueue work.
  *   - handles are opaque and owned by the library; one hako_ctx per device, no hidden statics
  *     (unlike `static thrs::RadixSort`, IntersectorOctreeGPU.hpp:58).
+ *   - a hako_ctx (and the octrees / path tracers made from it) may be used by ONE thread at a time: it owns staging buffers, build
+ *     statistics and internal streams that calls share.  Use one context per thread (several contexts per device are fine), as
+ *     tests/cpp/shim_demo.cpp does with one thread per GPU.
  *   - there is NO CPU fallback: every call fails with HAKO_E_CUDA when no sm_100 device is usable.
  */
 #ifndef HAKO_H
